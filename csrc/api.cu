@@ -1,0 +1,181 @@
+// extern "C" surface of libpsb200.so: argument checks, error text, launches.  See include/psb200.h.
+#include <stdarg.h>
+#include <string.h>
+
+#include "comm.cuh"
+
+static thread_local char g_err[512] = "";
+void psb_set_error(const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+
+int psb_launch_worker_simt(const PsbSolver*, const CommCtx&, int, const void*, const int*, const int*, const float*,
+                           float*, float*, int*, float*, cudaStream_t);
+int psb_launch_worker_tc(const PsbSolver*, const CommCtx&, int, const void*, const int*, const int*, const float*,
+                         float*, float*, int*, float*, cudaStream_t);
+int psb_launch_eval_simt(const void*, const int*, int, const float*, int, int, int*, cudaStream_t);
+int psb_launch_eval_tc(const void*, const int*, int, const float*, int, int, int*, cudaStream_t);
+int psb_launch_eval_finalize(const int*, float*, cudaStream_t);
+int psb_launch_ring_scatter(const uint32_t*, int, int, void*, int*, int, int, cudaStream_t);
+int psb_launch_ring_store_dense(const void*, int, const int*, const int*, int, void*, int*, int, int, cudaStream_t);
+int psb_launch_apply_delta(float*, const float*, float, int, int, cudaStream_t);
+
+extern "C" {
+
+const char* psb_last_error(void) { return g_err; }
+int psb_version(void) { return 100; }
+
+size_t psb_comm_block_bytes(int num_features, int num_ranks) { return CommLayout::make(num_features, num_ranks).bytes; }
+
+__global__ void psb_comm_init_kernel(CommBlock blk, const float4* __restrict__ w0, int rank) {
+    const CommLayout& L = blk.L;
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < L.n4) {
+        const float4 v = w0[i];
+        blk.rep(0)[i] = v;
+        blk.rep(1)[i] = v;
+        const int b = L.slice_begin(rank), e = L.slice_end(rank);
+        if (i >= b && i < e) blk.auth()[i - b] = v;
+    }
+}
+
+int psb_comm_init_block(void* d_block, const float* d_w0, int num_features, int num_ranks, int rank, void* stream) {
+    PSB_REQUIRE(d_block && d_w0, "psb_comm_init_block: null pointer");
+    PSB_REQUIRE(num_ranks >= 1 && num_ranks <= PSB_MAX_RANKS, "num_ranks must be in [1,%d]", PSB_MAX_RANKS);
+    PSB_REQUIRE(rank >= 0 && rank < num_ranks, "rank out of range");
+    const CommLayout L = CommLayout::make(num_features, num_ranks);
+    cudaStream_t st = (cudaStream_t)stream;
+    PSB_CHECK_CUDA(cudaMemsetAsync(d_block, 0, L.bytes, st));
+    psb_comm_init_kernel<<<(L.n4 + 255) / 256, 256, 0, st>>>(CommBlock(d_block, L), (const float4*)d_w0, rank);
+    PSB_CHECK_CUDA(cudaGetLastError());
+    return 0;
+}
+
+float* psb_comm_replica(void* d_block, int num_features, int num_ranks, int parity) {
+    return (float*)CommBlock(d_block, CommLayout::make(num_features, num_ranks)).rep(parity & 1);
+}
+float* psb_comm_shard_weights(void* d_block, int num_features, int num_ranks) {
+    return (float*)CommBlock(d_block, CommLayout::make(num_features, num_ranks)).auth();
+}
+unsigned int* psb_comm_status(void* d_block, int num_features, int num_ranks) {
+    return CommBlock(d_block, CommLayout::make(num_features, num_ranks)).status();
+}
+
+size_t psb_worker_scratch_bytes(int num_features) {
+    return (size_t)PSB_SCRATCH_VECS * (num_features + 1) * PSB_CLASS_PAD * sizeof(float);
+}
+
+int psb_worker_step(const PsbSolver* s, const PsbComm* comm, int num_workers, int impl, const void* d_X,
+                    const int* d_labels, const int* d_win, const float* d_w_in, float* d_delta, float* d_loss,
+                    int* d_info, float* d_scratch, void* stream) {
+    PSB_REQUIRE(s && comm, "psb_worker_step: null solver/comm");
+    PSB_REQUIRE(num_workers >= 1, "num_workers must be >= 1");
+    PSB_REQUIRE(s->num_class_rows >= 2 && s->num_class_rows <= PSB_CLASS_PAD, "num_class_rows must be in [2,8]");
+    PSB_REQUIRE(s->num_features >= 2 && s->cap >= 1, "bad num_features/cap");
+    PSB_REQUIRE(d_X && d_labels && d_win && d_loss && d_info && d_scratch, "psb_worker_step: null buffer");
+    PSB_REQUIRE(s->max_iter >= 0 && s->max_iter <= 64, "max_iter out of range");
+    CommCtx cx;
+    cx.c = *comm;
+    if (comm->mode == PSB_COMM_NONE) {
+        PSB_REQUIRE(d_w_in && d_delta, "comm mode NONE needs d_w_in and d_delta");
+        cx.L = CommLayout::make(s->num_features, 1);
+    } else {
+        PSB_REQUIRE(comm->num_ranks >= 1 && comm->num_ranks <= PSB_MAX_RANKS, "num_ranks out of range");
+        PSB_REQUIRE(comm->rank >= 0 && comm->rank < comm->num_ranks, "rank out of range");
+        PSB_REQUIRE(comm->workers_per_rank == num_workers, "workers_per_rank must equal num_workers");
+        for (int q = 0; q < comm->num_ranks; ++q) PSB_REQUIRE(comm->peers[q], "peer block %d is null", q);
+        cx.L = CommLayout::make(s->num_features, comm->num_ranks);
+    }
+    if (impl == 0)
+        return psb_launch_worker_simt(s, cx, num_workers, d_X, d_labels, d_win, d_w_in, d_delta, d_loss, d_info,
+                                      d_scratch, (cudaStream_t)stream);
+    return psb_launch_worker_tc(s, cx, num_workers, d_X, d_labels, d_win, d_w_in, d_delta, d_loss, d_info, d_scratch,
+                                (cudaStream_t)stream);
+}
+
+int psb_apply_delta(float* d_w, const float* d_delta, float lr, int num_features, int skip_class, void* stream) {
+    PSB_REQUIRE(d_w && d_delta, "psb_apply_delta: null pointer");
+    return psb_launch_apply_delta(d_w, d_delta, lr, num_features, skip_class, (cudaStream_t)stream);
+}
+
+int psb_eval(const void* d_X, const int* d_labels, int n, const float* d_w, int num_features, int num_class_rows,
+             int* d_conf, float* d_out, int impl, void* stream) {
+    PSB_REQUIRE(d_X && d_labels && d_w && d_conf && d_out, "psb_eval: null pointer");
+    PSB_REQUIRE(n >= 0 && num_features >= 2 && num_features % 2 == 0, "psb_eval: bad shape");
+    PSB_REQUIRE(num_class_rows >= 2 && num_class_rows <= PSB_CLASS_PAD, "num_class_rows must be in [2,8]");
+    cudaStream_t st = (cudaStream_t)stream;
+    PSB_CHECK_CUDA(cudaMemsetAsync(d_conf, 0, 64 * sizeof(int), st));
+    int rc = 0;
+    if (n > 0)
+        rc = impl == 0 ? psb_launch_eval_simt(d_X, d_labels, n, d_w, num_features, num_class_rows, d_conf, st)
+                       : psb_launch_eval_tc(d_X, d_labels, n, d_w, num_features, num_class_rows, d_conf, st);
+    if (rc) return rc;
+    return psb_launch_eval_finalize(d_conf, d_out, st);
+}
+
+int psb_ring_scatter(const uint32_t* d_stage, int n, int stride_words, void* d_X, int* d_labels, int cap,
+                     int num_features, void* stream) {
+    PSB_REQUIRE(d_stage && d_X && d_labels, "psb_ring_scatter: null pointer");
+    PSB_REQUIRE(num_features % 8 == 0, "num_features must be a multiple of 8");
+    return psb_launch_ring_scatter(d_stage, n, stride_words, d_X, d_labels, cap, num_features, (cudaStream_t)stream);
+}
+int psb_ring_store_dense(const void* d_rows, int src_half, const int* d_labels_in, const int* d_worker_slot, int n,
+                         void* d_X, int* d_labels, int cap, int num_features, void* stream) {
+    PSB_REQUIRE(d_rows && d_labels_in && d_worker_slot && d_X && d_labels, "psb_ring_store_dense: null pointer");
+    PSB_REQUIRE(num_features % 8 == 0, "num_features must be a multiple of 8");
+    return psb_launch_ring_store_dense(d_rows, src_half, d_labels_in, d_worker_slot, n, d_X, d_labels, cap,
+                                       num_features, (cudaStream_t)stream);
+}
+
+// ------------------------------------------------------------------ peer memory plumbing
+int psb_malloc(void** d_ptr_out, size_t bytes) {
+    PSB_REQUIRE(d_ptr_out && bytes > 0, "psb_malloc: bad arguments");
+    PSB_CHECK_CUDA(cudaMalloc(d_ptr_out, bytes));
+    return 0;
+}
+int psb_free(void* d_ptr) {
+    PSB_CHECK_CUDA(cudaFree(d_ptr));
+    return 0;
+}
+int psb_ipc_export(void* d_ptr, unsigned char handle_out[64]) {
+    cudaIpcMemHandle_t h;
+    PSB_CHECK_CUDA(cudaIpcGetMemHandle(&h, d_ptr));
+    static_assert(sizeof(h) == 64, "cudaIpcMemHandle_t is 64 bytes");
+    memcpy(handle_out, &h, 64);
+    return 0;
+}
+int psb_ipc_import(const unsigned char handle[64], void** d_ptr_out) {
+    cudaIpcMemHandle_t h;
+    memcpy(&h, handle, 64);
+    PSB_CHECK_CUDA(cudaIpcOpenMemHandle(d_ptr_out, h, cudaIpcMemLazyEnablePeerAccess));
+    return 0;
+}
+int psb_ipc_close(void* d_ptr) {
+    PSB_CHECK_CUDA(cudaIpcCloseMemHandle(d_ptr));
+    return 0;
+}
+int psb_enable_peer_access(int num_devices) {
+    int cur = 0;
+    PSB_CHECK_CUDA(cudaGetDevice(&cur));
+    for (int d = 0; d < num_devices; ++d) {
+        if (d == cur) continue;
+        int can = 0;
+        PSB_CHECK_CUDA(cudaDeviceCanAccessPeer(&can, cur, d));
+        if (!can) {
+            psb_set_error("device %d cannot access peer %d", cur, d);
+            return PSB_E_CUDA;
+        }
+        cudaError_t e = cudaDeviceEnablePeerAccess(d, 0);
+        if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) {
+            psb_set_error("cudaDeviceEnablePeerAccess(%d): %s", d, cudaGetErrorString(e));
+            return PSB_E_CUDA;
+        }
+        cudaGetLastError();
+    }
+    return 0;
+}
+
+}  // extern "C"

@@ -1,0 +1,163 @@
+// Fused pull / push / apply over NVLink peer memory (device side).
+//
+// Replaces: WEIGHTS_TOPIC broadcast (ServerProcessor.java:172-182), GRADIENTS_TOPIC push
+// (WorkerTrainingProcessor.java:95-97), the server's w += lr*g loop (ServerProcessor.java:148-151,
+// 225-228) and the MessageTracker gating (MessageTracker.java:69-87).  There is no server process:
+// the parameter vector is cut into num_ranks shards; rank s owns shard s.
+//
+// Sequential (BSP) protocol for clock v, parity p = v & 1:
+//   pull   : wait until version[s] >= v for every shard s (local acquire spins), read replica[p].
+//   push   : workers of a GPU reduce their deltas into acc[p] with 16-byte REDs (L2); the last one to
+//            finish (ticket) stores the GPU's slice s of the sum into owner s's inbox[p][rank] over
+//            P2P, fences, and bumps owner s's arrival counter.
+//   apply  : whoever observes the last arrival of shard s (ticket == num_ranks-1) sums the inbox
+//            slices in rank order (deterministic), computes w = replica[p] + lr * sum and writes it
+//            into replica[p^1] of EVERY rank, then releases version[s] = v+1 on every rank.
+// A weights "message" is therefore a replica half plus a version word; a gradient "message" is an
+// inbox slice plus an arrival count.  Quiescent snapshot: replica[p] is never written during clock v.
+//
+// Async protocol (eventual, or bounded delay k):
+//   pull   : wait until min_q clock[q] >= v - k (skipped when k < 0), read every shard from its owner.
+//   push   : the GPU's last worker REDs lr * (sum of deltas) straight into the owners' shards
+//            (apply == the reduction), fences, then publishes clock[rank] = v+1 on every rank.
+#pragma once
+#include "common.cuh"
+
+#define PSB_ERR_PULL_TIMEOUT 1u
+#define PSB_ERR_GATE_TIMEOUT 2u
+
+struct CommCtx {
+    PsbComm c;
+    CommLayout L;
+};
+
+// ---- pull: all threads of the CTA; loads the start weights into dst (global or shared), n4 float4s.
+__device__ __forceinline__ bool comm_pull(const CommCtx& cx, float4* dst) {
+    const PsbComm& c = cx.c;
+    CommBlock me(c.peers[c.rank], cx.L);
+    __shared__ int s_ok;
+    if (threadIdx.x == 0) s_ok = 1;
+    __syncthreads();
+    if (c.mode == PSB_COMM_SEQUENTIAL) {
+        if (threadIdx.x < c.num_ranks) {
+            if (!wait_ge_sys(me.version() + threadIdx.x, (unsigned)c.clock, c.spin_limit, me.status(),
+                             PSB_ERR_PULL_TIMEOUT))
+                s_ok = 0;
+        }
+        __syncthreads();
+        if (!s_ok) return false;
+        const float4* src = me.rep(c.clock & 1);
+        for (int i = threadIdx.x; i < cx.L.n4; i += blockDim.x) dst[i] = ld_cg_v4(src + i);
+    } else {
+        if (c.max_delay >= 0 && c.clock > c.max_delay) {
+            if (threadIdx.x < c.num_ranks) {
+                if (!wait_ge_sys(me.clocks() + threadIdx.x, (unsigned)(c.clock - c.max_delay), c.spin_limit,
+                                 me.status(), PSB_ERR_GATE_TIMEOUT))
+                    s_ok = 0;
+            }
+            __syncthreads();
+            if (!s_ok) return false;
+        }
+        for (int s = 0; s < c.num_ranks; ++s) {
+            CommBlock owner(c.peers[s], cx.L);
+            const int b = cx.L.slice_begin(s), e = cx.L.slice_end(s);
+            const float4* src = owner.auth();
+            for (int i = b + threadIdx.x; i < e; i += blockDim.x) dst[i] = ld_relaxed_sys_v4(src + (i - b));
+        }
+    }
+    __syncthreads();
+    return true;
+}
+
+// ---- push + apply: all threads of the CTA; delta (n4 float4s, global or shared) is this worker's result.
+__device__ __forceinline__ void comm_push(const CommCtx& cx, const float4* delta) {
+    const PsbComm& c = cx.c;
+    const CommLayout& L = cx.L;
+    CommBlock me(c.peers[c.rank], L);
+    const int p = c.clock & 1;
+    __shared__ unsigned int s_ticket;
+    __shared__ unsigned int s_apply_mask;
+
+    // 1. intra-GPU reduction in L2
+    float4* acc = me.acc(p);
+    for (int i = threadIdx.x; i < L.n4; i += blockDim.x) red_add_v4(acc + i, delta[i]);
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        s_ticket = atom_add_acqrel_gpu(me.ticket(p), 1u);
+        s_apply_mask = 0u;
+    }
+    __syncthreads();
+    if (s_ticket != (unsigned)c.workers_per_rank - 1u) return;   // not the last worker of this GPU
+    __threadfence();
+
+    if (c.mode == PSB_COMM_SEQUENTIAL) {
+        // 2. mailbox stores: my GPU's sum, cut into shards, into each owner's inbox[p][rank]
+        for (int s = 0; s < c.num_ranks; ++s) {
+            CommBlock owner(c.peers[s], L);
+            const int b = L.slice_begin(s), e = L.slice_end(s);
+            float4* box = owner.inbox(p, c.rank);
+            for (int i = b + threadIdx.x; i < e; i += blockDim.x) {
+                st_cg_v4(box + (i - b), ld_cg_v4(acc + i));
+                st_cg_v4(acc + i, make_float4(0.f, 0.f, 0.f, 0.f));      // ready for clock v+2
+            }
+        }
+        if (threadIdx.x == 0) *me.ticket(p) = 0u;
+        fence_acq_rel_sys();
+        __syncthreads();
+        // 3. arrival tickets, one thread per shard
+        if (threadIdx.x < c.num_ranks) {
+            CommBlock owner(c.peers[threadIdx.x], L);
+            const unsigned t = atom_add_acqrel_sys(owner.arrivals(p), 1u);
+            if (t == (unsigned)c.num_ranks - 1u) atomicOr(&s_apply_mask, 1u << threadIdx.x);
+        }
+        __syncthreads();
+        unsigned mask = s_apply_mask;
+        if (!mask) return;
+        fence_acq_rel_sys();
+        // 4. apply the shards whose last arrival we saw, broadcast into everyone's next replica
+        const float4* w_old = me.rep(p);
+        for (int s = 0; s < c.num_ranks; ++s) {
+            if (!(mask & (1u << s))) continue;
+            CommBlock owner(c.peers[s], L);
+            const int b = L.slice_begin(s), e = L.slice_end(s);
+            for (int i = b + threadIdx.x; i < e; i += blockDim.x) {
+                float4 sum = make_float4(0.f, 0.f, 0.f, 0.f);
+                for (int q = 0; q < c.num_ranks; ++q) {
+                    const float4 g = ld_relaxed_sys_v4(owner.inbox(p, q) + (i - b));
+                    sum.x += g.x, sum.y += g.y, sum.z += g.z, sum.w += g.w;
+                }
+                const float4 w = ld_cg_v4(w_old + i);
+                const float4 nw = make_float4(fmaf(c.lr, sum.x, w.x), fmaf(c.lr, sum.y, w.y), fmaf(c.lr, sum.z, w.z),
+                                              fmaf(c.lr, sum.w, w.w));
+                for (int q = 0; q < c.num_ranks; ++q) st_cg_v4(CommBlock(c.peers[q], L).rep(p ^ 1) + i, nw);
+            }
+        }
+        fence_acq_rel_sys();
+        __syncthreads();
+        if (threadIdx.x < c.num_ranks && (mask & (1u << threadIdx.x))) {
+            const int s = threadIdx.x;
+            *CommBlock(c.peers[s], L).arrivals(p) = 0u;
+            fence_acq_rel_sys();
+            for (int q = 0; q < c.num_ranks; ++q)
+                st_release_sys(CommBlock(c.peers[q], L).version() + s, (unsigned)c.clock + 1u);
+        }
+    } else {
+        // async: apply == reduction, straight into the owners' authoritative shards
+        for (int s = 0; s < c.num_ranks; ++s) {
+            CommBlock owner(c.peers[s], L);
+            const int b = L.slice_begin(s), e = L.slice_end(s);
+            float4* w = owner.auth();
+            for (int i = b + threadIdx.x; i < e; i += blockDim.x) {
+                float4 g = ld_cg_v4(acc + i);
+                st_cg_v4(acc + i, make_float4(0.f, 0.f, 0.f, 0.f));
+                red_add_v4_sys(w + (i - b), make_float4(c.lr * g.x, c.lr * g.y, c.lr * g.z, c.lr * g.w));
+            }
+        }
+        if (threadIdx.x == 0) *me.ticket(p) = 0u;
+        fence_acq_rel_sys();
+        __syncthreads();
+        if (threadIdx.x < c.num_ranks)
+            st_release_sys(CommBlock(c.peers[threadIdx.x], L).clocks() + c.rank, (unsigned)c.clock + 1u);
+    }
+}

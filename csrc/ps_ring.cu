@@ -1,0 +1,95 @@
+// K1: device side of ingestion — scatter a staged batch of rows into the workers' dense fp16 ring
+// slots.  The host (producer thread / DynamicBuffer) decides the slot of every row: the buffer policy
+// of WorkerSamplingProcessor.java:50-113 collapses to "write at head, window = last count rows",
+// so the device only needs (worker, slot) per row and the (head, count) pair per worker.
+#include "common.cuh"
+
+// staged row: word0 nnz, word1 label, word2 worker, word3 slot, then nnz x (int32 index, fp32 value)
+__global__ void __launch_bounds__(256) psb_ring_scatter_kernel(const uint32_t* __restrict__ stage, int n,
+                                                              int stride_words, __half* __restrict__ X,
+                                                              int* __restrict__ labels, int cap, int F) {
+    for (int r = blockIdx.x; r < n; r += gridDim.x) {
+        const uint32_t* row = stage + (size_t)r * stride_words;
+        const int nnz = (int)row[0], worker = (int)row[2], slot = (int)row[3];
+        __half* dst = X + ((size_t)worker * cap + slot) * F;
+        // zero-fill then scatter: two phases, rows are short
+        uint4* d16 = (uint4*)dst;
+        for (int i = threadIdx.x; i < F / 8; i += blockDim.x) d16[i] = make_uint4(0, 0, 0, 0);
+        __syncthreads();
+        for (int e = threadIdx.x; e < nnz; e += blockDim.x) {
+            const int idx = (int)row[4 + 2 * e];
+            const float v = __uint_as_float(row[5 + 2 * e]);
+            if (idx >= 0 && idx < F) dst[idx] = __float2half_rn(v);
+        }
+        if (threadIdx.x == 0) labels[(size_t)worker * cap + slot] = (int)row[1];
+        __syncthreads();
+    }
+}
+
+__global__ void __launch_bounds__(256) psb_ring_store_half_kernel(const __half* __restrict__ rows,
+                                                                 const int* __restrict__ labels_in,
+                                                                 const int* __restrict__ worker_slot, int n,
+                                                                 __half* __restrict__ X, int* __restrict__ labels,
+                                                                 int cap, int F) {
+    for (int r = blockIdx.x; r < n; r += gridDim.x) {
+        const int worker = worker_slot[2 * r], slot = worker_slot[2 * r + 1];
+        const uint4* src = (const uint4*)(rows + (size_t)r * F);
+        uint4* dst = (uint4*)(X + ((size_t)worker * cap + slot) * F);
+        for (int i = threadIdx.x; i < F / 8; i += blockDim.x) dst[i] = src[i];
+        if (threadIdx.x == 0) labels[(size_t)worker * cap + slot] = labels_in[r];
+    }
+}
+
+__global__ void __launch_bounds__(256) psb_ring_store_dense_kernel(const float* __restrict__ rows,
+                                                                  const int* __restrict__ labels_in,
+                                                                  const int* __restrict__ worker_slot, int n,
+                                                                  __half* __restrict__ X, int* __restrict__ labels,
+                                                                  int cap, int F) {
+    for (int r = blockIdx.x; r < n; r += gridDim.x) {
+        const int worker = worker_slot[2 * r], slot = worker_slot[2 * r + 1];
+        const float2* src = (const float2*)(rows + (size_t)r * F);
+        __half2* dst = (__half2*)(X + ((size_t)worker * cap + slot) * F);
+        for (int i = threadIdx.x; i < F / 2; i += blockDim.x) dst[i] = __float22half2_rn(src[i]);
+        if (threadIdx.x == 0) labels[(size_t)worker * cap + slot] = labels_in[r];
+    }
+}
+
+__global__ void psb_apply_delta_kernel(float* __restrict__ w, const float* __restrict__ delta, float lr, int n4,
+                                       int skip_index) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n4) return;
+    float4 a = ((float4*)w)[i];
+    const float4 d = ((const float4*)delta)[i];
+    float v[4] = {fmaf(lr, d.x, a.x), fmaf(lr, d.y, a.y), fmaf(lr, d.z, a.z), fmaf(lr, d.w, a.w)};
+    if (skip_index >= 4 * i && skip_index < 4 * i + 4) v[skip_index - 4 * i] = (&a.x)[skip_index - 4 * i];
+    ((float4*)w)[i] = make_float4(v[0], v[1], v[2], v[3]);
+}
+
+int psb_launch_ring_scatter(const uint32_t* d_stage, int n, int stride_words, void* d_X, int* d_labels, int cap, int F,
+                            cudaStream_t stream) {
+    if (n <= 0) return 0;
+    psb_ring_scatter_kernel<<<n < 1184 ? n : 1184, 256, 0, stream>>>(d_stage, n, stride_words, (__half*)d_X, d_labels,
+                                                                      cap, F);
+    PSB_CHECK_CUDA(cudaGetLastError());
+    return 0;
+}
+int psb_launch_ring_store_dense(const void* d_rows, int src_half, const int* d_labels_in, const int* d_ws, int n,
+                                void* d_X, int* d_labels, int cap, int F, cudaStream_t stream) {
+    if (n <= 0) return 0;
+    const int grid = n < 2368 ? n : 2368;
+    if (src_half)
+        psb_ring_store_half_kernel<<<grid, 256, 0, stream>>>((const __half*)d_rows, d_labels_in, d_ws, n, (__half*)d_X,
+                                                              d_labels, cap, F);
+    else
+        psb_ring_store_dense_kernel<<<grid, 256, 0, stream>>>((const float*)d_rows, d_labels_in, d_ws, n,
+                                                               (__half*)d_X, d_labels, cap, F);
+    PSB_CHECK_CUDA(cudaGetLastError());
+    return 0;
+}
+int psb_launch_apply_delta(float* d_w, const float* d_delta, float lr, int F, int skip_class, cudaStream_t stream) {
+    const int n4 = (F + 1) * 2;
+    const int skip = skip_class >= 0 ? F * 8 + skip_class : -1;
+    psb_apply_delta_kernel<<<(n4 + 255) / 256, 256, 0, stream>>>(d_w, d_delta, lr, n4, skip);
+    PSB_CHECK_CUDA(cudaGetLastError());
+    return 0;
+}

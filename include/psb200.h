@@ -1,0 +1,154 @@
+/*
+ * psb200 — C ABI of the Blackwell-native parameter server (libpsb200.so).
+ *
+ * Every entry point returns 0 on success or a negative PSB_E_* code; the text of
+ * the last error on the calling thread is available from psb_last_error().
+ * Pointers named d_* are device pointers, h_* are host pointers.  Kernels are
+ * enqueued on the cudaStream_t passed as `void* stream` and never synchronise.
+ *
+ * Parameter layout (device): W[(F+1)][8] fp32 — feature-major, one 32-byte
+ * sector per feature, row F = intercepts, class columns >= R are padding.
+ * Reference key k <-> W[k / R][k % R] for k < R*F, intercept c <-> W[F][c]
+ * (LogisticRegressionTaskSpark.java:98-140, 173).
+ *
+ * Input buffer (device): per worker a ring of `cap` rows, X[w][cap][F] fp16
+ * dense + labels[w][cap] int32 + win[w] = {head, count}: the active rows are the
+ * `count` most recent insertions, slots (head-count .. head-1) mod cap
+ * (WorkerSamplingProcessor.java:50-113 => "last min(prev+1, target) rows").
+ */
+#ifndef PSB200_H
+#define PSB200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define PSB_CLASS_PAD 8
+#define PSB_MAX_RANKS 8
+#define PSB_HIST 4                 /* L-BFGS pairs kept on device (reference runs 2 iterations) */
+#define PSB_SCRATCH_VECS (6 + 2 * PSB_HIST)
+
+#define PSB_E_INVALID (-1)
+#define PSB_E_CUDA (-2)
+#define PSB_E_LIMIT (-3)
+#define PSB_E_TIMEOUT (-4)
+
+#define PSB_SOLVER_LBFGS 0
+#define PSB_SOLVER_SGD 1
+
+#define PSB_COMM_NONE 0            /* write delta to d_delta (host applies)                     */
+#define PSB_COMM_SEQUENTIAL 1      /* mailbox push + last-arriver apply + replica broadcast      */
+#define PSB_COMM_ASYNC 2           /* red.add lr*delta into owner shard + clock table (k or inf) */
+
+const char* psb_last_error(void);
+int psb_version(void);
+
+/* ---------------------------------------------------------------- model / solver */
+typedef struct PsbSolver {
+    int num_features;              /* F                                                    */
+    int num_class_rows;            /* R = numClasses + 1  (<= 8)                             */
+    int cap;                       /* ring capacity per worker (max_buffer_size)           */
+    int solver;                    /* PSB_SOLVER_*                                          */
+    int max_iter;                  /* L-BFGS iterations (reference: 2)                      */
+    int standardize;               /* Spark standardization=true semantics                  */
+    int center;                    /* centre coefficients / intercepts across classes       */
+    float sgd_lr;
+} PsbSolver;
+
+/* Peer-memory block of one rank.  The same layout lives on every GPU; `peers[q]` is
+ * rank q's block mapped into this process (cudaIpc) — peers[rank] is the local one.
+ * Replaces WEIGHTS_TOPIC / GRADIENTS_TOPIC and the MessageTracker state
+ * (BaseKafkaApp.java:27-33, MessageTracker.java:42-88). */
+typedef struct PsbComm {
+    int mode;                      /* PSB_COMM_*                                            */
+    int rank, num_ranks;
+    int workers_per_rank;          /* worker CTAs launched on every rank                    */
+    int clock;                     /* vector clock of this step                             */
+    int max_delay;                 /* bounded delay k (async mode; <0: eventual)            */
+    float lr;                      /* server learning rate 1/numWorkers (ServerProcessor.java:36) */
+    unsigned long long spin_limit; /* clock64 cycles before a wait gives up (watchdog)      */
+    void* peers[PSB_MAX_RANKS];
+} PsbComm;
+
+size_t psb_comm_block_bytes(int num_features, int num_ranks);
+/* zero the block and write the initial weights into both replicas and the owned shard */
+int psb_comm_init_block(void* d_block, const float* d_w0, int num_features, int num_ranks, int rank, void* stream);
+/* host-visible views into a block (device pointers) */
+float* psb_comm_replica(void* d_block, int num_features, int num_ranks, int parity);
+float* psb_comm_shard_weights(void* d_block, int num_features, int num_ranks);
+unsigned int* psb_comm_status(void* d_block, int num_features, int num_ranks);   /* [0]=error flag, [1..]=debug */
+
+size_t psb_worker_scratch_bytes(int num_features);                               /* per worker */
+
+/* One parameter-server iteration for `num_workers` local workers (one CTA each):
+ * pull (wait + load weights) -> local solve on the buffer -> push/apply per comm.mode.
+ * Replaces WorkerTrainingProcessor.process + ServerProcessor.process
+ * (WorkerTrainingProcessor.java:63-98, ServerProcessor.java:143-183).
+ *   d_w_in  : weights to start from when comm.mode == NONE (else the replica is used)
+ *   d_delta : [num_workers][(F+1)*8] out when comm.mode == NONE (may be NULL otherwise)
+ *   d_loss  : [num_workers] final train loss of the local solve
+ *   d_info  : [num_workers][4] ints: evals, iterations, status, active rows
+ *   impl    : 0 = SIMT fp32 kernel, 1 = tcgen05/TMA kernel                                */
+int psb_worker_step(const PsbSolver* s, const PsbComm* comm, int num_workers, int impl,
+                    const void* d_X, const int* d_labels, const int* d_win,
+                    const float* d_w_in, float* d_delta, float* d_loss, int* d_info,
+                    float* d_scratch, void* stream);
+
+/* Server-side apply for comm.mode == NONE: w += lr * delta (ServerProcessor.java:148-151, 225-228);
+ * skip_class >= 0 leaves that class' intercept untouched (quirk Q1 compatibility), -1 updates all. */
+int psb_apply_delta(float* d_w, const float* d_delta, float lr, int num_features, int skip_class,
+                    void* stream);
+
+/* ---------------------------------------------------------------- evaluation */
+/* argmax(X W + b) -> confusion matrix -> weighted F1, accuracy (Metrics.java:15-24).
+ *   d_X fp16 dense [n][F]; d_conf: int[64] scratch (8x8, zeroed by the call);
+ *   d_out: float[2] = {f1, accuracy}.  impl as above.                                     */
+int psb_eval(const void* d_X, const int* d_labels, int n, const float* d_w, int num_features,
+             int num_class_rows, int* d_conf, float* d_out, int impl, void* stream);
+
+/* ---------------------------------------------------------------- ingestion */
+/* Scatter a staged batch of sparse rows into the dense fp16 ring slots (K1).
+ *   d_stage: packed rows [n][stride_words] (word0 = nnz, word1 = label, word2 = worker,
+ *   word3 = slot, then nnz x (int32 index, fp32 value)); the slot row is zero-filled first. */
+int psb_ring_scatter(const uint32_t* d_stage, int n, int stride_words, void* d_X, int* d_labels,
+                     int cap, int num_features, void* stream);
+/* dense rows [n][F] (fp32 when src_half == 0, fp16 otherwise) -> ring slots given (worker, slot) pairs */
+int psb_ring_store_dense(const void* d_rows, int src_half, const int* d_labels_in, const int* d_worker_slot, int n,
+                         void* d_X, int* d_labels, int cap, int num_features, void* stream);
+
+/* ---------------------------------------------------------------- host runtime (C++) */
+/* CSV -> CSR tokenizer (CsvProducer.java:46-58).  Two-pass: count, then fill. */
+int psb_csv_count(const char* path, int has_header, long long* n_rows, long long* n_nnz, int* n_cols);
+int psb_csv_parse(const char* path, int has_header, long long* indptr, int* indices, float* values,
+                  int* labels, long long n_rows, long long n_nnz);
+
+/* Consistency tracker (MessageTracker.java) — returns replies as (worker, clock) pairs */
+void* psb_tracker_create(int num_workers, int consistency_model);
+void psb_tracker_destroy(void* t);
+int psb_tracker_on_gradient(void* t, int worker, int clock, int* replies, int max_replies);
+int psb_tracker_clocks(void* t, int* clocks);
+
+/* Dynamic buffer policy (WorkerSamplingProcessor.java:115-135) */
+void* psb_buffer_create(int min_size, int max_size, float bc, int window);
+void psb_buffer_destroy(void* b);
+int psb_buffer_on_event(void* b, double now_ms, int* head, int* count, int* target);
+/* n events at once: fills worker_slot[n][2] and updates win[num_buffers][2] for the touched workers */
+int psb_buffers_on_batch(void** buffers, int num_buffers, const int* workers, const double* now_ms, int n,
+                         int* worker_slot, int* win);
+
+/* Peer memory: raw cudaMalloc (IPC-exportable, unlike a caching-allocator block) and IPC export /
+ * import of a device allocation (transport set-up; replaces ServerApp.createTopics, ServerApp.java:31-42) */
+int psb_malloc(void** d_ptr_out, size_t bytes);
+int psb_free(void* d_ptr);
+int psb_ipc_export(void* d_ptr, unsigned char handle_out[64]);
+int psb_ipc_import(const unsigned char handle[64], void** d_ptr_out);
+int psb_ipc_close(void* d_ptr);
+int psb_enable_peer_access(int num_devices);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

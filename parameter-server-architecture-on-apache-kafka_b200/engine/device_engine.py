@@ -1,0 +1,265 @@
+"""Device engine: the fused parameter-server step on one GPU rank.
+
+One object per rank owns what the reference spreads over a worker JVM, a server
+JVM and three Kafka topics:
+
+* the workers' input rings (``INPUT_DATA_BUFFER`` state store, ``WorkerApp.java:40-42``)
+  as one dense fp16 tensor ``X[W, cap, F]`` + labels + (head, count) windows;
+* this rank's peer-memory block (weights replicas, shard, inboxes, clocks —
+  ``csrc/common.cuh: CommLayout``) which stands in for ``WEIGHTS_TOPIC`` /
+  ``GRADIENTS_TOPIC`` / ``MessageTracker``;
+* a pinned staging ring + side stream for ingestion (``CsvProducer`` -> ``INPUT_DATA``).
+
+``step()`` enqueues ONE kernel: pull (gated by the consistency model) -> local
+solve -> push -> apply (``psb_worker_step``).  Nothing is synchronised with the
+host unless the caller asks for the loss.
+
+Multi-GPU: one engine per process, blocks exchanged with ``cudaIpc`` through
+``torch.distributed`` (``connect()``).  Tests on fewer GPUs than ranks build several
+engines on one device (``VirtualCluster``) and step them in clock order, which
+never makes one launch wait on another.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import List, Optional
+
+import numpy as np
+import torch
+
+from ..config import PSConfig
+from ..data.csr import CSRBatch
+from ..models.logreg import LogRegLayout
+from ..ops import native
+
+
+class DeviceEngine:
+    def __init__(self, cfg: PSConfig, workers_per_rank: int, rank: int = 0, world: int = 1, impl: int = native.IMPL_SIMT,
+                 device: Optional[torch.device] = None, w0: Optional[np.ndarray] = None, stage_rows: int = 0,
+                 spin_limit_cycles: int = 20_000_000_000):
+        if not torch.cuda.is_available():
+            raise native.NativeError("DeviceEngine needs a CUDA device")
+        native.lib()
+        self.cfg, self.W, self.rank, self.world, self.impl = cfg, workers_per_rank, rank, world, impl
+        self.device = device or torch.device("cuda", torch.cuda.current_device())
+        self.layout = LogRegLayout(cfg.num_features, cfg.num_classes)
+        F, cap = cfg.num_features, cfg.max_buffer_size
+        self.F, self.cap, self.nv = F, cap, self.layout.device_size
+        dev = self.device
+        self.X = torch.zeros((self.W, cap, F), dtype=torch.float16, device=dev)
+        self.labels = torch.zeros((self.W, cap), dtype=torch.int32, device=dev)
+        self.win_host = torch.zeros((self.W, 2), dtype=torch.int32).pin_memory()
+        self.win = torch.zeros((self.W, 2), dtype=torch.int32, device=dev)
+        self.loss = torch.zeros(self.W, dtype=torch.float32, device=dev)
+        self.info = torch.zeros((self.W, 4), dtype=torch.int32, device=dev)
+        self.delta = torch.zeros((self.W, self.nv), dtype=torch.float32, device=dev)
+        self.scratch = torch.zeros((self.W, native.scratch_floats(F)), dtype=torch.float32, device=dev)
+        self.loss_host = torch.zeros(self.W, dtype=torch.float32).pin_memory()
+        self.solver = native.make_solver(F, self.layout.R, cap, cfg.local_solver, cfg.max_iter, cfg.standardize,
+                                         cfg.center, cfg.sgd_lr)
+        self.total_workers = self.W * world
+        self.lr = 1.0 / self.total_workers                      # ServerProcessor.java:36
+        self.clock = 0
+        self.spin_limit = spin_limit_cycles
+        w0 = self.layout.zeros() if w0 is None else np.asarray(w0, dtype=np.float32)
+        self.w0 = torch.from_numpy(w0.reshape(-1).copy()).to(dev)
+        # peer-memory block (raw cudaMalloc so it can be exported over IPC)
+        self.block_bytes = native.comm_block_bytes(F, world)
+        self.block = native.device_malloc(self.block_bytes)
+        self.peers: List[int] = [0] * world
+        self.peers[rank] = self.block
+        native.check(native.lib().psb_comm_init_block(self.block, self.w0.data_ptr(), F, world, rank,
+                                                      native._stream()), "psb_comm_init_block")
+        # ingestion: host-side window bookkeeping + pinned staging + side stream
+        self.buffers = [native.NativeBuffer(cfg.min_buffer_size, cap, cfg.buffer_size_coefficient)
+                        for _ in range(self.W)]
+        self.rows_ingested = 0
+        self.stage_rows = stage_rows or self.W * 128
+        self.stage_host = torch.zeros((self.stage_rows, F), dtype=torch.float16).pin_memory()
+        self.stage_lab_host = torch.zeros(self.stage_rows, dtype=torch.int32).pin_memory()
+        self.stage_ws_host = torch.zeros((self.stage_rows, 2), dtype=torch.int32).pin_memory()
+        self.stage_dev = torch.zeros((self.stage_rows, F), dtype=torch.float16, device=dev)
+        self.stage_lab_dev = torch.zeros(self.stage_rows, dtype=torch.int32, device=dev)
+        self.stage_ws_dev = torch.zeros((self.stage_rows, 2), dtype=torch.int32, device=dev)
+        self.ingest_stream = torch.cuda.Stream(device=dev)
+        self.ingest_done = torch.cuda.Event()
+        self.h2d_bytes = 0
+        self.kernel_launches = 0
+        # evaluation buffers
+        self.conf = torch.zeros(64, dtype=torch.int32, device=dev)
+        self.metrics_dev = torch.zeros(2, dtype=torch.float32, device=dev)
+        self.metrics_host = torch.zeros(2, dtype=torch.float32).pin_memory()
+        self.test_X = self.test_y = None
+        torch.cuda.synchronize(dev)
+
+    # ------------------------------------------------------------------ transport set-up
+    def connect(self) -> None:
+        """Exchange IPC handles of the peer blocks (one engine per process, torch.distributed up)."""
+        import torch.distributed as dist
+        if self.world == 1:
+            return
+        handle = native.ipc_export(self.block)
+        handles = [None] * self.world
+        dist.all_gather_object(handles, handle)
+        for q in range(self.world):
+            if q != self.rank:
+                self.peers[q] = native.ipc_import(handles[q])
+        self._imported = True
+        dist.barrier()
+
+    def set_peers(self, peers: List[int]) -> None:
+        self.peers = list(peers)
+
+    def _comm(self, mode: int) -> native.PsbComm:
+        c = native.PsbComm()
+        c.mode, c.rank, c.num_ranks, c.workers_per_rank = mode, self.rank, self.world, self.W
+        c.clock, c.lr, c.spin_limit = self.clock, self.lr, self.spin_limit
+        cm = self.cfg.consistency_model
+        c.max_delay = cm if cm > 0 else -1
+        for q in range(self.world):
+            c.peers[q] = self.peers[q]
+        return c
+
+    @property
+    def comm_mode(self) -> int:
+        return native.COMM_SEQUENTIAL if self.cfg.consistency_model == 0 else native.COMM_ASYNC
+
+    # ------------------------------------------------------------------ ingestion
+    def load_test(self, test: CSRBatch) -> None:
+        self.test_X = torch.from_numpy(test.to_dense(np.float16)).to(self.device)
+        self.test_y = torch.from_numpy(test.labels.astype(np.int32)).to(self.device)
+
+    def fill(self, rows: torch.Tensor, labels: torch.Tensor) -> None:
+        """Bulk-load every ring: rows fp16 [W, n, F] (device or host), labels int32 [W, n]; n <= cap."""
+        n = rows.shape[1]
+        self.X[:, :n].copy_(rows)
+        self.labels[:, :n].copy_(labels)
+        self.buffers = [native.NativeBuffer(self.cfg.min_buffer_size, self.cap, self.cfg.buffer_size_coefficient)
+                        for _ in range(self.W)]
+        for b in self.buffers:                      # replay n unthrottled arrivals so the host mirror agrees
+            for _ in range(n):
+                b.on_event(0.0)
+        self.win_host[:, 0] = n % self.cap
+        self.win_host[:, 1] = n
+        self.win.copy_(self.win_host)
+
+    def ingest(self, rows_f16: torch.Tensor, labels: torch.Tensor, workers: np.ndarray,
+               now_ms: Optional[np.ndarray] = None, wait: bool = True) -> None:
+        """Stream `n` new rows (pinned fp16 [n, F] + int32 labels) to their workers' rings.
+
+        Host: slot per row from the dynamic-buffer policy; device: one H2D of the rows, one of the
+        (worker, slot) table, one scatter kernel — all on the ingestion stream.
+        """
+        n = rows_f16.shape[0]
+        assert n <= self.stage_rows, "ingest batch larger than the staging ring"
+        if now_ms is None:
+            now_ms = np.zeros(n, dtype=np.float64)
+        native.buffers_on_batch(self.buffers, workers[:n], now_ms[:n], self.stage_ws_host.numpy(),
+                                self.win_host.numpy())
+        self._ingest_staged(rows_f16, labels, n, wait)
+
+    def ingest_slots(self, rows_f16: torch.Tensor, labels: torch.Tensor, worker_slot: torch.Tensor,
+                     win: torch.Tensor, wait: bool = True) -> None:
+        """Same as ingest() with the (worker, slot) table and the new windows precomputed (bench hot path)."""
+        n = rows_f16.shape[0]
+        self.stage_ws_host[:n].copy_(worker_slot)
+        self.win_host.copy_(win)
+        self._ingest_staged(rows_f16, labels, n, wait)
+
+    def _ingest_staged(self, rows_f16, labels, n, wait) -> None:
+        s = self.ingest_stream
+        s.wait_stream(torch.cuda.current_stream())          # the previous step must be done with the ring
+        with torch.cuda.stream(s):
+            self.stage_dev[:n].copy_(rows_f16[:n], non_blocking=True)
+            self.stage_lab_dev[:n].copy_(labels[:n], non_blocking=True)
+            self.stage_ws_dev[:n].copy_(self.stage_ws_host[:n], non_blocking=True)
+            self.win.copy_(self.win_host, non_blocking=True)
+            native.ring_store_dense(self.stage_dev, self.stage_lab_dev, self.stage_ws_dev, n, self.X, self.labels,
+                                    self.cap, self.F, stream=s)
+            self.ingest_done.record(s)
+        self.kernel_launches += 1
+        self.rows_ingested += n
+        self.h2d_bytes += n * self.F * 2 + n * 4 + n * 8 + self.W * 8
+        if wait:
+            torch.cuda.current_stream().wait_event(self.ingest_done)
+
+    # ------------------------------------------------------------------ the step
+    def step(self, mode: Optional[int] = None) -> None:
+        mode = self.comm_mode if mode is None else mode
+        comm = self._comm(mode)
+        native.worker_step(self.solver, comm, self.W, self.impl, self.X, self.labels, self.win,
+                           self.w0 if mode == native.COMM_NONE else None,
+                           self.delta if mode == native.COMM_NONE else None,
+                           self.loss, self.info, self.scratch)
+        self.kernel_launches += 1
+        self.clock += 1
+
+    def read_loss(self) -> torch.Tensor:
+        """Device -> pinned host copy of the per-worker losses of the last step (synchronises)."""
+        self.loss_host.copy_(self.loss, non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+        return self.loss_host
+
+    def weights(self) -> torch.Tensor:
+        """Current global weights as seen by this rank ([(F+1), 8] view of device memory)."""
+        L = native.lib()
+        if self.comm_mode == native.COMM_SEQUENTIAL:
+            ptr = L.psb_comm_replica(self.block, self.F, self.world, self.clock & 1)
+            return _view(ptr, self.nv, self.device).view(self.layout.device_rows, 8)
+        if self.world != 1:
+            raise NotImplementedError("gather of async shards across ranks: use weights_gathered()")
+        ptr = L.psb_comm_shard_weights(self.block, self.F, self.world)
+        return _view(ptr, self.nv, self.device).view(self.layout.device_rows, 8)
+
+    def status(self) -> int:
+        ptr = native.lib().psb_comm_status(self.block, self.F, self.world)
+        return int(_view(ptr, 1, self.device, torch.int32).item())
+
+    def evaluate(self, weights: Optional[torch.Tensor] = None, impl: Optional[int] = None):
+        """Weighted F1 / accuracy of the weights on the loaded test set (device finalise, 8-byte D2H)."""
+        w = self.weights() if weights is None else weights
+        native.evaluate(self.test_X, self.test_y, self.test_X.shape[0], w, self.F, self.layout.R, self.conf,
+                        self.metrics_dev, self.impl if impl is None else impl)
+        self.kernel_launches += 2
+        self.metrics_host.copy_(self.metrics_dev, non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+        return float(self.metrics_host[0]), float(self.metrics_host[1])
+
+    def close(self) -> None:
+        if self.block:
+            torch.cuda.synchronize(self.device)
+            for q, p in enumerate(self.peers):
+                if q != self.rank and p and p != self.block and self._imported:
+                    native.lib().psb_ipc_close(p)
+            native.device_free(self.block)
+            self.block = 0
+
+    _imported = False
+
+
+def _view(ptr: int, n: int, device, dtype=torch.float32) -> torch.Tensor:
+    """Zero-copy torch view of raw device memory (through __cuda_array_interface__)."""
+    class _Holder:
+        pass
+    h = _Holder()
+    typestr = "<f4" if dtype == torch.float32 else "<i4"
+    h.__cuda_array_interface__ = {"shape": (n,), "typestr": typestr, "data": (int(ptr), False), "version": 2}
+    return torch.as_tensor(h, device=device)
+
+
+class VirtualCluster:
+    """N ranks on ONE device, stepped in clock order (tests / single-GPU emulation of the protocol)."""
+
+    def __init__(self, cfg: PSConfig, num_ranks: int, workers_per_rank: int, impl: int = native.IMPL_SIMT, w0=None):
+        self.engines = [DeviceEngine(cfg, workers_per_rank, r, num_ranks, impl, w0=w0) for r in range(num_ranks)]
+        peers = [e.block for e in self.engines]
+        for e in self.engines:
+            e.set_peers(peers)
+
+    def step(self) -> None:
+        for e in self.engines:
+            e.step()
+
+    def close(self) -> None:
+        for e in self.engines:
+            e.close()

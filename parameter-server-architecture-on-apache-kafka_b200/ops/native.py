@@ -1,0 +1,259 @@
+"""ctypes binding of libpsb200.so (C ABI in ``include/psb200.h``).
+
+The library is built in-tree by ``build.sh`` / ``__graft_entry__.build()`` for
+sm_100a and loaded from this directory.  Host-only entry points (CSV tokenizer,
+tracker, buffer policy) work on a machine without a GPU; anything that touches a
+device raises ``NativeError`` with the library's own message when it fails —
+there is no silent fallback to PyTorch ops.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+from typing import Optional, Tuple
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libpsb200.so")
+
+CLASS_PAD = 8
+MAX_RANKS = 8
+HIST = 4
+SCRATCH_VECS = 6 + 2 * HIST
+SOLVER_LBFGS, SOLVER_SGD = 0, 1
+COMM_NONE, COMM_SEQUENTIAL, COMM_ASYNC = 0, 1, 2
+IMPL_SIMT, IMPL_TC = 0, 1
+
+
+class NativeError(RuntimeError):
+    pass
+
+
+class PsbSolver(C.Structure):
+    _fields_ = [("num_features", C.c_int), ("num_class_rows", C.c_int), ("cap", C.c_int), ("solver", C.c_int),
+                ("max_iter", C.c_int), ("standardize", C.c_int), ("center", C.c_int), ("sgd_lr", C.c_float)]
+
+
+class PsbComm(C.Structure):
+    _fields_ = [("mode", C.c_int), ("rank", C.c_int), ("num_ranks", C.c_int), ("workers_per_rank", C.c_int),
+                ("clock", C.c_int), ("max_delay", C.c_int), ("lr", C.c_float), ("spin_limit", C.c_ulonglong),
+                ("peers", C.c_void_p * MAX_RANKS)]
+
+
+_lib: Optional[C.CDLL] = None
+
+
+def available() -> bool:
+    return os.path.exists(LIB_PATH)
+
+
+def lib() -> C.CDLL:
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not available():
+        raise NativeError(f"{LIB_PATH} is missing: run ./build.sh (or __graft_entry__.build()) first")
+    L = C.CDLL(LIB_PATH)
+    vp, ip, fp = C.c_void_p, C.c_void_p, C.c_void_p
+    L.psb_last_error.restype = C.c_char_p
+    L.psb_version.restype = C.c_int
+    L.psb_comm_block_bytes.restype = C.c_size_t
+    L.psb_comm_block_bytes.argtypes = [C.c_int, C.c_int]
+    L.psb_comm_init_block.argtypes = [vp, fp, C.c_int, C.c_int, C.c_int, vp]
+    for name in ("psb_comm_replica",):
+        getattr(L, name).restype = C.c_void_p
+        getattr(L, name).argtypes = [vp, C.c_int, C.c_int, C.c_int]
+    for name in ("psb_comm_shard_weights", "psb_comm_status"):
+        getattr(L, name).restype = C.c_void_p
+        getattr(L, name).argtypes = [vp, C.c_int, C.c_int]
+    L.psb_worker_scratch_bytes.restype = C.c_size_t
+    L.psb_worker_scratch_bytes.argtypes = [C.c_int]
+    L.psb_worker_step.argtypes = [C.POINTER(PsbSolver), C.POINTER(PsbComm), C.c_int, C.c_int, vp, ip, ip, fp, fp, fp,
+                                  ip, fp, vp]
+    L.psb_apply_delta.argtypes = [fp, fp, C.c_float, C.c_int, C.c_int, vp]
+    L.psb_eval.argtypes = [vp, ip, C.c_int, fp, C.c_int, C.c_int, ip, fp, C.c_int, vp]
+    L.psb_ring_scatter.argtypes = [vp, C.c_int, C.c_int, vp, ip, C.c_int, C.c_int, vp]
+    L.psb_ring_store_dense.argtypes = [vp, C.c_int, ip, ip, C.c_int, vp, ip, C.c_int, C.c_int, vp]
+    L.psb_malloc.argtypes = [C.POINTER(C.c_void_p), C.c_size_t]
+    L.psb_free.argtypes = [vp]
+    L.psb_csv_count.argtypes = [C.c_char_p, C.c_int, C.POINTER(C.c_longlong), C.POINTER(C.c_longlong),
+                                C.POINTER(C.c_int)]
+    L.psb_csv_parse.argtypes = [C.c_char_p, C.c_int, vp, vp, vp, vp, C.c_longlong, C.c_longlong]
+    L.psb_tracker_create.restype = C.c_void_p
+    L.psb_tracker_create.argtypes = [C.c_int, C.c_int]
+    L.psb_tracker_destroy.argtypes = [vp]
+    L.psb_tracker_on_gradient.argtypes = [vp, C.c_int, C.c_int, vp, C.c_int]
+    L.psb_tracker_clocks.argtypes = [vp, vp]
+    L.psb_buffer_create.restype = C.c_void_p
+    L.psb_buffer_create.argtypes = [C.c_int, C.c_int, C.c_float, C.c_int]
+    L.psb_buffer_destroy.argtypes = [vp]
+    L.psb_buffer_on_event.argtypes = [vp, C.c_double, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int)]
+    L.psb_buffers_on_batch.argtypes = [vp, C.c_int, vp, vp, C.c_int, vp, vp]
+    L.psb_ipc_export.argtypes = [vp, vp]
+    L.psb_ipc_import.argtypes = [vp, C.POINTER(C.c_void_p)]
+    L.psb_ipc_close.argtypes = [vp]
+    L.psb_enable_peer_access.argtypes = [C.c_int]
+    _lib = L
+    return L
+
+
+def check(rc: int, what: str = "") -> int:
+    if rc < 0:
+        raise NativeError(f"{what}: {lib().psb_last_error().decode()} (code {rc})")
+    return rc
+
+
+def _ptr(t) -> int:
+    """Device/host pointer of a torch tensor or numpy array (None -> NULL)."""
+    if t is None:
+        return None
+    if isinstance(t, np.ndarray):
+        return t.ctypes.data
+    return t.data_ptr()
+
+
+def _stream(stream=None) -> int:
+    import torch
+    s = stream if stream is not None else torch.cuda.current_stream()
+    return s.cuda_stream
+
+
+# ------------------------------------------------------------------ host runtime wrappers
+def csv_to_csr(path: str, has_header: bool = True):
+    from ..data.csr import CSRBatch
+    L = lib()
+    n_rows, n_nnz, n_cols = C.c_longlong(), C.c_longlong(), C.c_int()
+    check(L.psb_csv_count(path.encode(), int(has_header), C.byref(n_rows), C.byref(n_nnz), C.byref(n_cols)), "csv_count")
+    indptr = np.zeros(n_rows.value + 1, dtype=np.int64)
+    indices = np.zeros(max(1, n_nnz.value), dtype=np.int32)
+    values = np.zeros(max(1, n_nnz.value), dtype=np.float32)
+    labels = np.zeros(max(1, n_rows.value), dtype=np.int32)
+    check(L.psb_csv_parse(path.encode(), int(has_header), indptr.ctypes.data, indices.ctypes.data, values.ctypes.data,
+                          labels.ctypes.data, n_rows.value, n_nnz.value), "csv_parse")
+    return CSRBatch(indptr, indices[: n_nnz.value], values[: n_nnz.value], labels[: n_rows.value], n_cols.value)
+
+
+class NativeTracker:
+    def __init__(self, num_workers: int, consistency_model: int):
+        self.n = num_workers
+        self.h = lib().psb_tracker_create(num_workers, consistency_model)
+        if not self.h:
+            raise NativeError("psb_tracker_create failed")
+        self._buf = np.zeros(2 * num_workers, dtype=np.int32)
+
+    def on_gradient(self, worker: int, clock: int):
+        n = check(lib().psb_tracker_on_gradient(self.h, worker, clock, self._buf.ctypes.data, self.n), "tracker")
+        return [(int(self._buf[2 * i]), int(self._buf[2 * i + 1])) for i in range(n)]
+
+    def clocks(self):
+        out = np.zeros(self.n, dtype=np.int32)
+        lib().psb_tracker_clocks(self.h, out.ctypes.data)
+        return out.tolist()
+
+    def __del__(self):
+        if getattr(self, "h", None) and _lib is not None:
+            _lib.psb_tracker_destroy(self.h)
+            self.h = None
+
+
+class NativeBuffer:
+    def __init__(self, min_size: int, max_size: int, bc: float, window: int = 500):
+        self.h = lib().psb_buffer_create(min_size, max_size, bc, window)
+        if not self.h:
+            raise NativeError("psb_buffer_create failed")
+        self.head = self.count = self.target = 0
+
+    def on_event(self, now_ms: float) -> int:
+        h, c, t = C.c_int(), C.c_int(), C.c_int()
+        slot = lib().psb_buffer_on_event(self.h, float(now_ms), C.byref(h), C.byref(c), C.byref(t))
+        self.head, self.count, self.target = h.value, c.value, t.value
+        return slot
+
+    def __del__(self):
+        if getattr(self, "h", None) and _lib is not None:
+            _lib.psb_buffer_destroy(self.h)
+            self.h = None
+
+
+def buffers_on_batch(buffers, workers: np.ndarray, now_ms: np.ndarray, worker_slot: np.ndarray, win: np.ndarray):
+    """buffers: list of NativeBuffer; fills worker_slot[n,2] / win[W,2] (int32 numpy views, may be pinned)."""
+    n = len(workers)
+    arr = (C.c_void_p * len(buffers))(*[b.h for b in buffers])
+    workers = np.ascontiguousarray(workers, dtype=np.int32)
+    now_ms = np.ascontiguousarray(now_ms, dtype=np.float64)
+    check(lib().psb_buffers_on_batch(arr, len(buffers), workers.ctypes.data, now_ms.ctypes.data, n,
+                                     worker_slot.ctypes.data, win.ctypes.data), "psb_buffers_on_batch")
+
+
+# ------------------------------------------------------------------ device wrappers
+def make_solver(num_features, num_class_rows, cap, solver="lbfgs2", max_iter=2, standardize=True, center=True,
+                sgd_lr=0.5) -> PsbSolver:
+    return PsbSolver(num_features, num_class_rows, cap, SOLVER_LBFGS if solver == "lbfgs2" else SOLVER_SGD, max_iter,
+                     int(standardize), int(center), sgd_lr)
+
+
+def comm_none() -> PsbComm:
+    c = PsbComm()
+    c.mode = COMM_NONE
+    c.num_ranks = 1
+    return c
+
+
+def worker_step(solver: PsbSolver, comm: PsbComm, num_workers: int, impl: int, X, labels, win, w_in, delta, loss,
+                info, scratch, stream=None) -> None:
+    check(lib().psb_worker_step(C.byref(solver), C.byref(comm), num_workers, impl, _ptr(X), _ptr(labels), _ptr(win),
+                                _ptr(w_in), _ptr(delta), _ptr(loss), _ptr(info), _ptr(scratch), _stream(stream)),
+          "psb_worker_step")
+
+
+def apply_delta(w, delta, lr: float, num_features: int, skip_class: int = -1, stream=None) -> None:
+    check(lib().psb_apply_delta(_ptr(w), _ptr(delta), lr, num_features, skip_class, _stream(stream)), "psb_apply_delta")
+
+
+def evaluate(X, labels, n: int, w, num_features: int, num_class_rows: int, conf, out, impl: int = 0, stream=None):
+    check(lib().psb_eval(_ptr(X), _ptr(labels), n, _ptr(w), num_features, num_class_rows, _ptr(conf), _ptr(out), impl,
+                         _stream(stream)), "psb_eval")
+
+
+def ring_scatter(stage, n: int, stride_words: int, X, labels, cap: int, num_features: int, stream=None) -> None:
+    check(lib().psb_ring_scatter(_ptr(stage), n, stride_words, _ptr(X), _ptr(labels), cap, num_features,
+                                 _stream(stream)), "psb_ring_scatter")
+
+
+def ring_store_dense(rows, labels_in, worker_slot, n: int, X, labels, cap: int, num_features: int, stream=None):
+    import torch
+    src_half = int(rows.dtype == torch.float16)
+    check(lib().psb_ring_store_dense(_ptr(rows), src_half, _ptr(labels_in), _ptr(worker_slot), n, _ptr(X),
+                                     _ptr(labels), cap, num_features, _stream(stream)), "psb_ring_store_dense")
+
+
+def device_malloc(nbytes: int) -> int:
+    p = C.c_void_p()
+    check(lib().psb_malloc(C.byref(p), nbytes), "psb_malloc")
+    return p.value
+
+
+def device_free(ptr: int) -> None:
+    check(lib().psb_free(ptr), "psb_free")
+
+
+def ipc_export(ptr: int) -> bytes:
+    buf = (C.c_ubyte * 64)()
+    check(lib().psb_ipc_export(ptr, buf), "psb_ipc_export")
+    return bytes(buf)
+
+
+def ipc_import(handle: bytes) -> int:
+    buf = (C.c_ubyte * 64).from_buffer_copy(handle)
+    p = C.c_void_p()
+    check(lib().psb_ipc_import(buf, C.byref(p)), "psb_ipc_import")
+    return p.value
+
+
+def scratch_floats(num_features: int) -> int:
+    return lib().psb_worker_scratch_bytes(num_features) // 4
+
+
+def comm_block_bytes(num_features: int, num_ranks: int) -> int:
+    return lib().psb_comm_block_bytes(num_features, num_ranks)

@@ -1,0 +1,97 @@
+"""Fused pull/push/apply protocol on virtual ranks, and the CUDA backend of the event-driven engine."""
+import numpy as np
+import pytest
+
+torch = pytest.importorskip("torch")
+
+from psb200.config import PSConfig
+from psb200.data import CSRBatch, ReviewGenerator
+from psb200.engine.sim import NumpyBackend, PSSimulation
+from psb200.models import LogRegLayout
+from psb200.oracle import LogisticRegressionTask
+from psb200.utils.logs import parse_log
+
+pytestmark = pytest.mark.gpu
+
+
+def _half_batch(batch):
+    return CSRBatch.from_dense(batch.to_dense(np.float16).astype(np.float32), batch.labels)
+
+
+def _oracle_rounds(cfg, per_worker, clocks):
+    """Lock-step reference: every clock all workers solve from the same weights, w += (1/N) sum(delta)."""
+    lay = LogRegLayout(cfg.num_features, cfg.num_classes)
+    W = lay.zeros()
+    n = len(per_worker)
+    losses = []
+    for _ in range(clocks):
+        total = np.zeros_like(W, dtype=np.float64)
+        ls = []
+        for b in per_worker:
+            t = LogisticRegressionTask(cfg.num_features, cfg.num_classes, None, cfg.local_solver, cfg.max_iter,
+                                       cfg.sgd_lr, cfg.standardize, cfg.center)
+            t.set_weights(W)
+            total += t.calculate_gradients(b, eval_test=False)
+            ls.append(t.loss)
+        W = (W + total / n).astype(np.float32)
+        losses.append(ls)
+    return W, np.asarray(losses)
+
+
+@pytest.mark.parametrize("impl", [0, 1])
+@pytest.mark.parametrize("model,ranks,wpr", [(0, 1, 2), (0, 4, 2), (0, 3, 1), (-1, 2, 2), (3, 4, 1)])
+def test_virtual_cluster_matches_lockstep_oracle(impl, model, ranks, wpr):
+    from psb200.engine.device_engine import VirtualCluster
+    F, cap, n = 256, 128, 96
+    cfg = PSConfig(num_workers=ranks * wpr, num_features=F, consistency_model=model, max_buffer_size=cap,
+                   min_buffer_size=16, local_solver="sgd", sgd_lr=0.8)
+    gen = ReviewGenerator(F, 5, vocab=3000, mean_len=120.0)
+    full = _half_batch(gen.train_split(n * ranks * wpr))
+    per_worker = [full.slice(np.arange(i * n, (i + 1) * n)) for i in range(ranks * wpr)]
+    vc = VirtualCluster(cfg, ranks, wpr, impl)
+    try:
+        for r, e in enumerate(vc.engines):
+            rows = torch.stack([torch.from_numpy(per_worker[r * wpr + j].to_dense(np.float16)) for j in range(wpr)])
+            labs = torch.stack([torch.from_numpy(per_worker[r * wpr + j].labels) for j in range(wpr)])
+            e.fill(rows.cuda(), labs.cuda())
+        clocks = 4
+        losses = []
+        for _ in range(clocks):
+            vc.step()
+            losses.append(np.concatenate([e.read_loss().numpy().copy() for e in vc.engines]))
+        torch.cuda.synchronize()
+        assert all(e.status() == 0 for e in vc.engines)
+        Wref, lref = _oracle_rounds(cfg, per_worker, clocks)
+        assert np.allclose(np.asarray(losses), lref, rtol=3e-3, atol=3e-3)
+        if model == 0:
+            for e in vc.engines:                               # every replica holds the same snapshot
+                Wd = e.weights().cpu().numpy()
+                assert np.abs(Wd - Wref).max() < 3e-3 * max(1e-2, np.abs(Wref).max())
+        else:
+            shards = []
+            for e in vc.engines:
+                from psb200.ops import native
+                ptr = native.lib().psb_comm_shard_weights(e.block, F, ranks)
+                from psb200.engine.device_engine import _view
+                L4 = (e.nv // 4 + ranks - 1) // ranks * 4
+                b = min(e.rank * L4, e.nv)
+                shards.append(_view(ptr, L4, e.device).cpu().numpy()[: max(0, min(L4, e.nv - b))])
+            Wd = np.concatenate(shards)[: vc.engines[0].nv].reshape(F + 1, 8)
+            assert np.abs(Wd - Wref).max() < 3e-3 * max(1e-2, np.abs(Wref).max())
+    finally:
+        vc.close()
+
+
+def test_cuda_backend_tracks_numpy_backend():
+    from psb200.engine.cuda_backend import CudaBackend
+    gen = ReviewGenerator(mean_len=300.0)
+    tr, te = _half_batch(gen.train_split(1200)), _half_batch(gen.test_split(800))
+    cfg = PSConfig(num_workers=2, producer_time_per_event=0, max_clock=6, max_buffer_size=256)
+    logs = []
+    for mk in (lambda: NumpyBackend(cfg, te), lambda: CudaBackend(cfg, te)):
+        sim = PSSimulation(cfg, tr, te, backend=mk(), server_start_ms=0.0)
+        sim.run()
+        logs.append(parse_log(sim.server_log.rows, "server"))
+    assert logs[0].shape == logs[1].shape == (6, 6)
+    assert np.abs(logs[0][:, 4] - logs[1][:, 4]).max() < 0.01          # F1 within a point at every clock
+    assert np.abs(logs[0][:, 5] - logs[1][:, 5]).max() < 0.01
