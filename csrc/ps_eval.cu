@@ -78,7 +78,7 @@ int psb_launch_eval_simt(const void* d_X, const int* d_labels, int n, const floa
         psb_set_error("evaluation kernel: num_features %d does not fit shared memory", F);
         return PSB_E_LIMIT;
     }
-    PSB_CHECK_CUDA(cudaFuncSetAttribute(psb_eval_simt_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+    PSB_CHECK_CUDA(cudaFuncSetAttribute(psb_eval_simt_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     int blocks = (n + 7) / 8;
     if (blocks > 148 * 2) blocks = 148 * 2;
     if (blocks < 1) blocks = 1;

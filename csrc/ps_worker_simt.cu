@@ -186,17 +186,12 @@ int psb_launch_worker_simt(const PsbSolver* s, const CommCtx& cx, int num_worker
     const int nv = (s->num_features + 1) * 8;
     const size_t smem = (size_t)nv * 4 + (size_t)s->cap * 32 + (size_t)s->num_features * 4 + 64 + 34 * 8;
     PSB_REQUIRE(s->num_features % 2 == 0, "num_features must be even (got %d)", s->num_features);
-    if (smem > 227 * 1024) {
+    if (smem > 226 * 1024) {
         psb_set_error("SIMT worker kernel needs %zu bytes of shared memory (> 227 KB): lower max_buffer_size (%d) "
                       "or num_features (%d)", smem, s->cap, s->num_features);
         return PSB_E_LIMIT;
     }
-    static bool attr_set = false;
-    if (!attr_set) {
-        PSB_CHECK_CUDA(cudaFuncSetAttribute(psb_worker_simt_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                            227 * 1024));
-        attr_set = true;
-    }
+    PSB_CHECK_CUDA(cudaFuncSetAttribute(psb_worker_simt_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     psb_worker_simt_kernel<<<num_workers, 512, smem, stream>>>(*s, cx, (const __half*)d_X, d_labels, d_win, d_w_in,
                                                                 d_delta, d_loss, d_info, d_scratch);
     PSB_CHECK_CUDA(cudaGetLastError());

@@ -10,11 +10,11 @@ struct WorkerScratch {
     float* w0;
     __device__ WorkerScratch(float* base, int nv) {
         for (int i = 0; i < PSB_SCRATCH_VECS; ++i) vec[i] = base + (size_t)i * nv;
-        w0 = vec[PSB_SCRATCH_VECS - 1];
+        w0 = vec[6];
     }
     __device__ void bind(SolveVecs& v) const {
         v.x = vec[0], v.g = vec[1], v.d = vec[2], v.xt = vec[3], v.gt = vec[4], v.tmp = vec[5];
-        for (int i = 0; i < PSB_HIST; ++i) v.s[i] = vec[6 + i], v.y[i] = vec[6 + PSB_HIST + i];
+        for (int i = 0; i < PSB_HIST; ++i) v.s[i] = vec[7 + i], v.y[i] = vec[7 + PSB_HIST + i];
     }
 };
 

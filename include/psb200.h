@@ -29,7 +29,7 @@ extern "C" {
 #define PSB_CLASS_PAD 8
 #define PSB_MAX_RANKS 8
 #define PSB_HIST 4                 /* L-BFGS pairs kept on device (reference runs 2 iterations) */
-#define PSB_SCRATCH_VECS (6 + 2 * PSB_HIST)
+#define PSB_SCRATCH_VECS (7 + 2 * PSB_HIST)   /* x g d xt gt tmp w0 + s[], y[] */
 
 #define PSB_E_INVALID (-1)
 #define PSB_E_CUDA (-2)

@@ -20,7 +20,7 @@ LIB_PATH = os.path.join(_HERE, "libpsb200.so")
 CLASS_PAD = 8
 MAX_RANKS = 8
 HIST = 4
-SCRATCH_VECS = 6 + 2 * HIST
+SCRATCH_VECS = 7 + 2 * HIST
 SOLVER_LBFGS, SOLVER_SGD = 0, 1
 COMM_NONE, COMM_SEQUENTIAL, COMM_ASYNC = 0, 1, 2
 IMPL_SIMT, IMPL_TC = 0, 1

@@ -18,22 +18,26 @@ def _half_batch(batch):
     return CSRBatch.from_dense(batch.to_dense(np.float16).astype(np.float32), batch.labels)
 
 
-def _oracle_rounds(cfg, per_worker, clocks):
-    """Lock-step reference: every clock all workers solve from the same weights, w += (1/N) sum(delta)."""
+def _oracle_rounds(cfg, per_worker, clocks, group):
+    """Reference for ranks stepped one after the other: the `group` workers of a rank solve from the same
+    weights and their summed delta is applied (w += sum/N) before the next group starts.  Sequential
+    consistency is group == all workers (one snapshot per clock); the async modes on a virtual cluster
+    are group == workers_per_rank (a later rank already sees the earlier ranks' pushes of that clock)."""
     lay = LogRegLayout(cfg.num_features, cfg.num_classes)
     W = lay.zeros()
     n = len(per_worker)
     losses = []
     for _ in range(clocks):
-        total = np.zeros_like(W, dtype=np.float64)
         ls = []
-        for b in per_worker:
-            t = LogisticRegressionTask(cfg.num_features, cfg.num_classes, None, cfg.local_solver, cfg.max_iter,
-                                       cfg.sgd_lr, cfg.standardize, cfg.center)
-            t.set_weights(W)
-            total += t.calculate_gradients(b, eval_test=False)
-            ls.append(t.loss)
-        W = (W + total / n).astype(np.float32)
+        for g0 in range(0, n, group):
+            total = np.zeros_like(W, dtype=np.float64)
+            for b in per_worker[g0:g0 + group]:
+                t = LogisticRegressionTask(cfg.num_features, cfg.num_classes, None, cfg.local_solver, cfg.max_iter,
+                                           cfg.sgd_lr, cfg.standardize, cfg.center)
+                t.set_weights(W)
+                total += t.calculate_gradients(b, eval_test=False)
+                ls.append(t.loss)
+            W = (W + total / n).astype(np.float32)
         losses.append(ls)
     return W, np.asarray(losses)
 
@@ -61,7 +65,7 @@ def test_virtual_cluster_matches_lockstep_oracle(impl, model, ranks, wpr):
             losses.append(np.concatenate([e.read_loss().numpy().copy() for e in vc.engines]))
         torch.cuda.synchronize()
         assert all(e.status() == 0 for e in vc.engines)
-        Wref, lref = _oracle_rounds(cfg, per_worker, clocks)
+        Wref, lref = _oracle_rounds(cfg, per_worker, clocks, ranks * wpr if model == 0 else wpr)
         assert np.allclose(np.asarray(losses), lref, rtol=3e-3, atol=3e-3)
         if model == 0:
             for e in vc.engines:                               # every replica holds the same snapshot
