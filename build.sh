@@ -17,5 +17,5 @@ for src in csrc/*.cu csrc/*.cpp; do
 done
 wait
 for obj in $OBJS; do [ -f "$obj" ] || { echo "build failed: $obj missing"; exit 1; }; done
-$NVCC -shared -gencode arch=compute_100a,code=sm_100a -o "$OUT" $OBJS -lcudart -lcuda
+$NVCC -shared -gencode arch=compute_100a,code=sm_100a -o "$OUT" $OBJS -lcudart
 echo "built $OUT"
