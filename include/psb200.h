@@ -97,6 +97,21 @@ int psb_worker_step(const PsbSolver* s, const PsbComm* comm, int num_workers, in
                     const float* d_w_in, float* d_delta, float* d_loss, int* d_info,
                     float* d_scratch, void* stream);
 
+/* The same step for callers that must not allocate device memory (a host process whose GPU memory
+ * belongs to another framework's pool, a real-time loop that cannot afford cudaMalloc's device-wide
+ * synchronisation, a plugin ABI that forbids allocation after start-up): the solver scratch is a fixed
+ * array inside the library's device image instead of a caller buffer.  It has no counterpart in the
+ * reference (the JVM allocates freely); it exists for embedders of this library.
+ * Limit: psb_static_scratch_bytes() (about 1.9 MiB per GPU, held until exit) = 4 workers at 1024
+ * features; larger requests return PSB_E_LIMIT and launch nothing.  All calls on a device share the
+ * array (it keeps the previous call's contents; nothing in it needs zeroing), so calls that can overlap
+ * on the GPU race — keep them on one stream.  The first call on each device resolves the array's
+ * address and should be made outside stream capture.  See csrc/ps_noalloc.cu. */
+size_t psb_static_scratch_bytes(void);
+int psb_worker_step_static(const PsbSolver* s, const PsbComm* comm, int num_workers, int impl,
+                           const void* d_X, const int* d_labels, const int* d_win,
+                           const float* d_w_in, float* d_delta, float* d_loss, int* d_info, void* stream);
+
 /* Server-side apply for comm.mode == NONE: w += lr * delta (ServerProcessor.java:148-151, 225-228);
  * skip_class >= 0 leaves that class' intercept untouched (quirk Q1 compatibility), -1 updates all. */
 int psb_apply_delta(float* d_w, const float* d_delta, float lr, int num_features, int skip_class,
