@@ -34,7 +34,7 @@ def parse():
     p.add_argument("--warmup", type=int, default=3)
     p.add_argument("--impl", default="ours", choices=["ours", "reference"])
     p.add_argument("--kernel", default="auto", choices=["auto", "simt", "tc"])
-    p.add_argument("--workers_per_gpu", type=int, default=148)
+    p.add_argument("--workers_per_gpu", type=int, default=296, help="2 worker CTAs per SM")
     p.add_argument("--buffer", type=int, default=1024, help="rows per worker buffer (reference -max default)")
     p.add_argument("--features", type=int, default=1024)
     p.add_argument("--density", type=float, default=0.45, help="non-zero fraction of the hashed BoW rows")
@@ -242,6 +242,7 @@ def main():
                        "local_solver": a.solver, "consistency_model": a.consistency_model,
                        "l2": f"inputs larger than L2 ({W * cap * F * 2 / 2**20:.0f} MiB of rows per GPU streamed per pass)",
                        "evals_per_step": float(info[:, 0].mean()), "status": status,
+                       "cycles64_stats_solve_push_total": [float(info[:, k].mean()) for k in (4, 5, 6, 7)],
                        "mean_loss": float(np.nanmean(loss))},
         }
         print(json.dumps(out))

@@ -129,6 +129,7 @@ psb_worker_simt_kernel(PsbSolver sv, CommCtx cx, const __half* __restrict__ X, c
     const int* lw = labels + (size_t)w * cap;
 
     // ---- pull
+    const long long t_begin = clock64();
     float* w0 = ws.w0;
     if (cx.c.mode == PSB_COMM_NONE) {
         for (int i = threadIdx.x; i < n4; i += blockDim.x) ((float4*)w0)[i] = ((const float4*)w_in)[i];
@@ -139,7 +140,7 @@ psb_worker_simt_kernel(PsbSolver sv, CommCtx cx, const __half* __restrict__ X, c
     if (count <= 0) {                       // "There is no data for partition" (WorkerTrainingProcessor.java:131)
         if (threadIdx.x == 0) {
             loss_out[w] = nanf("");
-            info_out[4 * w + 2] = -1, info_out[4 * w + 3] = 0;
+            info_out[8 * w + 2] = -1, info_out[8 * w + 3] = 0;
         }
         if (cx.c.mode != PSB_COMM_NONE) {   // still take part in the protocol with a zero delta
             for (int i = threadIdx.x; i < n4; i += blockDim.x) ((float4*)ws.vec[5])[i] = make_float4(0, 0, 0, 0);
@@ -152,6 +153,7 @@ psb_worker_simt_kernel(PsbSolver sv, CommCtx cx, const __half* __restrict__ X, c
     // ---- standardisation statistics (unbiased sample std over the window)
     feature_inv_std(Xw, start, count, cap, F, sv.standardize, inv);
     __syncthreads();
+    const long long t_stats = clock64();
 
     // ---- start point in scaled space: x = w0 * std
     SolveVecs v;
@@ -162,6 +164,7 @@ psb_worker_simt_kernel(PsbSolver sv, CommCtx cx, const __half* __restrict__ X, c
 
     SimtEval ev = {Xw, lw, start, count, cap, F, R, Ws, Rs, inv, sred, red};
     SolveResult res = local_solve(ev, v, sv.solver, sv.max_iter, sv.sgd_lr, red);
+    const long long t_solve = clock64();
 
     // ---- back to model space, centre, delta = float(new) - old
     float* delta = v.tmp;
@@ -169,8 +172,9 @@ psb_worker_simt_kernel(PsbSolver sv, CommCtx cx, const __half* __restrict__ X, c
     __syncthreads();
     if (threadIdx.x == 0) {
         loss_out[w] = (float)res.loss;
-        info_out[4 * w + 0] = res.evals, info_out[4 * w + 1] = res.iterations;
-        info_out[4 * w + 2] = res.status, info_out[4 * w + 3] = count;
+        info_out[8 * w + 0] = res.evals, info_out[8 * w + 1] = res.iterations;
+        info_out[8 * w + 2] = res.status, info_out[8 * w + 3] = count;
+        info_out[8 * w + 4] = (int)((t_stats - t_begin) >> 6), info_out[8 * w + 5] = (int)((t_solve - t_stats) >> 6);
     }
     if (cx.c.mode == PSB_COMM_NONE) {
         float4* out = (float4*)(delta_out + (size_t)w * nv);
@@ -178,6 +182,7 @@ psb_worker_simt_kernel(PsbSolver sv, CommCtx cx, const __half* __restrict__ X, c
     } else {
         comm_push(cx, (const float4*)delta);
     }
+    if (threadIdx.x == 0) info_out[8 * w + 6] = (int)((clock64() - t_solve) >> 6), info_out[8 * w + 7] = (int)((clock64() - t_begin) >> 6);
 }
 
 int psb_launch_worker_simt(const PsbSolver* s, const CommCtx& cx, int num_workers, const void* d_X,

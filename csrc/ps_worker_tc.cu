@@ -1,16 +1,21 @@
 // K2, tensor flavour: the worker's local solve with every pass over the input buffer running on
 // tcgen05 tensor cores fed by TMA, accumulators in TMEM.  One CTA per worker, one CTA per SM.
 //
-// One loss/gradient evaluation streams the buffer ONCE, 64 rows (one "slab") at a time:
-//   TMA     : slab = F/64 chunks of [64 rows x 64 features] fp16 (8 KB, SWIZZLE_128B) into a shared ring
-//   GEMM1   : Z[64 x 16]   = slab (K-major A, M=64) x Wsp[F x 16]   (fp16 hi | lo halves of the weights)
+// One loss/gradient evaluation is one continuous TMA stream through a shared-memory ring of
+// [128 rows x 64 features] fp16 chunks (16 KB, SWIZZLE_128B); a "slab" is 128 rows = F/64 chunks:
+//   A(s)    : slab s, consumed K-major by GEMM1   Z_s[128 x 16] = slab x Wsp[F x 16]
+//             (Wsp = fp16 hi | lo halves of the 8 weight columns, resident in shared memory)
 //   epilogue: TMEM -> registers, + intercept, softmax over the R class rows, loss, residual r = p - y,
-//             r -> fp16 hi | lo -> shared memory as a 16 x 64 MN-major B operand
-//   GEMM2   : G[F x 16]   += slab^T (the SAME shared tiles read MN-major, M=128 features) x Rsp[64 x 16]
-// so the gradient X^T R needs neither atomics nor a second read of X.  After the last slab the G
-// accumulators (F/128 tiles x 16 TMEM columns) are drained, scaled by 1/(n std_f) and written to the
-// solver's gradient vector.  A first pass with the same TMA ring computes the per-feature standard
-// deviation (Spark standardisation) straight from shared memory.
+//             r -> fp16 hi | lo -> shared memory as a 16 x 128 MN-major B operand (double buffered)
+//   B(s)    : slab s AGAIN (an L2 hit: A(s) is fetched with an evict-last policy, B(s) right behind it with
+//             evict-first), the same bytes consumed MN-major by GEMM2
+//             G[F x 16] += slab^T x Rsp_s   (M = 128 features per tile, K = 128 rows)
+// The stream order is A(0) B(0) A(1) B(1) ...: while the epilogue of slab s runs, the ring keeps filling
+// with B(s) and A(s+1); every chunk is released as soon as its MMAs retire, so the ring never drains
+// and DRAM sees each row once per evaluation.  X^T R needs no atomics.  After the last slab the G accumulators
+// (F/128 tiles x 16 TMEM columns) are drained, scaled by 1/(n std_f) and written to the solver's
+// gradient vector.  A first pass over the same ring computes the per-feature standard deviation
+// (Spark standardisation) straight from shared memory.
 //
 // The solver driving these evaluations (L-BFGS + strong-Wolfe, or SGD) is solver.cuh; pull / push /
 // apply over peer memory is comm.cuh.  Replaces LogisticRegressionTaskSpark.calculateGradients
@@ -23,30 +28,32 @@
 
 namespace {
 constexpr int kThreads = 256;
-constexpr int kSlabRows = 64;
-constexpr int kBlockK = 64;                          // features per chunk (128-byte swizzle row)
-constexpr int kChunkBytes = kSlabRows * kBlockK * 2;  // 8 KB
-constexpr int kBChunkBytes = 16 * kBlockK * 2;        // 2 KB of Wsp per chunk
-constexpr int kRBytes = 2048;                         // Rsp: 8 k-groups x (2 n-groups x 128 B)
-constexpr int kTmemCols = 256;
-constexpr int kColZ = 0;
-constexpr int kColG = 32;
+constexpr int kSlabRows = 128;
+constexpr int kBlockK = 64;                           // features per chunk (128-byte swizzle row)
+constexpr int kChunkBytes = kSlabRows * kBlockK * 2;   // 16 KB
+constexpr int kBChunkBytes = 16 * kBlockK * 2;         // 2 KB of Wsp per chunk
+constexpr int kRBytes = 4096;                          // Rsp: 16 k-groups x (2 n-groups x 128 B)
+constexpr int kTmemCols = 256;                         // two co-resident CTAs fit the SM's 512 columns
+constexpr int kColZ = 0;                               // Z_0 at 0, Z_1 at 16
+constexpr int kColG = 32;                              // G tile j at 32 + 16*j
+// (Rotating consecutive MMAs over independent accumulators was measured: no gain — an SS-mode
+//  128x16x16 MMA costs ~80 cycles of operand fetch regardless of accumulator dependencies.)
 
 struct TcShared {
-    unsigned char* ring;      // NS x 8 KB, 1024-aligned
+    unsigned char* ring;      // kNS x 16 KB, 1024-aligned
     unsigned char* sB;        // nkb x 2 KB
-    unsigned char* sR;        // 2 KB
+    unsigned char* sR;        // 2 x 4 KB
     float* inv;               // [F]
-    float* sred;              // [16]
+    float* sred;              // [32]
     double* red;              // [34]
-    uint64_t* full;           // [NS]
-    uint64_t* empty;          // [NS]
-    uint64_t* z_full;
-    uint64_t* r_full;
+    uint64_t* full;           // [kNS]
+    uint64_t* empty;          // [kNS]
+    uint64_t* z_full;         // [2]
+    uint64_t* r_full;         // [2]
     uint64_t* g_full;
     uint32_t* tmem_slot;
     volatile int* fail;
-    volatile unsigned int* chunk_base;   // chunks streamed so far (ring position), shared by all roles
+    volatile unsigned int* chunk_base;   // ring position (chunks streamed so far), shared by all roles
 };
 
 __device__ __forceinline__ bool wait_or_fail(uint64_t* bar, uint32_t parity, volatile int* fail) {
@@ -65,9 +72,13 @@ struct TcEval {
     const CUtensorMap* tmX;
     const int* labels;        // this worker's [cap]
     int row_base;             // w * cap (row coordinate of slot 0 in the tensor map)
-    int start, count, cap, F, R, NS;
+    int start, count, cap, F, R, kNS;      // kNS: ring slots (even: chunk pairs stay adjacent)
     uint32_t tmem;
     TcShared sh;
+    unsigned int zuse[2], ruse[2], guse;   // per-thread running barrier use counts (persist across evaluations)
+#ifdef PSB_TC_PROFILE
+    long long prof[4];                     // cycles: [0] wait full(A) [1] wait r_full [2] wait full(B) [3] role total
+#endif
 
     __device__ __forceinline__ bool row_valid(int slot) const {
         int d = slot - start;
@@ -75,59 +86,75 @@ struct TcEval {
         return d < count;
     }
     __device__ __forceinline__ bool slab_active(int b) const {
-        // window = [start, start+count) mod cap; slab = [64b, 64b+64)
         const int lo = b * kSlabRows, hi = lo + kSlabRows;
         const int e = start + count;
         if (e <= cap) return lo < e && hi > start;
         return hi > start || lo < e - cap;
     }
+    __device__ int num_active_slabs() const {
+        int n = 0;
+        for (int b = 0; b < cap / kSlabRows; ++b) n += slab_active(b) ? 1 : 0;
+        return n;
+    }
+    // b-th slab index of the q-th active slab
+    __device__ int active_slab(int q) const {
+        for (int b = 0; b < cap / kSlabRows; ++b)
+            if (slab_active(b) && q-- == 0) return b;
+        return 0;
+    }
 
-    // ---- TMA producer (one thread): all chunks of all active slabs
-    __device__ void produce() const {
-        const int nkb = F / kBlockK;
+    // ---- TMA producer (one thread).  with_b: stream every slab twice, A(s) then B(s).
+    __device__ void produce(bool with_b) const {
+        const int nkb = F / kBlockK, S = num_active_slabs();
         unsigned int pc = *sh.chunk_base;
-        for (int b = 0; b < cap / kSlabRows; ++b) {
-            if (!slab_active(b)) continue;
-            for (int c = 0; c < nkb; ++c, ++pc) {
-                const int slot = pc % NS;
-                const unsigned use = pc / NS;
-                if (use > 0 && !wait_or_fail(sh.empty + slot, (use - 1) & 1, sh.fail)) return;
-                tc::mbar_arrive_expect_tx(sh.full + slot, kChunkBytes);
-                tc::tma_load_2d(sh.ring + (size_t)slot * kChunkBytes, tmX, c * kBlockK, row_base + b * kSlabRows,
-                                sh.full + slot);
-            }
+        auto load = [&](int b, int c, uint64_t policy) -> bool {
+            const int slot = pc % kNS;
+            const unsigned use = pc / kNS;
+            if (use > 0 && !wait_or_fail(sh.empty + slot, (use - 1) & 1, sh.fail)) return false;
+            tc::mbar_arrive_expect_tx(sh.full + slot, kChunkBytes);
+            tc::tma_load_2d_hint(sh.ring + (size_t)slot * kChunkBytes, tmX, c * kBlockK, row_base + b * kSlabRows,
+                                 sh.full + slot, policy);
+            ++pc;
+            return true;
+        };
+        for (int q = 0; q < S; ++q) {
+            const int b = active_slab(q);
+            for (int c = 0; c < nkb; ++c)
+                if (!load(b, c, with_b ? tc::kL2EvictLast : tc::kL2EvictFirst)) return;
+            if (with_b)
+                for (int c = 0; c < nkb; ++c)
+                    if (!load(b, c, tc::kL2EvictFirst)) return;
         }
     }
 
     // ---- statistics pass consumer: warp `wi` of 4 takes chunks c with c % 4 == wi; lane = feature pair
     __device__ void stats_consume(int wi, int lane) const {
-        const int nkb = F / kBlockK;
+        const int nkb = F / kBlockK, S = num_active_slabs();
         const unsigned int base = *sh.chunk_base;
         float s0[4] = {0.f, 0.f, 0.f, 0.f}, s1[4] = {0.f, 0.f, 0.f, 0.f};
         float q0[4] = {0.f, 0.f, 0.f, 0.f}, q1[4] = {0.f, 0.f, 0.f, 0.f};
-        unsigned int q = 0;
-        for (int b = 0; b < cap / kSlabRows; ++b) {
-            if (!slab_active(b)) continue;
+        for (int q = 0; q < S; ++q) {
+            const int b = active_slab(q);
 #pragma unroll
             for (int k = 0; k < 4; ++k) {
                 const int c = wi + 4 * k;
                 if (c >= nkb) break;
                 const unsigned int pc = base + q * nkb + c;
-                const int slot = pc % NS;
-                if (!wait_or_fail(sh.full + slot, (pc / NS) & 1, sh.fail)) return;
+                const int slot = pc % kNS;
+                if (!wait_or_fail(sh.full + slot, (pc / kNS) & 1, sh.fail)) return;
                 const unsigned char* tile = sh.ring + (size_t)slot * kChunkBytes;
-#pragma unroll 8
+#pragma unroll 16
                 for (int r = 0; r < kSlabRows; ++r) {
-                    if (!row_valid(b * kSlabRows + r)) continue;
+                    const float m = row_valid(b * kSlabRows + r) ? 1.f : 0.f;
                     const __half2 h = *(const __half2*)(tile + tc::sw128_off(r, lane >> 2) + (lane & 3) * 4);
-                    const float2 x = __half22float2(h);
+                    float2 x = __half22float2(h);
+                    x.x *= m, x.y *= m;
                     s0[k] += x.x, q0[k] = fmaf(x.x, x.x, q0[k]);
                     s1[k] += x.y, q1[k] = fmaf(x.y, x.y, q1[k]);
                 }
                 __syncwarp();
                 if (lane == 0) tc::mbar_arrive(sh.empty + slot);
             }
-            ++q;
         }
         const float n = (float)count;
 #pragma unroll
@@ -142,96 +169,137 @@ struct TcEval {
         }
     }
 
-    // ---- MMA issuer (one thread)
+    // ---- MMA issuer: the whole warp walks the ring in stream order (warp-uniform state), one elected
+    //      lane issues the tcgen05 instructions
     __device__ void mma_loop() {
-        const int nkb = F / kBlockK;
-        constexpr uint32_t idesc1 = tc::idesc_f16(64, 16, 0, 0);     // GEMM1: A K-major, B K-major
+        const int nkb = F / kBlockK, S = __shfl_sync(0xffffffffu, num_active_slabs(), 0);
+        constexpr uint32_t idesc1 = tc::idesc_f16(128, 16, 0, 0);    // GEMM1: A K-major, B K-major
         constexpr uint32_t idesc2 = tc::idesc_f16(128, 16, 1, 1);    // GEMM2: A MN-major, B MN-major
-        const unsigned int base = *sh.chunk_base;
-        unsigned int q = 0;
+        unsigned int pc = __shfl_sync(0xffffffffu, *sh.chunk_base, 0);
+        const uint32_t tmem_u = __shfl_sync(0xffffffffu, tmem, 0);
         const uint32_t sB0 = tc::smem_u32(sh.sB), sR0 = tc::smem_u32(sh.sR), ring0 = tc::smem_u32(sh.ring);
-        for (int b = 0; b < cap / kSlabRows; ++b) {
-            if (!slab_active(b)) continue;
-            const unsigned int pc0 = base + q * nkb;
-            // GEMM1 over the slab's chunks as they land
-            for (int c = 0; c < nkb; ++c) {
-                const unsigned int pc = pc0 + c;
-                const int slot = pc % NS;
-                if (!wait_or_fail(sh.full + slot, (pc / NS) & 1, sh.fail)) return;
+
+        auto gemm1 = [&](int q) -> bool {                       // Z_{q&1} = A(q) x Wsp
+            for (int c = 0; c < nkb; ++c, ++pc) {
+                const int slot = pc % kNS;
+#ifdef PSB_TC_PROFILE
+                const long long tw = clock64();
+#endif
+                if (!wait_or_fail(sh.full + slot, (pc / kNS) & 1, sh.fail)) return false;
+#ifdef PSB_TC_PROFILE
+                prof[0] += clock64() - tw;
+#endif
                 tc::tc_fence_after();
                 const uint64_t ad = tc::desc_k_sw128(ring0 + slot * kChunkBytes, 1024);
                 const uint64_t bd = tc::desc_k_sw128(sB0 + c * kBChunkBytes, 1024);
+                if (tc::elect_one()) {
 #pragma unroll
-                for (int k = 0; k < kBlockK / 16; ++k)
-                    tc::umma_f16(tmem + kColZ, ad + 2 * k, bd + 2 * k, idesc1, (c | k) ? 1u : 0u);
-            }
-            tc::umma_commit(sh.z_full);
-            // residuals of this slab are written by the epilogue warps
-            if (!wait_or_fail(sh.r_full, rphase & 1, sh.fail)) return;
-            ++rphase;
-            tc::tc_fence_after();
-            // GEMM2: G[128 features x 16] += slab^T[128 x 16 rows] x Rsp[16 rows x 16], 4 K-steps of 16 rows
-            for (int j = 0; j < nkb / 2; ++j) {
-                const int slot = (pc0 + 2 * j) % NS;            // chunks 2j and 2j+1 are adjacent in the ring
-#pragma unroll
-                for (int ks = 0; ks < kSlabRows / 16; ++ks) {
-                    const uint64_t ad = tc::desc_mn_sw128(ring0 + slot * kChunkBytes + ks * 2048, kChunkBytes, 1024);
-                    const uint64_t bd = tc::desc_mn_none(sR0 + ks * 512, 256, 128);
-                    tc::umma_f16(tmem + kColG + 16 * j, ad, bd, idesc2, (q | ks) ? 1u : 0u);
+                    for (int k = 0; k < kBlockK / 16; ++k)
+                        tc::umma_f16(tmem_u + kColZ + 16 * (q & 1), ad + 2 * k, bd + 2 * k, idesc1, (c | k) ? 1u : 0u);
+                    tc::umma_commit(sh.empty + slot);
+                    if (c == nkb - 1) tc::umma_commit(sh.z_full + (q & 1));
                 }
+                __syncwarp();
             }
-            for (int c = 0; c < nkb; ++c) tc::umma_commit(sh.empty + (pc0 + c) % NS);
-            ++q;
+            return true;
+        };
+        auto gemm2 = [&](int q) -> bool {                       // G += B(q)^T x Rsp_{q&1}
+#ifdef PSB_TC_PROFILE
+            const long long tr = clock64();
+#endif
+            if (!wait_or_fail(sh.r_full + (q & 1), ruse[q & 1] & 1, sh.fail)) return false;
+            ++ruse[q & 1];
+#ifdef PSB_TC_PROFILE
+#endif
+            tc::tc_fence_after();
+            for (int j = 0; j < nkb / 2; ++j, pc += 2) {
+                const int slot = pc % kNS;                      // chunks 2j, 2j+1 sit in adjacent slots
+#ifdef PSB_TC_PROFILE
+                const long long tb = clock64();
+#endif
+                if (!wait_or_fail(sh.full + slot, (pc / kNS) & 1, sh.fail)) return false;
+                if (!wait_or_fail(sh.full + slot + 1, ((pc + 1) / kNS) & 1, sh.fail)) return false;
+#ifdef PSB_TC_PROFILE
+                prof[2] += clock64() - tb;
+#endif
+                tc::tc_fence_after();
+                const uint64_t ad0 = tc::desc_mn_sw128(ring0 + slot * kChunkBytes, kChunkBytes, 1024);
+                const uint64_t bd0 = tc::desc_mn_none(sR0 + (q & 1) * kRBytes, 256, 128);
+                if (tc::elect_one()) {
+#pragma unroll
+                    for (int ks = 0; ks < kSlabRows / 16; ++ks)      // +2048 B of A, +512 B of B per 16 rows
+                        tc::umma_f16(tmem_u + kColG + 16 * j, ad0 + (uint64_t)(ks * 128), bd0 + (uint64_t)(ks * 32),
+                                     idesc2, (q | ks) ? 1u : 0u);
+                    tc::umma_commit(sh.empty + slot);
+                    tc::umma_commit(sh.empty + slot + 1);
+                }
+                __syncwarp();
+            }
+            return true;
+        };
+        for (int q = 0; q < S; ++q) {
+#ifdef PSB_TC_PROFILE
+            const long long tg = clock64();
+#endif
+            if (!gemm1(q)) return;
+#ifdef PSB_TC_PROFILE
+            prof[1] += clock64() - tg;
+#endif
+            if (!gemm2(q)) return;
         }
-        tc::umma_commit(sh.g_full);
+        if (tc::elect_one()) tc::umma_commit(sh.g_full);
+        __syncwarp();
     }
 
-    // ---- epilogue warps (4 warps; wi = TMEM sub-partition = warp % 4)
+    // ---- epilogue warps (4 warps; wi = TMEM sub-partition = warp % 4); thread = row of the slab
     __device__ void epilogue(int wi, int lane, float* g, float invn) {
-        const int nkb = F / kBlockK;
+        const int nkb = F / kBlockK, S = num_active_slabs();
         float lsum = 0.f, rs[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
         const float* bias = sh.sred + 16;            // intercepts staged behind the reduction words
-        for (int b = 0; b < cap / kSlabRows; ++b) {
-            if (!slab_active(b)) continue;
-            if (!wait_or_fail(sh.z_full, zphase & 1, sh.fail)) return;
-            ++zphase;
+        for (int q = 0; q < S; ++q) {
+            const int b = active_slab(q), zb = q & 1;
+            if (!wait_or_fail(sh.z_full + zb, zuse[zb] & 1, sh.fail)) return;
+            ++zuse[zb];
             tc::tc_fence_after();
             float v[16];
-            tc::tmem_ld_32x32b_x16(tmem + kColZ + ((uint32_t)(wi * 32) << 16), v);
-            if (lane < 16) {                         // M=64: rows 16*wi .. 16*wi+15 sit in lanes 0..15
-                const int r = wi * 16 + lane;
-                const int slot = b * kSlabRows + r;
-                float rr[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-                if (row_valid(slot)) {
-                    float z[8];
+            tc::tmem_ld_32x32b_x16(tmem + kColZ + 16 * zb + ((uint32_t)(wi * 32) << 16), v);
+            const int r = wi * 32 + lane;
+            const int slot = b * kSlabRows + r;
+            float rr[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+            if (row_valid(slot)) {
+                float z[8];
 #pragma unroll
-                    for (int c = 0; c < 8; ++c) z[c] = v[c] + v[8 + c];
-                    lsum += softmax_residual(z, bias, labels[slot], R, rr);
+                for (int c = 0; c < 8; ++c) z[c] = v[c] + v[8 + c];
+                lsum += softmax_residual(z, bias, labels[slot], R, rr);
 #pragma unroll
-                    for (int c = 0; c < 8; ++c) rs[c] += rr[c];
-                }
-                // Rsp as MN-major no-swizzle B: core matrix (k-group kg, n-group ng) at kg*256 + ng*128,
-                // row k%8 at +16 bytes each; n-group 0 = fp16 high parts, n-group 1 = low parts
-                __align__(16) __half hi[8], lo[8];
-#pragma unroll
-                for (int c = 0; c < 8; ++c) tc::split_half(rr[c], hi[c], lo[c]);
-                unsigned char* dst = sh.sR + (r >> 3) * 256 + (r & 7) * 16;
-                *(uint4*)dst = *(const uint4*)hi;
-                *(uint4*)(dst + 128) = *(const uint4*)lo;
+                for (int c = 0; c < 8; ++c) rs[c] += rr[c];
             }
+            // Rsp as MN-major no-swizzle B: core matrix (k-group kg, n-group ng) at kg*256 + ng*128,
+            // row k%8 at +16 bytes each; n-group 0 = fp16 high parts, n-group 1 = low parts
+            __align__(16) __half hi[8], lo[8];
+#pragma unroll
+            for (int c = 0; c < 8; ++c) tc::split_half(rr[c], hi[c], lo[c]);
+            unsigned char* dst = sh.sR + zb * kRBytes + (r >> 3) * 256 + (r & 7) * 16;
+            *(uint4*)dst = *(const uint4*)hi;
+            *(uint4*)(dst + 128) = *(const uint4*)lo;
             tc::fence_proxy_async_smem();
             tc::tc_fence_before();
             __syncwarp();
-            if (lane == 0) tc::mbar_arrive(sh.r_full);
+            if (lane == 0) tc::mbar_arrive(sh.r_full + zb);
         }
-        if (lane < 16) {
+        for (int o = 16; o; o >>= 1) {
+            lsum += __shfl_xor_sync(0xffffffffu, lsum, o);
+#pragma unroll
+            for (int c = 0; c < 8; ++c) rs[c] += __shfl_xor_sync(0xffffffffu, rs[c], o);
+        }
+        if (lane == 0) {
             atomicAdd(&sh.sred[0], lsum);
 #pragma unroll
             for (int c = 0; c < 8; ++c) atomicAdd(&sh.sred[1 + c], rs[c]);
         }
         // drain the gradient accumulators: thread = feature row of each 128-feature tile
-        if (!wait_or_fail(sh.g_full, gphase & 1, sh.fail)) return;
-        ++gphase;
+        if (!wait_or_fail(sh.g_full, guse & 1, sh.fail)) return;
+        ++guse;
         tc::tc_fence_after();
         for (int j = 0; j < nkb / 2; ++j) {
             float v[16];
@@ -245,14 +313,6 @@ struct TcEval {
         tc::tc_fence_before();
     }
 
-    unsigned int zphase, gphase, rphase;   // per-thread running barrier phases (persist across evaluations)
-
-    __device__ int num_active_slabs() const {
-        int n = 0;
-        for (int b = 0; b < cap / kSlabRows; ++b) n += slab_active(b) ? 1 : 0;
-        return n;
-    }
-
     // ---- statistics pass (all threads enter)
     __device__ void stats_pass(int standardize) {
         const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -262,7 +322,7 @@ struct TcEval {
             return;
         }
         if (warp == 0) {
-            if (lane == 0) produce();
+            if (lane == 0) produce(false);
             __syncwarp();
         } else if (warp >= 2 && warp < 6) {
             stats_consume(warp - 2, lane);
@@ -296,16 +356,22 @@ struct TcEval {
         __syncthreads();
         const float invn = 1.f / (float)count;
         if (warp == 0) {
-            if (lane == 0) produce();
+            if (lane == 0) produce(true);
             __syncwarp();
         } else if (warp == 1) {
-            if (lane == 0) mma_loop();
+#ifdef PSB_TC_PROFILE
+            const long long tm0 = clock64();
+#endif
+            mma_loop();
+#ifdef PSB_TC_PROFILE
+            prof[3] += clock64() - tm0;
+#endif
             __syncwarp();
         } else if (warp < 6) {
             epilogue(warp & 3, lane, g, invn);
         }
         __syncthreads();
-        if (tid == 0) *sh.chunk_base += (unsigned)num_active_slabs() * (F / kBlockK);
+        if (tid == 0) *sh.chunk_base += 2u * (unsigned)num_active_slabs() * (F / kBlockK);
         if (tid < 8) g[F * 8 + tid] = sh.sred[1 + tid] * invn;
         const double loss = (double)sh.sred[0] * (double)invn;
         __syncthreads();
@@ -314,8 +380,8 @@ struct TcEval {
 };
 }  // namespace
 
-__global__ void __launch_bounds__(kThreads, 1)
-psb_worker_tc_kernel(const __grid_constant__ CUtensorMap tmX, PsbSolver sv, CommCtx cx, int NS,
+__global__ void __launch_bounds__(kThreads, 2)
+psb_worker_tc_kernel(const __grid_constant__ CUtensorMap tmX, PsbSolver sv, CommCtx cx, int kNS,
                      const int* __restrict__ labels, const int* __restrict__ win, const float* __restrict__ w_in,
                      float* __restrict__ delta_out, float* __restrict__ loss_out, int* __restrict__ info_out,
                      float* __restrict__ scratch) {
@@ -329,16 +395,16 @@ psb_worker_tc_kernel(const __grid_constant__ CUtensorMap tmX, PsbSolver sv, Comm
 
     TcShared sh;
     sh.ring = smem;
-    sh.sB = sh.ring + (size_t)NS * kChunkBytes;
+    sh.sB = sh.ring + (size_t)kNS * kChunkBytes;
     sh.sR = sh.sB + (size_t)nkb * kBChunkBytes;
-    sh.inv = (float*)(sh.sR + kRBytes);
+    sh.inv = (float*)(sh.sR + 2 * kRBytes);
     sh.sred = sh.inv + F;
     sh.red = (double*)(sh.sred + 32);
     sh.full = (uint64_t*)(sh.red + 34);
-    sh.empty = sh.full + NS;
-    sh.z_full = sh.empty + NS;
-    sh.r_full = sh.z_full + 1;
-    sh.g_full = sh.r_full + 1;
+    sh.empty = sh.full + kNS;
+    sh.z_full = sh.empty + kNS;
+    sh.r_full = sh.z_full + 2;
+    sh.g_full = sh.r_full + 2;
     sh.tmem_slot = (uint32_t*)(sh.g_full + 1);
     sh.fail = &s_fail;
     sh.chunk_base = &s_chunk_base;
@@ -346,9 +412,8 @@ psb_worker_tc_kernel(const __grid_constant__ CUtensorMap tmX, PsbSolver sv, Comm
     if (tid == 0) {
         s_fail = 0, s_chunk_base = 0;
         tc::tma_prefetch_desc(&tmX);
-        for (int s = 0; s < NS; ++s) tc::mbar_init(sh.full + s, 1), tc::mbar_init(sh.empty + s, 1);
-        tc::mbar_init(sh.z_full, 1);
-        tc::mbar_init(sh.r_full, 4);
+        for (int s = 0; s < kNS; ++s) tc::mbar_init(sh.full + s, 1), tc::mbar_init(sh.empty + s, 1);
+        for (int i = 0; i < 2; ++i) tc::mbar_init(sh.z_full + i, 1), tc::mbar_init(sh.r_full + i, 4);
         tc::mbar_init(sh.g_full, 1);
         tc::mbar_fence_init();
     }
@@ -365,6 +430,7 @@ psb_worker_tc_kernel(const __grid_constant__ CUtensorMap tmX, PsbSolver sv, Comm
     const int* lw = labels + (size_t)w * cap;
 
     // ---- pull
+    const long long t_begin = clock64();
     float* w0 = ws.w0;
     bool alive = true;
     if (cx.c.mode == PSB_COMM_NONE) {
@@ -376,7 +442,7 @@ psb_worker_tc_kernel(const __grid_constant__ CUtensorMap tmX, PsbSolver sv, Comm
     if (alive && count <= 0) {
         if (tid == 0) {
             loss_out[w] = nanf("");
-            info_out[4 * w + 2] = -1, info_out[4 * w + 3] = 0;
+            info_out[8 * w + 2] = -1, info_out[8 * w + 3] = 0;
         }
         if (cx.c.mode != PSB_COMM_NONE) {
             for (int i = tid; i < n4; i += blockDim.x) ((float4*)ws.vec[5])[i] = make_float4(0, 0, 0, 0);
@@ -388,10 +454,15 @@ psb_worker_tc_kernel(const __grid_constant__ CUtensorMap tmX, PsbSolver sv, Comm
     if (alive) {
         TcEval ev;
         ev.tmX = &tmX, ev.labels = lw, ev.row_base = w * cap;
-        ev.start = start, ev.count = count, ev.cap = cap, ev.F = F, ev.R = R, ev.NS = NS;
-        ev.tmem = tmem, ev.sh = sh, ev.zphase = 0, ev.gphase = 0, ev.rphase = 0;
+        ev.start = start, ev.count = count, ev.cap = cap, ev.F = F, ev.R = R, ev.kNS = kNS;
+        ev.tmem = tmem, ev.sh = sh;
+        ev.zuse[0] = ev.zuse[1] = ev.ruse[0] = ev.ruse[1] = ev.guse = 0;
+#ifdef PSB_TC_PROFILE
+        ev.prof[0] = ev.prof[1] = ev.prof[2] = ev.prof[3] = 0;
+#endif
 
         ev.stats_pass(sv.standardize);
+        const long long t_stats = clock64();
 
         SolveVecs v;
         ws.bind(v);
@@ -400,14 +471,16 @@ psb_worker_tc_kernel(const __grid_constant__ CUtensorMap tmX, PsbSolver sv, Comm
         __syncthreads();
 
         SolveResult res = local_solve(ev, v, sv.solver, sv.max_iter, sv.sgd_lr, sh.red);
+        const long long t_solve = clock64();
 
         float* delta = v.tmp;
         finish_delta(delta, v.x, w0, sh.inv, F, R, sv.center && sv.solver == PSB_SOLVER_LBFGS);
         __syncthreads();
         if (tid == 0) {
             loss_out[w] = s_fail ? nanf("") : (float)res.loss;
-            info_out[4 * w + 0] = res.evals, info_out[4 * w + 1] = res.iterations;
-            info_out[4 * w + 2] = s_fail ? -2 : res.status, info_out[4 * w + 3] = count;
+            info_out[8 * w + 0] = res.evals, info_out[8 * w + 1] = res.iterations;
+            info_out[8 * w + 2] = s_fail ? -2 : res.status, info_out[8 * w + 3] = count;
+            info_out[8 * w + 4] = (int)((t_stats - t_begin) >> 6), info_out[8 * w + 5] = (int)((t_solve - t_stats) >> 6);
         }
         if (cx.c.mode == PSB_COMM_NONE) {
             float4* out = (float4*)(delta_out + (size_t)w * nv);
@@ -415,6 +488,11 @@ psb_worker_tc_kernel(const __grid_constant__ CUtensorMap tmX, PsbSolver sv, Comm
         } else {
             comm_push(cx, (const float4*)delta);
         }
+        if (tid == 0) info_out[8 * w + 6] = (int)((clock64() - t_solve) >> 6), info_out[8 * w + 7] = (int)((clock64() - t_begin) >> 6);
+#ifdef PSB_TC_PROFILE
+        __syncthreads();
+        if (tid == 32) for (int k = 0; k < 4; ++k) info_out[8 * w + 4 + k] = (int)(ev.prof[k] >> 6);
+#endif
     }
     tc::tc_fence_before();
     __syncthreads();
@@ -426,22 +504,36 @@ int psb_launch_worker_tc(const PsbSolver* s, const CommCtx& cx, int num_workers,
                          float* d_scratch, cudaStream_t stream) {
     const int F = s->num_features, cap = s->cap;
     if (F % 128 != 0 || F > 1024 || cap % kSlabRows != 0) {
-        psb_set_error("tcgen05 worker kernel needs num_features %% 128 == 0, <= 1024 and max_buffer_size %% 64 == 0 "
+        psb_set_error("tcgen05 worker kernel needs num_features %% 128 == 0, <= 1024 and max_buffer_size %% 128 == 0 "
                       "(got %d, %d): use the SIMT kernel for this shape", F, cap);
         return PSB_E_INVALID;
     }
     const int nkb = F / kBlockK;
-    int NS = nkb + 4;                                           // one resident slab + 4 chunks of prefetch
-    size_t fixed = (size_t)nkb * kBChunkBytes + kRBytes + (size_t)F * 4 + 32 * 4 + 34 * 8 + 64;
-    while ((size_t)(NS + 2) * kChunkBytes + fixed + (size_t)(NS + 2) * 16 + 2048 <= 225 * 1024 && NS + 2 <= 2 * nkb)
-        NS += 2;
-    const size_t smem = 1024 + (size_t)NS * kChunkBytes + fixed + (size_t)NS * 16 + 64;
+    // More workers than SMs: 4-slot rings so that two CTAs share an SM and one worker's vector / epilogue
+    // phases overlap the other's streaming; otherwise one CTA per SM with a deep ring.
+    int num_sms = 148;
+    {
+        int dev = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, dev);
+    }
+    auto smem_for = [&](int ns) {
+        return 1024 + (size_t)ns * kChunkBytes + (size_t)nkb * kBChunkBytes + 2 * kRBytes + (size_t)F * 4 + 32 * 4 +
+               34 * 8 + (size_t)(2 * ns + 5) * 8 + 64;
+    };
+    int kNS = 10;
+    while (kNS > 2 && smem_for(kNS) > 225 * 1024) kNS -= 2;
+    if (num_workers > num_sms) {
+        kNS = 4;
+        while (kNS > 2 && 2 * (smem_for(kNS) + 1024) > 227 * 1024) kNS -= 2;
+    }
+    const size_t smem = smem_for(kNS);
     CUtensorMap tm;
     int rc = psb_make_tmap_2d_f16(&tm, d_X, (uint64_t)num_workers * cap, (uint64_t)F, kSlabRows, kBlockK);
     if (rc) return rc;
     PSB_CHECK_CUDA(cudaFuncSetAttribute(psb_worker_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    psb_worker_tc_kernel<<<num_workers, kThreads, smem, stream>>>(tm, *s, cx, NS, d_labels, d_win, d_w_in, d_delta,
-                                                                  d_loss, d_info, d_scratch);
+    psb_worker_tc_kernel<<<num_workers, kThreads, smem, stream>>>(tm, *s, cx, kNS, d_labels, d_win, d_w_in, d_delta, d_loss,
+                                                                  d_info, d_scratch);
     PSB_CHECK_CUDA(cudaGetLastError());
     return 0;
 }

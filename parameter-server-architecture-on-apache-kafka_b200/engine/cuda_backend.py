@@ -38,7 +38,7 @@ class CudaBackend:
         self.w_in = torch.zeros(self.nv, dtype=torch.float32, device=dev)
         self.delta = torch.zeros((1, self.nv), dtype=torch.float32, device=dev)
         self.loss = torch.zeros(1, dtype=torch.float32, device=dev)
-        self.info = torch.zeros((1, 4), dtype=torch.int32, device=dev)
+        self.info = torch.zeros((1, 8), dtype=torch.int32, device=dev)
         self.scratch = torch.zeros(native.scratch_floats(F), dtype=torch.float32, device=dev)
         self.conf = torch.zeros(64, dtype=torch.int32, device=dev)
         self.mout = torch.zeros(2, dtype=torch.float32, device=dev)

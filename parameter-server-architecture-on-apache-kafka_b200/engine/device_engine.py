@@ -51,7 +51,7 @@ class DeviceEngine:
         self.win_host = torch.zeros((self.W, 2), dtype=torch.int32).pin_memory()
         self.win = torch.zeros((self.W, 2), dtype=torch.int32, device=dev)
         self.loss = torch.zeros(self.W, dtype=torch.float32, device=dev)
-        self.info = torch.zeros((self.W, 4), dtype=torch.int32, device=dev)
+        self.info = torch.zeros((self.W, 8), dtype=torch.int32, device=dev)
         self.delta = torch.zeros((self.W, self.nv), dtype=torch.float32, device=dev)
         self.scratch = torch.zeros((self.W, native.scratch_floats(F)), dtype=torch.float32, device=dev)
         self.loss_host = torch.zeros(self.W, dtype=torch.float32).pin_memory()

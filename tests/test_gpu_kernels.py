@@ -53,7 +53,7 @@ def _run_step(native, batches, W0, F, cap, solver, impl, standardize=True, cente
     w_in = torch.from_numpy(W0.reshape(-1)).to(dev)
     delta = torch.zeros((W, lay.device_size), dtype=torch.float32, device=dev)
     loss = torch.zeros(W, dtype=torch.float32, device=dev)
-    info = torch.zeros((W, 4), dtype=torch.int32, device=dev)
+    info = torch.zeros((W, 8), dtype=torch.int32, device=dev)
     scratch = torch.zeros((W, native.scratch_floats(F)), dtype=torch.float32, device=dev)
     sv = native.make_solver(F, lay.R, cap, solver, max_iter, standardize, center, 0.5)
     native.worker_step(sv, native.comm_none(), W, impl, X, labels, win, w_in, delta, loss, info, scratch)

@@ -56,7 +56,7 @@ def test_static_scratch_step_matches_regular_step_twice(impl):
         for name in ("regular", "static"):
             delta = torch.zeros((W, nv), dtype=torch.float32, device=dev)
             loss = torch.zeros(W, dtype=torch.float32, device=dev)
-            info = torch.zeros((W, 4), dtype=torch.int32, device=dev)
+            info = torch.zeros((W, 8), dtype=torch.int32, device=dev)
             if name == "regular":
                 rc = L.psb_worker_step(C.byref(sv), C.byref(comm), W, impl, X.data_ptr(), y.data_ptr(), win.data_ptr(),
                                        w_in.data_ptr(), delta.data_ptr(), loss.data_ptr(), info.data_ptr(),
@@ -71,7 +71,7 @@ def test_static_scratch_step_matches_regular_step_twice(impl):
         d0, l0, i0 = out["regular"]
         d1, l1, i1 = out["static"]
         assert np.isfinite(l1).all() and np.abs(d0).max() > 0
-        assert np.array_equal(i0, i1)
+        assert np.array_equal(i0[:, :4], i1[:, :4])                             # evals, iterations, status, rows
         assert np.abs(l0 - l1).max() < 2e-3 * max(1.0, np.abs(l0).max())        # same tolerance as test_gpu_kernels
         assert np.abs(d0 - d1).max() < 2e-3 * max(1e-3, np.abs(d0).max())
 
