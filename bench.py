@@ -42,6 +42,8 @@ def parse():
     p.add_argument("--consistency_model", type=int, default=0)
     p.add_argument("--ingest_rows", type=int, default=128, help="new rows per worker per step in the e2e run")
     p.add_argument("--no_e2e", action="store_true")
+    p.add_argument("--transport", default="p2p", choices=["p2p", "nccl"],
+                   help="p2p: fused peer-memory push/apply/pull (product); nccl: all_reduce baseline")
     return p.parse_args()
 
 
@@ -146,7 +148,11 @@ def main():
                    max_buffer_size=cap, min_buffer_size=min(128, cap), local_solver=a.solver)
     w0 = (np.random.default_rng(0).standard_normal((F + 1, 8)) * 0.01).astype(np.float32)   # random-init weights
     w0[:, 6:] = 0
-    eng = DeviceEngine(cfg, W, rank, world, impl, dev, w0=w0, stage_rows=W * a.ingest_rows)
+    if a.transport == "nccl":
+        from psb200.parallel.nccl_baseline import NcclBaselineEngine as Engine
+    else:
+        Engine = DeviceEngine
+    eng = Engine(cfg, W, rank, world, impl, dev, w0=w0, stage_rows=W * a.ingest_rows)
     eng.connect()
     X, y = synth_buffers(torch, W, cap, F, a.density, 1234 + rank, dev)
     eng.fill(X, y)
@@ -233,7 +239,7 @@ def main():
             "ms_per_step": ms / a.steps, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": value / BASELINE_SAMPLES_PER_SEC, "dtype": "fp16 data / fp32 accumulate+weights",
             "data": "synthetic (fine-food-reviews-shaped hashed BoW rows generated on device; random-init weights)",
-            "impl": "ours", "kernel": "tcgen05" if impl == native.IMPL_TC else "simt",
+            "impl": "ours", "transport": a.transport, "kernel": "tcgen05" if impl == native.IMPL_TC else "simt",
             "gpu_launches": launches, "clocks": clocks, "e2e": e2e,
             "config": {"model": f"multinomial logistic regression {F}->6 class rows ({(F + 1) * 6} params)",
                        "global_batch": W * world * cap, "seq_len": None,

@@ -156,6 +156,8 @@ class DeviceEngine:
             now_ms = np.zeros(n, dtype=np.float64)
         native.buffers_on_batch(self.buffers, workers[:n], now_ms[:n], self.stage_ws_host.numpy(),
                                 self.win_host.numpy())
+        for w, c in zip(*np.unique(np.asarray(workers[:n]), return_counts=True)):
+            self.buffers[int(w)].total += int(c)
         self._ingest_staged(rows_f16, labels, n, wait)
 
     def ingest_slots(self, rows_f16: torch.Tensor, labels: torch.Tensor, worker_slot: torch.Tensor,
@@ -210,6 +212,15 @@ class DeviceEngine:
             raise NotImplementedError("gather of async shards across ranks: use weights_gathered()")
         ptr = L.psb_comm_shard_weights(self.block, self.F, self.world)
         return _view(ptr, self.nv, self.device).view(self.layout.device_rows, 8)
+
+    def reset_clock_words(self, clock: int) -> None:
+        """After a resume: every version / clock word of this rank's block restarts at `clock`."""
+        words = torch.full((2 * 32,), int(clock), dtype=torch.int32, device=self.device)
+        L = native.lib()
+        st = L.psb_comm_status(self.block, self.F, self.world)
+        # layout (csrc/common.cuh): status 256 B | arrivals 256 B | tickets 256 B | version 128 B | clocks 128 B
+        _view(st + 768, 64, self.device, torch.int32).copy_(words)
+        torch.cuda.synchronize(self.device)
 
     def status(self) -> int:
         ptr = native.lib().psb_comm_status(self.block, self.F, self.world)

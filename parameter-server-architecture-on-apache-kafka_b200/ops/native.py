@@ -163,11 +163,17 @@ class NativeBuffer:
         if not self.h:
             raise NativeError("psb_buffer_create failed")
         self.head = self.count = self.target = 0
+        self.total = 0
+
+    def ring_total(self) -> int:
+        """rows ever inserted (numTuplesSeen of the reference worker log)"""
+        return self.total
 
     def on_event(self, now_ms: float) -> int:
         h, c, t = C.c_int(), C.c_int(), C.c_int()
         slot = lib().psb_buffer_on_event(self.h, float(now_ms), C.byref(h), C.byref(c), C.byref(t))
         self.head, self.count, self.target = h.value, c.value, t.value
+        self.total += 1
         return slot
 
     def __del__(self):

@@ -1,0 +1,42 @@
+"""The fused entry point end to end on one GPU: logs in the reference format, checkpoint and resume."""
+import os
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+
+torch = pytest.importorskip("torch")
+
+from psb200.config import SERVER_LOG_HEADER, WORKER_LOG_HEADER
+from psb200.utils.logs import parse_log
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ENV = dict(os.environ, PYTHONPATH=ROOT + os.pathsep + os.environ.get("PYTHONPATH", ""))
+
+
+def _node(cwd, *extra):
+    cmd = [sys.executable, "-m", "psb200.apps.node", "-training", "synthetic:3000", "-test", "synthetic:800", "-p", "0",
+           "--workers_per_gpu", "4", "-max", "256", "-l", *extra]
+    return subprocess.run(cmd, env=ENV, cwd=cwd, capture_output=True, text=True, timeout=600)
+
+
+@pytest.mark.parametrize("model", [0, -1])
+def test_node_streams_learns_and_resumes(tmp_path, model):
+    ck = str(tmp_path / "ck")
+    r = _node(tmp_path, "--max_clock", "4", "-c", str(model), "--checkpoint_dir", ck, "--checkpoint_every", "2")
+    assert r.returncode == 0, r.stderr[-3000:]
+    s = open(tmp_path / "logs-server.csv").read().splitlines()
+    w = open(tmp_path / "logs-worker.csv").read().splitlines()
+    assert s[0] == SERVER_LOG_HEADER and w[0] == WORKER_LOG_HEADER
+    srows, wrows = parse_log(s, "server"), parse_log(w, "worker")
+    assert list(srows[:, 2]) == [0, 1, 2, 3] and len(wrows) == 16
+    assert np.all(np.isfinite(wrows[:, 3])) and srows[-1, 4] > 0.2
+    if model == 0:
+        assert os.path.exists(os.path.join(ck, "weights-4.csv"))
+        r = _node(tmp_path, "--max_clock", "6", "--checkpoint_dir", ck, "--resume")
+        assert r.returncode == 0, r.stderr[-3000:]
+        s2 = parse_log(str(tmp_path / "logs-server.csv"), "server")
+        assert list(s2[:, 2]) == [4, 5]                    # resumed at the checkpointed clock
+        assert s2[0, 4] > 0.2                              # ... with the checkpointed weights, not zeros
