@@ -278,3 +278,154 @@ extern "C" int psb_buffers_on_batch(void** buffers, int num_buffers, const int* 
     }
     return 0;
 }
+
+// ------------------------------------------------------------------ streaming producer thread
+// Replaces CsvProducer (CsvProducer.java:36-87) + the INPUT_DATA topic: a host thread tokenises the CSV,
+// keeps the rows of this rank's partitions (row i -> worker i % numWorkers, :61), converts them to dense
+// fp16 and fills a ring of PINNED batches that the engine ships with cudaMemcpyAsync on its ingestion
+// stream.  Pacing is the reference's: the first numWorkers*128 rows unthrottled (:73), then a 1000 ms
+// sleep every 1000/p rows (:75-82); p > 1000 sleeps p ms per row and p == 0 never sleeps (quirk Q7).
+#include <atomic>
+#include <chrono>
+#include <thread>
+
+#include <cuda_fp16.h>
+
+namespace {
+struct Producer {
+    std::string path;
+    int has_header, num_workers, wbegin, wcount, F, p_ms, batch_rows, num_batches, flush_ms;
+    uint16_t* rows;
+    int* labels;
+    int* workers;
+    double* times;
+    std::vector<std::atomic<int>> ready;      // -1 free, >=0 rows published
+    std::atomic<long long> rows_sent{0};      // global rows "sent" (all partitions)
+    std::atomic<int> eof{0}, stop{0};
+    std::thread th;
+    int read_cursor = 0;                      // consumer side: next batch to poll
+    Producer(int nb) : ready(nb) {
+        for (auto& r : ready) r.store(-1);
+    }
+};
+
+void producer_main(Producer* P) {
+    FILE* f = fopen(P->path.c_str(), "rb");
+    if (!f) {
+        P->eof.store(2);
+        return;
+    }
+    const auto t0 = std::chrono::steady_clock::now();
+    auto now_ms = [&] { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count(); };
+    std::vector<char> line(1 << 16);
+    std::string acc;
+    long long row_count = 0;
+    const long long warm = (long long)P->num_workers * 128;
+    int batch = 0, fill = 0;
+    double batch_t0 = 0.0;
+    auto publish = [&] {
+        if (fill == 0) return;
+        P->ready[batch].store(fill, std::memory_order_release);
+        batch = (batch + 1) % P->num_batches, fill = 0;
+    };
+    auto wait_free = [&]() -> bool {
+        while (P->ready[batch].load(std::memory_order_acquire) != -1) {
+            if (P->stop.load()) return false;
+            std::this_thread::sleep_for(std::chrono::microseconds(100));
+        }
+        return true;
+    };
+    bool first = true;
+    while (!P->stop.load() && fgets(line.data(), (int)line.size(), f)) {
+        acc.assign(line.data());
+        while (!acc.empty() && acc.back() != '\n' && fgets(line.data(), (int)line.size(), f)) acc += line.data();
+        while (!acc.empty() && (acc.back() == '\n' || acc.back() == '\r' || acc.back() == ' ')) acc.pop_back();
+        if (first && P->has_header) {
+            first = false;
+            continue;
+        }
+        first = false;
+        if (acc.empty()) continue;
+        const int part = (int)(row_count % P->num_workers);
+        if (part >= P->wbegin && part < P->wbegin + P->wcount) {
+            if (fill == 0) {
+                if (!wait_free()) break;
+                batch_t0 = now_ms();
+            }
+            uint16_t* dst = P->rows + ((size_t)batch * P->batch_rows + fill) * P->F;
+            memset(dst, 0, (size_t)P->F * 2);
+            int nc = 0;
+            const int F = P->F;
+            const int label = parse_line(acc.data(), acc.data() + acc.size(), &nc, [&](int c, float v) {
+                if (c < F) {
+                    const __half h = __float2half(v);
+                    memcpy(dst + c, &h, 2);
+                }
+            });
+            const size_t o = (size_t)batch * P->batch_rows + fill;
+            P->labels[o] = label, P->workers[o] = part - P->wbegin, P->times[o] = now_ms();
+            if (++fill == P->batch_rows) publish();
+        }
+        ++row_count;
+        P->rows_sent.store(row_count);
+        if (fill && now_ms() - batch_t0 > P->flush_ms) publish();
+        if (P->p_ms > 0 && row_count >= warm) {
+            int sleep_ms = 0;
+            if (P->p_ms <= 1000) {
+                if (row_count % (1000 / P->p_ms) == 0) sleep_ms = 1000;
+            } else {
+                sleep_ms = P->p_ms;
+            }
+            if (sleep_ms) {
+                publish();
+                for (int s = 0; s < sleep_ms && !P->stop.load(); s += 10)
+                    std::this_thread::sleep_for(std::chrono::milliseconds(std::min(10, sleep_ms - s)));
+            }
+        }
+    }
+    publish();
+    fclose(f);
+    P->eof.store(1);
+}
+}  // namespace
+
+extern "C" void* psb_producer_start(const char* path, int has_header, int num_workers_total, int worker_begin,
+                                    int worker_count, int num_features, int p_ms, int batch_rows, int num_batches,
+                                    void* h_rows_f16, int* h_labels, int* h_workers, double* h_times, int flush_ms) {
+    if (!path || num_workers_total < 1 || worker_count < 1 || batch_rows < 1 || num_batches < 2 || !h_rows_f16) {
+        psb_set_error("psb_producer_start: bad arguments");
+        return nullptr;
+    }
+    Producer* P = new Producer(num_batches);
+    P->path = path, P->has_header = has_header, P->num_workers = num_workers_total, P->wbegin = worker_begin;
+    P->wcount = worker_count, P->F = num_features, P->p_ms = p_ms, P->batch_rows = batch_rows;
+    P->num_batches = num_batches, P->flush_ms = flush_ms > 0 ? flush_ms : 50;
+    P->rows = (uint16_t*)h_rows_f16, P->labels = h_labels, P->workers = h_workers, P->times = h_times;
+    P->th = std::thread(producer_main, P);
+    return P;
+}
+// 1: *batch holds *n rows (release it after the copy); 0: nothing ready.  *eof: 1 when the file is done
+// AND every batch was consumed ("CSV Producer sent all records!"), 2 when the file could not be opened.
+extern "C" int psb_producer_poll(void* h, int* batch, int* n, int* eof) {
+    Producer* P = (Producer*)h;
+    const int r = P->ready[P->read_cursor].load(std::memory_order_acquire);
+    if (r >= 0) {
+        *batch = P->read_cursor, *n = r, *eof = 0;
+        return 1;
+    }
+    const int e = P->eof.load();
+    *eof = (e && P->ready[P->read_cursor].load(std::memory_order_acquire) < 0) ? e : 0;
+    return 0;
+}
+extern "C" void psb_producer_release(void* h, int batch) {
+    Producer* P = (Producer*)h;
+    P->ready[batch].store(-1, std::memory_order_release);
+    P->read_cursor = (batch + 1) % P->num_batches;
+}
+extern "C" long long psb_producer_rows_sent(void* h) { return ((Producer*)h)->rows_sent.load(); }
+extern "C" void psb_producer_stop(void* h) {
+    Producer* P = (Producer*)h;
+    P->stop.store(1);
+    if (P->th.joinable()) P->th.join();
+    delete P;
+}

@@ -155,6 +155,19 @@ int psb_buffer_on_event(void* b, double now_ms, int* head, int* count, int* targ
 int psb_buffers_on_batch(void** buffers, int num_buffers, const int* workers, const double* now_ms, int n,
                          int* worker_slot, int* win);
 
+/* Streaming producer thread (CsvProducer.java:36-87 + INPUT_DATA): tokenises the CSV on a host thread,
+ * keeps the rows of partitions [worker_begin, worker_begin + worker_count), converts them to dense fp16
+ * and fills a ring of `num_batches` caller-provided PINNED batches (h_rows_f16[num_batches][batch_rows][F],
+ * h_labels / h_workers / h_times [num_batches][batch_rows]); -p pacing as in the reference.
+ * poll: 1 = batch ready (*batch, *n), 0 = nothing; *eof = 1 once the file is exhausted and drained. */
+void* psb_producer_start(const char* path, int has_header, int num_workers_total, int worker_begin,
+                         int worker_count, int num_features, int p_ms, int batch_rows, int num_batches,
+                         void* h_rows_f16, int* h_labels, int* h_workers, double* h_times, int flush_ms);
+int psb_producer_poll(void* h, int* batch, int* n, int* eof);
+void psb_producer_release(void* h, int batch);
+long long psb_producer_rows_sent(void* h);
+void psb_producer_stop(void* h);
+
 /* Peer memory: raw cudaMalloc (IPC-exportable, unlike a caching-allocator block) and IPC export /
  * import of a device allocation (transport set-up; replaces ServerApp.createTopics, ServerApp.java:31-42) */
 int psb_malloc(void** d_ptr_out, size_t bytes);

@@ -66,7 +66,8 @@ def main(argv: Optional[List[str]] = None) -> int:
                   "min_buffer_size", "max_buffer_size", "buffer_size_coefficient", "num_workers"):
             print(f"    {k}: {getattr(cfg, k)}")
         print(f"    ranks: {world} x {W} workers\n")
-    train = load_csv_or_synthetic(cfg.training_data_file_path, cfg, "train")
+    streaming_file = not cfg.training_data_file_path.startswith("synthetic:")
+    train = None if streaming_file else load_csv_or_synthetic(cfg.training_data_file_path, cfg, "train")
     test = load_csv_or_synthetic(cfg.test_data_file_path, cfg, "test")
     impl = native.IMPL_TC if ns.impl == "tc" else native.IMPL_SIMT
     if impl == native.IMPL_TC and (cfg.num_features % 128 or cfg.num_features > 1024 or cfg.max_buffer_size % 128):
@@ -94,13 +95,23 @@ def main(argv: Optional[List[str]] = None) -> int:
     worker_log = LogSink.to_file(wl_name, WORKER_LOG_HEADER) if cfg.logging else (LogSink() if rank == 0 else None)
 
     # this rank's slice of the stream: global row i goes to worker i % numWorkers (CsvProducer.java:61)
-    n_total = len(train)
-    gw = np.arange(n_total) % cfg.num_workers
-    mine = np.nonzero((gw >= rank * W) & (gw < (rank + 1) * W))[0]
-    cursor = int(resume_meta["rows_ingested"]) // max(world, 1) if resume_meta else 0
-    dense = train.to_dense(np.float16)
-    pin_rows = torch.zeros((eng.stage_rows, cfg.num_features), dtype=torch.float16).pin_memory()
-    pin_lab = torch.zeros(eng.stage_rows, dtype=torch.int32).pin_memory()
+    producer = None
+    if streaming_file:
+        # real CSV: the C++ producer thread tokenises, paces (-p) and fills pinned batches for this rank
+        if not os.path.exists(cfg.training_data_file_path):
+            raise FileNotFoundError(f"training data file not found: {cfg.training_data_file_path}")
+        producer = native.StreamProducer(cfg.training_data_file_path, cfg.num_workers, rank * W, W, cfg.num_features,
+                                         cfg.producer_time_per_event, batch_rows=eng.stage_rows, num_batches=4)
+        n_total, mine, cursor = 0, np.zeros(0, dtype=np.int64), 0
+    else:
+        n_total = len(train)
+        gw = np.arange(n_total) % cfg.num_workers
+        mine = np.nonzero((gw >= rank * W) & (gw < (rank + 1) * W))[0]
+        cursor = int(resume_meta["rows_ingested"]) // max(world, 1) if resume_meta else 0
+        dense = train.to_dense(np.float16)
+        pin_rows = torch.zeros((eng.stage_rows, cfg.num_features), dtype=torch.float16).pin_memory()
+        pin_lab = torch.zeros(eng.stage_rows, dtype=torch.int32).pin_memory()
+    producer_eof = False
     delays = {int(a): float(b) for a, b in (x.split(":") for x in cfg.inject_delay.split(",") if x)}
     wd = Watchdog(lambda: eng.clock, eng.status, ns.watchdog_s).start()
     p_ms = cfg.producer_time_per_event
@@ -110,16 +121,32 @@ def main(argv: Optional[List[str]] = None) -> int:
     max_clock = cfg.max_clock
     try:
         while True:
-            # ---- producer slice: how many of my rows are due now?
-            if p_ms <= 0:
+            if producer is not None:
+                # ---- drain whatever the producer thread has published
+                for _ in range(4):
+                    b, n, eof = producer.poll()
+                    if b is None:
+                        if eof == 2:
+                            raise FileNotFoundError(cfg.training_data_file_path)
+                        producer_eof = producer_eof or eof == 1
+                        break
+                    eng.ingest(producer.rows[b, :n], producer.labels[b, :n], producer.workers[b, :n].numpy(),
+                               producer.times[b, :n].numpy())
+                    eng.ingest_done.synchronize()           # the pinned batch may be refilled after this
+                    producer.release(b)
+                    if p_ms <= 0:
+                        break                               # unthrottled: one batch per clock
+            # ---- in-memory slice: how many of my rows are due now?
+            elif p_ms <= 0:
                 due = min(len(mine), cursor + W * rows_per_clock)
             else:
                 elapsed = time.time() - t_start
                 rate = (1000.0 / p_ms) if p_ms <= 1000 else 1000.0 / p_ms
                 global_due = min(n_total, warm + int(elapsed * rate))
                 due = int(np.searchsorted(mine, global_due))
-            due = min(due, cursor + eng.stage_rows)
-            if due > cursor:
+            if producer is None:
+                due = min(due, cursor + eng.stage_rows)
+            if producer is None and due > cursor:
                 idx = mine[cursor:due]
                 n = len(idx)
                 pin_rows[:n].copy_(torch.from_numpy(dense[idx]))
@@ -128,7 +155,8 @@ def main(argv: Optional[List[str]] = None) -> int:
                     np.arange(n, dtype=np.float64) // max(W, 1)
                 eng.ingest(pin_rows[:n], pin_lab[:n], (gw[idx] - rank * W).astype(np.int32), now)
                 cursor = due
-            if cursor >= len(mine) and not eof_announced and rank == 0:
+            done_feeding = producer_eof if producer is not None else cursor >= len(mine)
+            if done_feeding and not eof_announced and rank == 0:
                 server_log.println("CSV Producer sent all records!")
                 eof_announced = True
             if eng.rows_ingested == 0:
@@ -156,10 +184,12 @@ def main(argv: Optional[List[str]] = None) -> int:
                 raise RuntimeError(wd.tripped)
             if max_clock >= 0 and eng.clock >= max_clock:
                 break
-            if max_clock < 0 and cursor >= len(mine):
+            if max_clock < 0 and done_feeding:
                 break
     finally:
         wd.stop()
+        if producer is not None:
+            producer.stop()
     if world > 1:
         dist.barrier()
     for s in (server_log, worker_log):

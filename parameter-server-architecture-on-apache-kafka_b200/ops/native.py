@@ -90,6 +90,14 @@ def lib() -> C.CDLL:
     L.psb_buffer_destroy.argtypes = [vp]
     L.psb_buffer_on_event.argtypes = [vp, C.c_double, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int)]
     L.psb_buffers_on_batch.argtypes = [vp, C.c_int, vp, vp, C.c_int, vp, vp]
+    L.psb_producer_start.restype = C.c_void_p
+    L.psb_producer_start.argtypes = [C.c_char_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
+                                     vp, vp, vp, vp, C.c_int]
+    L.psb_producer_poll.argtypes = [vp, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int)]
+    L.psb_producer_release.argtypes = [vp, C.c_int]
+    L.psb_producer_rows_sent.restype = C.c_longlong
+    L.psb_producer_rows_sent.argtypes = [vp]
+    L.psb_producer_stop.argtypes = [vp]
     L.psb_ipc_export.argtypes = [vp, vp]
     L.psb_ipc_import.argtypes = [vp, C.POINTER(C.c_void_p)]
     L.psb_ipc_close.argtypes = [vp]
@@ -190,6 +198,51 @@ def buffers_on_batch(buffers, workers: np.ndarray, now_ms: np.ndarray, worker_sl
     now_ms = np.ascontiguousarray(now_ms, dtype=np.float64)
     check(lib().psb_buffers_on_batch(arr, len(buffers), workers.ctypes.data, now_ms.ctypes.data, n,
                                      worker_slot.ctypes.data, win.ctypes.data), "psb_buffers_on_batch")
+
+
+class StreamProducer:
+    """Host producer thread filling a ring of pinned batches (see psb_producer_start)."""
+
+    def __init__(self, path: str, num_workers_total: int, worker_begin: int, worker_count: int, num_features: int,
+                 p_ms: int, batch_rows: int = 1024, num_batches: int = 4, has_header: bool = True, flush_ms: int = 50):
+        import torch
+        pin = torch.cuda.is_available()
+        mk = (lambda *s, dtype: torch.zeros(*s, dtype=dtype).pin_memory()) if pin else \
+            (lambda *s, dtype: torch.zeros(*s, dtype=dtype))
+        self.rows = mk(num_batches, batch_rows, num_features, dtype=torch.float16)
+        self.labels = mk(num_batches, batch_rows, dtype=torch.int32)
+        self.workers = mk(num_batches, batch_rows, dtype=torch.int32)
+        self.times = mk(num_batches, batch_rows, dtype=torch.float64)
+        self.h = lib().psb_producer_start(path.encode(), int(has_header), num_workers_total, worker_begin, worker_count,
+                                          num_features, int(p_ms), batch_rows, num_batches, self.rows.data_ptr(),
+                                          self.labels.data_ptr(), self.workers.data_ptr(), self.times.data_ptr(),
+                                          flush_ms)
+        if not self.h:
+            raise NativeError("psb_producer_start: " + lib().psb_last_error().decode())
+
+    def poll(self):
+        """(batch, n, eof): batch is None when nothing is ready; eof is 0, 1 (done) or 2 (file not found)."""
+        b, n, e = C.c_int(), C.c_int(), C.c_int()
+        if lib().psb_producer_poll(self.h, C.byref(b), C.byref(n), C.byref(e)):
+            return b.value, n.value, 0
+        return None, 0, e.value
+
+    def release(self, batch: int) -> None:
+        lib().psb_producer_release(self.h, batch)
+
+    def rows_sent(self) -> int:
+        return lib().psb_producer_rows_sent(self.h)
+
+    def stop(self) -> None:
+        if self.h:
+            lib().psb_producer_stop(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.stop()
+        except Exception:
+            pass
 
 
 # ------------------------------------------------------------------ device wrappers

@@ -40,3 +40,20 @@ def test_node_streams_learns_and_resumes(tmp_path, model):
         s2 = parse_log(str(tmp_path / "logs-server.csv"), "server")
         assert list(s2[:, 2]) == [4, 5]                    # resumed at the checkpointed clock
         assert s2[0, 4] > 0.2                              # ... with the checkpointed weights, not zeros
+
+
+def test_node_streams_a_csv_file_through_the_producer_thread(tmp_path):
+    from psb200.data import ReviewGenerator, write_csv
+    gen = ReviewGenerator(num_features=256, vocab=2000, mean_len=60.0)
+    write_csv(str(tmp_path / "train.csv"), gen.train_split(1500))
+    write_csv(str(tmp_path / "test.csv"), gen.test_split(400))
+    cmd = [sys.executable, "-m", "psb200.apps.node", "-training", "train.csv", "-test", "test.csv", "-p", "0",
+           "--num_features", "256", "--workers_per_gpu", "2", "-max", "256", "-l"]
+    r = subprocess.run(cmd, env=ENV, cwd=tmp_path, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stderr[-3000:]
+    s = open(tmp_path / "logs-server.csv").read().splitlines()
+    assert "CSV Producer sent all records!" in s
+    srows = parse_log(s, "server")
+    wrows = parse_log(str(tmp_path / "logs-worker.csv"), "worker")
+    assert len(srows) >= 2 and wrows[:, 6].max() == 750          # each of the 2 workers saw half of the 1500 rows
+    assert srows[-1, 4] > srows[0, 4] - 0.05

@@ -1,0 +1,61 @@
+"""The C++ producer thread: partition filter, fp16 rows, batching, pacing, EOF (CsvProducer.java:36-87)."""
+import os
+import time
+
+import numpy as np
+
+from psb200.data import ReviewGenerator, write_csv
+from psb200.ops import native
+
+
+def _drain(prod, timeout=20.0):
+    rows, labels, workers, times = [], [], [], []
+    t0 = time.time()
+    while time.time() - t0 < timeout:
+        b, n, eof = prod.poll()
+        if b is None:
+            if eof:
+                break
+            time.sleep(0.002)
+            continue
+        rows.append(prod.rows[b, :n].clone()), labels.append(prod.labels[b, :n].clone())
+        workers.append(prod.workers[b, :n].clone()), times.append(prod.times[b, :n].clone())
+        prod.release(b)
+    cat = lambda xs: np.concatenate([x.numpy() for x in xs]) if xs else np.zeros(0)
+    return cat(rows), cat(labels), cat(workers), cat(times), eof
+
+
+def test_unthrottled_partition_slice(tmp_path):
+    b = ReviewGenerator(num_features=64, vocab=500, mean_len=12).train_split(500)
+    path = os.path.join(tmp_path, "t.csv")
+    write_csv(path, b)
+    prod = native.StreamProducer(path, 4, 1, 2, 64, 0, batch_rows=64, num_batches=3)   # partitions 1 and 2 of 4
+    rows, labels, workers, times, eof = _drain(prod)
+    prod.stop()
+    assert eof == 1
+    idx = np.nonzero(np.isin(np.arange(500) % 4, (1, 2)))[0]
+    assert len(rows) == len(idx) == 250
+    assert np.array_equal(labels, b.labels[idx]) and np.array_equal(workers, (idx % 4) - 1)
+    assert np.allclose(rows.astype(np.float32), b.to_dense(np.float16)[idx].astype(np.float32), atol=2e-3)
+
+
+def test_pacing_after_warmup(tmp_path):
+    b = ReviewGenerator(num_features=16, vocab=100, mean_len=6).train_split(128 + 30)
+    path = os.path.join(tmp_path, "t.csv")
+    write_csv(path, b)
+    prod = native.StreamProducer(path, 1, 0, 1, 16, 100, batch_rows=32, num_batches=4)   # 10 rows / s after 128 rows
+    t0 = time.time()
+    rows, labels, workers, times, eof = _drain(prod, timeout=15)
+    took = time.time() - t0
+    prod.stop()
+    assert eof == 1 and len(rows) == 158
+    assert times[127] < 500.0                        # warm-up rows arrive at once
+    assert 2.5 < took < 6.0                          # 30 paced rows at 10 rows/s -> ~3 s
+    assert times[-1] - times[128] > 1900.0
+
+
+def test_missing_file_reports_error(tmp_path):
+    prod = native.StreamProducer(os.path.join(tmp_path, "nope.csv"), 1, 0, 1, 16, 0)
+    _, _, _, _, eof = _drain(prod, timeout=5)
+    prod.stop()
+    assert eof == 2
