@@ -1,0 +1,25 @@
+"""BASELINE config 1: the shipped small sample through the in-process runner (sequential, 2 workers, CPU)."""
+import os
+import subprocess
+import sys
+
+import numpy as np
+
+from psb200.utils.logs import parse_log
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+SAMPLE = os.path.join(ROOT, "mockData", "small-sample")
+
+
+def test_small_sample_sequential_two_workers(tmp_path):
+    env = dict(os.environ, PYTHONPATH=ROOT)
+    r = subprocess.run([sys.executable, "-m", "psb200.apps.server_app_runner",
+                        "-training", os.path.join(SAMPLE, "small_sample_reviews_embedded_training.csv"),
+                        "-test", os.path.join(SAMPLE, "small_sample_reviews_embedded_test.csv"),
+                        "-c", "0", "-p", "0", "--num_workers", "2", "--in_process", "--max_clock", "4", "-l",
+                        "-min", "16", "-max", "64"], env=env, cwd=tmp_path, capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stderr
+    s = parse_log(str(tmp_path / "logs-server.csv"), "server")
+    w = parse_log(str(tmp_path / "logs-worker.csv"), "worker")
+    assert len(s) == 4 and len(w) >= 8 and np.all(w[:, 6] == 60)
+    assert np.all((s[:, 4] >= 0) & (s[:, 4] <= 1))
