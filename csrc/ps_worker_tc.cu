@@ -14,8 +14,8 @@
 // with B(s) and A(s+1); every chunk is released as soon as its MMAs retire, so the ring never drains
 // and DRAM sees each row once per evaluation.  X^T R needs no atomics.  After the last slab the G accumulators
 // (F/128 tiles x 16 TMEM columns) are drained, scaled by 1/(n std_f) and written to the solver's
-// gradient vector.  A first pass over the same ring computes the per-feature standard deviation
-// (Spark standardisation) straight from shared memory.
+// gradient vector.  The per-feature standard deviation (Spark standardisation) is computed by two
+// otherwise idle warps straight from the shared-memory chunks of the FIRST evaluation's A stream.
 //
 // The solver driving these evaluations (L-BFGS + strong-Wolfe, or SGD) is solver.cuh; pull / push /
 // apply over peer memory is comm.cuh.  Replaces LogisticRegressionTaskSpark.calculateGradients
@@ -42,7 +42,7 @@ constexpr int kColG = 32;                              // G tile j at 32 + 16*j
 struct TcShared {
     unsigned char* ring;      // kNS x 16 KB, 1024-aligned
     unsigned char* sB;        // nkb x 2 KB
-    unsigned char* sR;        // 2 x 4 KB
+    unsigned char* sR;        // 4 KB Rsp + 4 KB per-feature sums of the fused statistics
     float* inv;               // [F]
     float* sred;              // [32]
     double* red;              // [34]
@@ -51,9 +51,12 @@ struct TcShared {
     uint64_t* z_full;         // [2]
     uint64_t* r_full;         // [2]
     uint64_t* g_full;
+    uint64_t* sdone;          // [kNS] statistics warps finished reading the slot (fused first evaluation)
+    uint64_t* inv_ready;      // 1/std written (fused first evaluation)
     uint32_t* tmem_slot;
     volatile int* fail;
     volatile unsigned int* chunk_base;   // ring position (chunks streamed so far), shared by all roles
+    volatile int* need_redo;             // a constant non-zero column was found: redo the first evaluation
 };
 
 __device__ __forceinline__ bool wait_or_fail(uint64_t* bar, uint32_t parity, volatile int* fail) {
@@ -91,6 +94,15 @@ struct TcEval {
         if (e <= cap) return lo < e && hi > start;
         return hi > start || lo < e - cap;
     }
+    // true when the window cannot start or end strictly inside slab b (so first/last row valid => all valid)
+    __device__ __forceinline__ bool slab_rows_contiguous(int b) const {
+        const int lo = b * kSlabRows, hi = lo + kSlabRows;
+        int e = start + count;
+        if (e > cap) e -= cap;
+        const bool start_inside = start > lo && start < hi;
+        const bool end_inside = e > lo && e < hi;
+        return count == cap || !(start_inside || end_inside);
+    }
     __device__ int num_active_slabs() const {
         int n = 0;
         for (int b = 0; b < cap / kSlabRows; ++b) n += slab_active(b) ? 1 : 0;
@@ -104,13 +116,23 @@ struct TcEval {
     }
 
     // ---- TMA producer (one thread).  with_b: stream every slab twice, A(s) then B(s).
-    __device__ void produce(bool with_b) const {
+    // fused: the statistics warps also read every A chunk, so a slot whose previous occupant was an A chunk
+    // of this pass is refilled only after their sdone arrival as well.
+    __device__ void produce(bool with_b, bool fused = false) const {
         const int nkb = F / kBlockK, S = num_active_slabs();
         unsigned int pc = *sh.chunk_base;
+        const unsigned int base = pc;
+        unsigned int sd_cnt[16];
+#pragma unroll
+        for (int i = 0; i < 16; ++i) sd_cnt[i] = 0;
         auto load = [&](int b, int c, uint64_t policy) -> bool {
             const int slot = pc % kNS;
             const unsigned use = pc / kNS;
             if (use > 0 && !wait_or_fail(sh.empty + slot, (use - 1) & 1, sh.fail)) return false;
+            if (fused && pc >= base + (unsigned)kNS && (((pc - kNS - base) / nkb) & 1u) == 0u) {
+                if (!wait_or_fail(sh.sdone + slot, sd_cnt[slot] & 1, sh.fail)) return false;
+                ++sd_cnt[slot];
+            }
             tc::mbar_arrive_expect_tx(sh.full + slot, kChunkBytes);
             tc::tma_load_2d_hint(sh.ring + (size_t)slot * kChunkBytes, tmX, c * kBlockK, row_base + b * kSlabRows,
                                  sh.full + slot, policy);
@@ -127,46 +149,78 @@ struct TcEval {
         }
     }
 
-    // ---- statistics pass consumer: warp `wi` of 4 takes chunks c with c % 4 == wi; lane = feature pair
-    __device__ void stats_consume(int wi, int lane) const {
+    // ---- statistics fused into the first evaluation: 2 warps (wi = 0, 1) read the A chunks with c % 2 == wi
+    //      while the MMA warp consumes them.  Each half-warp takes every other row, a lane reads 8 bytes
+    //      (4 features) per row; per-chunk register sums are folded into shared per-feature accumulators
+    //      (sum in the spare half of the Rsp region, sum of squares in inv[], converted in place at the end).
+    //      The warp also waits on the B chunks of its slots, doing nothing: every use of a ring slot has the
+    //      same chunk parity, so a warp that follows all of them is never more than one mbarrier phase ahead.
+    __device__ void stats_fused(int wi, int lane) const {
         const int nkb = F / kBlockK, S = num_active_slabs();
         const unsigned int base = *sh.chunk_base;
-        float s0[4] = {0.f, 0.f, 0.f, 0.f}, s1[4] = {0.f, 0.f, 0.f, 0.f};
-        float q0[4] = {0.f, 0.f, 0.f, 0.f}, q1[4] = {0.f, 0.f, 0.f, 0.f};
+        float* ssum = (float*)(sh.sR + kRBytes);
+        float* ssq = sh.inv;
+        const int h = lane >> 4, j8 = lane & 15;
         for (int q = 0; q < S; ++q) {
             const int b = active_slab(q);
-#pragma unroll
-            for (int k = 0; k < 4; ++k) {
-                const int c = wi + 4 * k;
-                if (c >= nkb) break;
-                const unsigned int pc = base + q * nkb + c;
+            const bool full_slab = row_valid(b * kSlabRows) && row_valid(b * kSlabRows + kSlabRows - 1) &&
+                                   slab_rows_contiguous(b);
+            for (int c = wi; c < nkb; c += 2) {
+                const unsigned int pc = base + (unsigned)q * 2u * nkb + c;
                 const int slot = pc % kNS;
                 if (!wait_or_fail(sh.full + slot, (pc / kNS) & 1, sh.fail)) return;
-                const unsigned char* tile = sh.ring + (size_t)slot * kChunkBytes;
-#pragma unroll 16
-                for (int r = 0; r < kSlabRows; ++r) {
-                    const float m = row_valid(b * kSlabRows + r) ? 1.f : 0.f;
-                    const __half2 h = *(const __half2*)(tile + tc::sw128_off(r, lane >> 2) + (lane & 3) * 4);
-                    float2 x = __half22float2(h);
-                    x.x *= m, x.y *= m;
-                    s0[k] += x.x, q0[k] = fmaf(x.x, x.x, q0[k]);
-                    s1[k] += x.y, q1[k] = fmaf(x.y, x.y, q1[k]);
+                const unsigned char* tile = sh.ring + (size_t)slot * kChunkBytes + (j8 & 1) * 8;
+                float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f, q0 = 0.f, q1 = 0.f, q2 = 0.f, q3 = 0.f;
+#pragma unroll 8
+                for (int i = 0; i < kSlabRows / 2; ++i) {
+                    const int r = 2 * i + h;
+                    const uint2 raw = *(const uint2*)(tile + tc::sw128_off(r, j8 >> 1));
+                    float2 x = __half22float2(*(const __half2*)&raw.x), y = __half22float2(*(const __half2*)&raw.y);
+                    if (!full_slab) {
+                        const float m = row_valid(b * kSlabRows + r) ? 1.f : 0.f;
+                        x.x *= m, x.y *= m, y.x *= m, y.y *= m;
+                    }
+                    a0 += x.x, a1 += x.y, a2 += y.x, a3 += y.y;
+                    q0 = fmaf(x.x, x.x, q0), q1 = fmaf(x.y, x.y, q1), q2 = fmaf(y.x, y.x, q2), q3 = fmaf(y.y, y.y, q3);
+                }
+                a0 += __shfl_xor_sync(0xffffffffu, a0, 16), a1 += __shfl_xor_sync(0xffffffffu, a1, 16);
+                a2 += __shfl_xor_sync(0xffffffffu, a2, 16), a3 += __shfl_xor_sync(0xffffffffu, a3, 16);
+                q0 += __shfl_xor_sync(0xffffffffu, q0, 16), q1 += __shfl_xor_sync(0xffffffffu, q1, 16);
+                q2 += __shfl_xor_sync(0xffffffffu, q2, 16), q3 += __shfl_xor_sync(0xffffffffu, q3, 16);
+                if (h == 0) {
+                    float4* ps = (float4*)(ssum + c * kBlockK + 4 * j8);
+                    float4* pq = (float4*)(ssq + c * kBlockK + 4 * j8);
+                    float4 u = *ps, v = *pq;
+                    *ps = make_float4(u.x + a0, u.y + a1, u.z + a2, u.w + a3);
+                    *pq = make_float4(v.x + q0, v.y + q1, v.z + q2, v.w + q3);
                 }
                 __syncwarp();
-                if (lane == 0) tc::mbar_arrive(sh.empty + slot);
+                if (lane == 0) tc::mbar_arrive(sh.sdone + slot);
+            }
+            for (int c = wi; c < nkb; c += 2) {                 // B chunks of my slots: follow the phases only
+                const unsigned int pc = base + (unsigned)q * 2u * nkb + nkb + c;
+                if (!wait_or_fail(sh.full + pc % kNS, (pc / kNS) & 1, sh.fail)) return;
             }
         }
+        __syncwarp();
         const float n = (float)count;
-#pragma unroll
-        for (int k = 0; k < 4; ++k) {
-            const int c = wi + 4 * k;
-            if (c >= nkb) break;
+        bool redo = false;
+        for (int c = wi; c < nkb; c += 2) {
             const int f = c * kBlockK + 2 * lane;
-            const float v0 = count > 1 ? (q0[k] - s0[k] * s0[k] / n) / (n - 1.f) : 0.f;
-            const float v1 = count > 1 ? (q1[k] - s1[k] * s1[k] / n) / (n - 1.f) : 0.f;
-            sh.inv[f] = v0 > 1e-12f ? rsqrtf(v0) : 0.f;
-            sh.inv[f + 1] = v1 > 1e-12f ? rsqrtf(v1) : 0.f;
+#pragma unroll
+            for (int e = 0; e < 2; ++e) {
+                const float s1 = ssum[f + e], s2 = ssq[f + e];
+                const float var = count > 1 ? (s2 - s1 * s1 / n) / (n - 1.f) : 0.f;
+                const float iv = var > 1e-12f ? rsqrtf(var) : 0.f;
+                ssq[f + e] = iv;                               // inv[] in place
+                // a constant NON-zero column gets weight 0 under standardisation, but this pass used w0 for it
+                redo = redo || (iv == 0.f && s2 != 0.f);
+            }
         }
+        if (redo) *sh.need_redo = 1;
+        __threadfence_block();
+        __syncwarp();
+        if (lane == 0) tc::mbar_arrive(sh.inv_ready);
     }
 
     // ---- MMA issuer: the whole warp walks the ring in stream order (warp-uniform state), one elected
@@ -207,8 +261,8 @@ struct TcEval {
 #ifdef PSB_TC_PROFILE
             const long long tr = clock64();
 #endif
-            if (!wait_or_fail(sh.r_full + (q & 1), ruse[q & 1] & 1, sh.fail)) return false;
-            ++ruse[q & 1];
+            if (!wait_or_fail(sh.r_full, ruse[0] & 1, sh.fail)) return false;
+            ++ruse[0];
 #ifdef PSB_TC_PROFILE
 #endif
             tc::tc_fence_after();
@@ -224,7 +278,7 @@ struct TcEval {
 #endif
                 tc::tc_fence_after();
                 const uint64_t ad0 = tc::desc_mn_sw128(ring0 + slot * kChunkBytes, kChunkBytes, 1024);
-                const uint64_t bd0 = tc::desc_mn_none(sR0 + (q & 1) * kRBytes, 256, 128);
+                const uint64_t bd0 = tc::desc_mn_none(sR0, 256, 128);   // one Rsp buffer: epilogue(q+1) starts after GEMM2(q)
                 if (tc::elect_one()) {
 #pragma unroll
                     for (int ks = 0; ks < kSlabRows / 16; ++ks)      // +2048 B of A, +512 B of B per 16 rows
@@ -252,7 +306,7 @@ struct TcEval {
     }
 
     // ---- epilogue warps (4 warps; wi = TMEM sub-partition = warp % 4); thread = row of the slab
-    __device__ void epilogue(int wi, int lane, float* g, float invn) {
+    __device__ void epilogue(int wi, int lane, float* g, float invn, bool fused) {
         const int nkb = F / kBlockK, S = num_active_slabs();
         float lsum = 0.f, rs[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
         const float* bias = sh.sred + 16;            // intercepts staged behind the reduction words
@@ -279,13 +333,13 @@ struct TcEval {
             __align__(16) __half hi[8], lo[8];
 #pragma unroll
             for (int c = 0; c < 8; ++c) tc::split_half(rr[c], hi[c], lo[c]);
-            unsigned char* dst = sh.sR + zb * kRBytes + (r >> 3) * 256 + (r & 7) * 16;
+            unsigned char* dst = sh.sR + (r >> 3) * 256 + (r & 7) * 16;
             *(uint4*)dst = *(const uint4*)hi;
             *(uint4*)(dst + 128) = *(const uint4*)lo;
             tc::fence_proxy_async_smem();
             tc::tc_fence_before();
             __syncwarp();
-            if (lane == 0) tc::mbar_arrive(sh.r_full + zb);
+            if (lane == 0) tc::mbar_arrive(sh.r_full);
         }
         for (int o = 16; o; o >>= 1) {
             lsum += __shfl_xor_sync(0xffffffffu, lsum, o);
@@ -298,6 +352,7 @@ struct TcEval {
             for (int c = 0; c < 8; ++c) atomicAdd(&sh.sred[1 + c], rs[c]);
         }
         // drain the gradient accumulators: thread = feature row of each 128-feature tile
+        if (fused && !wait_or_fail(sh.inv_ready, 0, sh.fail)) return;
         if (!wait_or_fail(sh.g_full, guse & 1, sh.fail)) return;
         ++guse;
         tc::tc_fence_after();
@@ -313,32 +368,23 @@ struct TcEval {
         tc::tc_fence_before();
     }
 
-    // ---- statistics pass (all threads enter)
-    __device__ void stats_pass(int standardize) {
-        const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-        if (!standardize) {
-            for (int f = tid; f < F; f += blockDim.x) sh.inv[f] = 1.f;
-            __syncthreads();
-            return;
-        }
-        if (warp == 0) {
-            if (lane == 0) produce(false);
-            __syncwarp();
-        } else if (warp >= 2 && warp < 6) {
-            stats_consume(warp - 2, lane);
-        }
-        __syncthreads();
-        if (tid == 0) *sh.chunk_base += (unsigned)num_active_slabs() * (F / kBlockK);
+    // ---- no standardisation: 1/std = 1 (all threads enter)
+    __device__ void unit_scale() {
+        for (int f = threadIdx.x; f < F; f += blockDim.x) sh.inv[f] = 1.f;
         __syncthreads();
     }
 
     // ---- loss + gradient at x (scaled space); all threads enter, all get the same loss
-    __device__ double eval(const float* x, float* g) {
+    __device__ double eval(const float* x, float* g) { return eval_impl(x, g, false); }
+
+    // fused: x holds the UNSCALED start weights w0 (1/std is not known yet: the statistics warps compute it
+    // during this very pass); the gradient is still returned in the scaled space.
+    __device__ double eval_impl(const float* x, float* g, bool fused) {
         const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
         // Wsp = (x * inv) split into fp16 hi | lo, K-major SWIZZLE_128B, 16 rows per 64-feature chunk
         for (int f = tid; f < F; f += blockDim.x) {
             const float4 a = ((const float4*)x)[2 * f], b = ((const float4*)x)[2 * f + 1];
-            const float sc = sh.inv[f];
+            const float sc = fused ? 1.f : sh.inv[f];
             const float w[8] = {a.x * sc, a.y * sc, a.z * sc, a.w * sc, b.x * sc, b.y * sc, b.z * sc, b.w * sc};
             const int kb = f >> 6, k = f & 63, j = k >> 3, e = k & 7;
             unsigned char* chunk = sh.sB + (size_t)kb * kBChunkBytes;
@@ -352,11 +398,13 @@ struct TcEval {
         }
         if (tid < 16) sh.sred[tid] = 0.f;
         if (tid < 8) sh.sred[16 + tid] = x[F * 8 + tid];          // intercepts (unscaled)
+        if (fused)
+            for (int f = tid; f < F; f += blockDim.x) sh.inv[f] = 0.f, ((float*)(sh.sR + kRBytes))[f] = 0.f;
         tc::fence_proxy_async_smem();
         __syncthreads();
         const float invn = 1.f / (float)count;
         if (warp == 0) {
-            if (lane == 0) produce(true);
+            if (lane == 0) produce(true, fused);
             __syncwarp();
         } else if (warp == 1) {
 #ifdef PSB_TC_PROFILE
@@ -368,7 +416,9 @@ struct TcEval {
 #endif
             __syncwarp();
         } else if (warp < 6) {
-            epilogue(warp & 3, lane, g, invn);
+            epilogue(warp & 3, lane, g, invn, fused);
+        } else if (fused) {
+            stats_fused(warp - 6, lane);
         }
         __syncthreads();
         if (tid == 0) *sh.chunk_base += 2u * (unsigned)num_active_slabs() * (F / kBlockK);
@@ -392,6 +442,7 @@ psb_worker_tc_kernel(const __grid_constant__ CUtensorMap tmX, PsbSolver sv, Comm
     const int w = blockIdx.x, tid = threadIdx.x, warp = tid >> 5;
     __shared__ int s_fail;
     __shared__ unsigned int s_chunk_base;
+    __shared__ int s_need_redo;
 
     TcShared sh;
     sh.ring = smem;
@@ -405,16 +456,21 @@ psb_worker_tc_kernel(const __grid_constant__ CUtensorMap tmX, PsbSolver sv, Comm
     sh.z_full = sh.empty + kNS;
     sh.r_full = sh.z_full + 2;
     sh.g_full = sh.r_full + 2;
-    sh.tmem_slot = (uint32_t*)(sh.g_full + 1);
+    sh.sdone = sh.g_full + 1;
+    sh.inv_ready = sh.sdone + kNS;
+    sh.tmem_slot = (uint32_t*)(sh.inv_ready + 1);
     sh.fail = &s_fail;
     sh.chunk_base = &s_chunk_base;
+    sh.need_redo = &s_need_redo;
 
     if (tid == 0) {
-        s_fail = 0, s_chunk_base = 0;
+        s_fail = 0, s_chunk_base = 0, s_need_redo = 0;
         tc::tma_prefetch_desc(&tmX);
         for (int s = 0; s < kNS; ++s) tc::mbar_init(sh.full + s, 1), tc::mbar_init(sh.empty + s, 1);
-        for (int i = 0; i < 2; ++i) tc::mbar_init(sh.z_full + i, 1), tc::mbar_init(sh.r_full + i, 4);
+        for (int i = 0; i < 2; ++i) tc::mbar_init(sh.z_full + i, 1), tc::mbar_init(sh.r_full + i, 4);   // r_full[1] unused
         tc::mbar_init(sh.g_full, 1);
+        for (int s = 0; s < kNS; ++s) tc::mbar_init(sh.sdone + s, 1);
+        tc::mbar_init(sh.inv_ready, 2);
         tc::mbar_fence_init();
     }
     if (warp == 0) tc::tmem_alloc(sh.tmem_slot, kTmemCols);
@@ -461,16 +517,24 @@ psb_worker_tc_kernel(const __grid_constant__ CUtensorMap tmX, PsbSolver sv, Comm
         ev.prof[0] = ev.prof[1] = ev.prof[2] = ev.prof[3] = 0;
 #endif
 
-        ev.stats_pass(sv.standardize);
-        const long long t_stats = clock64();
-
         SolveVecs v;
         ws.bind(v);
         v.n4 = n4;
+        // First evaluation with the standardisation statistics fused in (one pass over the buffer
+        // instead of two): at the start point the effective weights are w0 itself.
+        bool have_f0 = false;
+        double f0 = 0.0;
+        if (sv.standardize) {
+            f0 = ev.eval_impl(w0, v.g, true);
+            have_f0 = !s_need_redo;
+        } else {
+            ev.unit_scale();
+        }
+        const long long t_stats = clock64();
         to_scaled_space(v.x, w0, sh.inv, F);
         __syncthreads();
 
-        SolveResult res = local_solve(ev, v, sv.solver, sv.max_iter, sv.sgd_lr, sh.red);
+        SolveResult res = local_solve(ev, v, sv.solver, sv.max_iter, sv.sgd_lr, sh.red, have_f0, f0);
         const long long t_solve = clock64();
 
         float* delta = v.tmp;
@@ -519,7 +583,7 @@ int psb_launch_worker_tc(const PsbSolver* s, const CommCtx& cx, int num_workers,
     }
     auto smem_for = [&](int ns) {
         return 1024 + (size_t)ns * kChunkBytes + (size_t)nkb * kBChunkBytes + 2 * kRBytes + (size_t)F * 4 + 32 * 4 +
-               34 * 8 + (size_t)(2 * ns + 5) * 8 + 64;
+               34 * 8 + (size_t)(3 * ns + 6) * 8 + 64;
     };
     int kNS = 10;
     while (kNS > 2 && smem_for(kNS) > 225 * 1024) kNS -= 2;

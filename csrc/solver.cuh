@@ -138,10 +138,12 @@ __device__ bool strong_wolfe(Eval& ev, SolveVecs& v, double f0, double dd0, doub
 
 // On entry v.x holds the start point.  On exit v.x holds the result.
 template <class Eval>
-__device__ SolveResult local_solve(Eval& ev, SolveVecs& v, int solver, int max_iter, float sgd_lr, double* red) {
+__device__ SolveResult local_solve(Eval& ev, SolveVecs& v, int solver, int max_iter, float sgd_lr, double* red,
+                                   bool have_f0 = false, double f0 = 0.0) {
     SolveResult r;
     r.evals = 0, r.iterations = 0, r.status = 0;
-    double f = ev.eval(v.x, v.g);
+    // have_f0: the caller already evaluated loss (f0) and gradient (in v.g) at the start point v.x
+    double f = have_f0 ? f0 : ev.eval(v.x, v.g);
     r.evals = 1;
     if (solver == PSB_SOLVER_SGD) {
         vec_axpy_to(v.x, v.x, -(double)sgd_lr, v.g, v.n4);
