@@ -116,6 +116,11 @@ int psb_eval(const void* d_X, const int* d_labels, int n, const float* d_w, int 
     return psb_launch_eval_finalize(d_conf, d_out, st);
 }
 
+int psb_eval_finalize(const int* d_conf, float* d_out, void* stream) {
+    PSB_REQUIRE(d_conf && d_out, "psb_eval_finalize: null pointer");
+    return psb_launch_eval_finalize(d_conf, d_out, (cudaStream_t)stream);
+}
+
 int psb_ring_scatter(const uint32_t* d_stage, int n, int stride_words, void* d_X, int* d_labels, int cap,
                      int num_features, void* stream) {
     PSB_REQUIRE(d_stage && d_X && d_labels, "psb_ring_scatter: null pointer");

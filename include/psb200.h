@@ -118,12 +118,38 @@ int psb_worker_step_static(const PsbSolver* s, const PsbComm* comm, int num_work
 int psb_apply_delta(float* d_w, const float* d_delta, float lr, int num_features, int skip_class,
                     void* stream);
 
+/* ---------------------------------------------------------------- sharded sparse path (2^24 features) */
+/* Weights range-partitioned over the ranks (KeyRange, BaseMessage.java:24-27; the reference keeps a
+ * single server partition, ServerApp.java:38).  shard[s]: (rows_per_shard + 1) x 8 floats on rank s,
+ * the intercept row is the extra row of shard 0.  phase[q]: num_ranks counters on rank q. */
+typedef struct PsbSparseComm {
+    void* shard[PSB_MAX_RANKS];
+    void* phase[PSB_MAX_RANKS];
+    void* ticket;                  /* one zeroed uint32 on this rank */
+    void* status;                  /* one uint32 error flag on this rank */
+    int rank, num_ranks, rows_per_shard;
+    unsigned long long spin_limit;
+} PsbSparseComm;
+/* One SGD step of a worker on a CSR batch.  mode bit 0 = forward (pull fused into the GEMV operand loads,
+ * residuals -> d_residuals when given), bit 1 = scatter (push + apply fused: w += scale * v * r over P2P).
+ * wait_phase / publish_phase (0 = none): device-side barrier over peer memory for sequential consistency.
+ * scale = -eta / (batch * numWorkers).  d_loss: one float, the batch's summed loss is ADDED to it. */
+int psb_sparse_step(const PsbSparseComm* comm, int mode, unsigned int wait_phase, unsigned int publish_phase,
+                    const long long* d_indptr, const int* d_indices, const float* d_values, const int* d_labels,
+                    int batch, int num_features, int num_class_rows, float scale, float* d_residuals, float* d_loss,
+                    void* stream);
+int psb_sparse_eval(const PsbSparseComm* comm, const long long* d_indptr, const int* d_indices, const float* d_values,
+                    const int* d_labels, int n, int num_features, int num_class_rows, int* d_conf, void* stream);
+
 /* ---------------------------------------------------------------- evaluation */
 /* argmax(X W + b) -> confusion matrix -> weighted F1, accuracy (Metrics.java:15-24).
  *   d_X fp16 dense [n][F]; d_conf: int[64] scratch (8x8, zeroed by the call);
  *   d_out: float[2] = {f1, accuracy}.  impl as above.                                     */
 int psb_eval(const void* d_X, const int* d_labels, int n, const float* d_w, int num_features,
              int num_class_rows, int* d_conf, float* d_out, int impl, void* stream);
+
+/* weighted F1 + accuracy from an 8x8 confusion matrix (shared by the dense and the sparse evaluation) */
+int psb_eval_finalize(const int* d_conf, float* d_out, void* stream);
 
 /* ---------------------------------------------------------------- ingestion */
 /* Scatter a staged batch of sparse rows into the dense fp16 ring slots (K1).

@@ -1,0 +1,184 @@
+"""Sharded sparse engine (BASELINE config 5): 2^24 hashed features, server shards across the GPUs.
+
+The dense engine replicates the 6150-parameter model on every GPU; here the model (F x 8 fp32, 512 MiB
+at F = 2^24) is range-partitioned — rank s owns rows [s*Fs, (s+1)*Fs) — which is the key-range sharding
+the reference designs for (``KeyRange`` in every message, ``BaseMessage.java:24-27``) but never turns on
+(``ServerApp.java:38``, ``README.md:115-119``, future work ``README.md:333``).  A worker step is one SGD
+step on a CSR batch (``psb_sparse_step``): the pull is the forward's operand loads from the owning shards,
+the push is a 16-byte RED into them.  Sequential consistency separates readers from writers with a
+device-side phase barrier over peer memory; eventual consistency fuses both into one kernel.
+"""
+from __future__ import annotations
+
+from typing import List, Optional
+
+import numpy as np
+import torch
+
+from ..data.csr import CSRBatch
+from ..ops import native
+from .device_engine import _view
+
+
+class DeviceCSR:
+    def __init__(self, batch: CSRBatch, device):
+        self.indptr = torch.from_numpy(batch.indptr.astype(np.int64)).to(device)
+        self.indices = torch.from_numpy(batch.indices.astype(np.int32)).to(device)
+        self.values = torch.from_numpy(batch.values.astype(np.float32)).to(device)
+        self.labels = torch.from_numpy(batch.labels.astype(np.int32)).to(device)
+        self.n, self.nnz = len(batch), batch.nnz
+
+
+class SparseShardedEngine:
+    def __init__(self, num_features: int, num_classes: int = 5, rank: int = 0, world: int = 1,
+                 num_workers_total: Optional[int] = None, eta: float = 0.5, consistency_model: int = 0,
+                 device: Optional[torch.device] = None, spin_limit_cycles: int = 20_000_000_000):
+        if not torch.cuda.is_available():
+            raise native.NativeError("SparseShardedEngine needs a CUDA device")
+        native.lib()
+        self.F, self.R = num_features, num_classes + 1
+        self.rank, self.world = rank, world
+        self.num_workers = num_workers_total or world
+        self.eta, self.model = eta, consistency_model
+        if consistency_model > 0:
+            raise ValueError("the sharded sparse path implements sequential (0) and eventual (-1) consistency")
+        self.device = device or torch.device("cuda", torch.cuda.current_device())
+        self.Fs = (num_features + world - 1) // world
+        self.shard_bytes = (self.Fs + 1) * 32
+        self.shard = native.device_malloc(self.shard_bytes)
+        self.ctrl = native.device_malloc(512)                    # [0..32) phases, [32] ticket, [33] status
+        _view(self.shard, (self.Fs + 1) * 8, self.device).zero_()
+        _view(self.ctrl, 128, self.device, torch.int32).zero_()
+        self.shards: List[int] = [0] * world
+        self.ctrls: List[int] = [0] * world
+        self.shards[rank], self.ctrls[rank] = self.shard, self.ctrl
+        self.loss = torch.zeros(1, dtype=torch.float32, device=self.device)
+        self.residuals: Optional[torch.Tensor] = None
+        self.conf = torch.zeros(64, dtype=torch.int32, device=self.device)
+        self.mout = torch.zeros(2, dtype=torch.float32, device=self.device)
+        self.step_index = 0
+        self.spin_limit = spin_limit_cycles
+        self.kernel_launches = 0
+        self._imported = False
+        torch.cuda.synchronize(self.device)
+
+    # -- transport ------------------------------------------------------------
+    def connect(self) -> None:
+        import torch.distributed as dist
+        if self.world == 1:
+            return
+        mine = (native.ipc_export(self.shard), native.ipc_export(self.ctrl))
+        handles = [None] * self.world
+        dist.all_gather_object(handles, mine)
+        for q in range(self.world):
+            if q != self.rank:
+                self.shards[q] = native.ipc_import(handles[q][0])
+                self.ctrls[q] = native.ipc_import(handles[q][1])
+        self._imported = True
+        dist.barrier()
+
+    def set_peers(self, shards: List[int], ctrls: List[int]) -> None:
+        self.shards, self.ctrls = list(shards), list(ctrls)
+
+    def _comm(self) -> native.PsbSparseComm:
+        c = native.PsbSparseComm()
+        for q in range(self.world):
+            c.shard[q] = self.shards[q]
+            c.phase[q] = self.ctrls[q]
+        c.ticket, c.status = self.ctrl + 128, self.ctrl + 132
+        c.rank, c.num_ranks, c.rows_per_shard, c.spin_limit = self.rank, self.world, self.Fs, self.spin_limit
+        return c
+
+    # -- the step ---------------------------------------------------------------
+    def _launch(self, mode: int, wait: int, publish: int, batch: DeviceCSR) -> None:
+        if self.residuals is None or self.residuals.shape[0] < batch.n:
+            self.residuals = torch.zeros((batch.n, 8), dtype=torch.float32, device=self.device)
+        scale = -self.eta / (batch.n * self.num_workers)
+        comm = self._comm()
+        native.check(native.lib().psb_sparse_step(
+            native.C.byref(comm), mode, wait, publish, batch.indptr.data_ptr(), batch.indices.data_ptr(),
+            batch.values.data_ptr(), batch.labels.data_ptr(), batch.n, self.F, self.R, scale,
+            self.residuals.data_ptr(), self.loss.data_ptr(), native._stream()), "psb_sparse_step")
+        self.kernel_launches += 1
+
+    def step_forward(self, batch: DeviceCSR) -> None:
+        self.loss.zero_()
+        k = self.step_index
+        self._launch(1, 2 * k if (self.world > 1 and k > 0) else 0, 2 * k + 1 if self.world > 1 else 0, batch)
+
+    def step_scatter(self, batch: DeviceCSR) -> None:
+        k = self.step_index
+        self._launch(2, 2 * k + 1 if self.world > 1 else 0, 2 * k + 2 if self.world > 1 else 0, batch)
+        self.step_index += 1
+
+    def step(self, batch: DeviceCSR) -> None:
+        """One worker SGD step.  Sequential: forward | barrier | scatter | barrier.  Eventual: one kernel."""
+        if self.model == 0:
+            self.step_forward(batch)
+            self.step_scatter(batch)
+        else:
+            self.loss.zero_()
+            self._launch(3, 0, 0, batch)
+            self.step_index += 1
+
+    def mean_loss(self, batch: DeviceCSR) -> float:
+        return float(self.loss.item()) / batch.n
+
+    def evaluate(self, test: DeviceCSR):
+        comm = self._comm()
+        native.check(native.lib().psb_sparse_eval(native.C.byref(comm), test.indptr.data_ptr(), test.indices.data_ptr(),
+                                                  test.values.data_ptr(), test.labels.data_ptr(), test.n, self.F, self.R,
+                                                  self.conf.data_ptr(), native._stream()), "psb_sparse_eval")
+        native.check(native.lib().psb_eval_finalize(self.conf.data_ptr(), self.mout.data_ptr(), native._stream()),
+                     "psb_eval_finalize")
+        f1, acc = self.mout.cpu().tolist()
+        return f1, acc
+
+    def shard_weights(self) -> torch.Tensor:
+        return _view(self.shard, (self.Fs + 1) * 8, self.device).view(self.Fs + 1, 8)
+
+    def status(self) -> int:
+        return int(_view(self.ctrl + 132, 1, self.device, torch.int32).item())
+
+    def close(self) -> None:
+        if self.shard:
+            torch.cuda.synchronize(self.device)
+            if self._imported:
+                for q in range(self.world):
+                    if q != self.rank:
+                        native.lib().psb_ipc_close(self.shards[q])
+                        native.lib().psb_ipc_close(self.ctrls[q])
+            native.device_free(self.shard)
+            native.device_free(self.ctrl)
+            self.shard = 0
+
+
+class VirtualSparseCluster:
+    """N shards on ONE device (tests): forwards of all ranks, then scatters of all ranks, in launch order."""
+
+    def __init__(self, num_features: int, num_ranks: int, consistency_model: int = 0, eta: float = 0.5):
+        self.engines = [SparseShardedEngine(num_features, 5, r, num_ranks, num_ranks, eta, consistency_model)
+                        for r in range(num_ranks)]
+        shards = [e.shard for e in self.engines]
+        ctrls = [e.ctrl for e in self.engines]
+        for e in self.engines:
+            e.set_peers(shards, ctrls)
+
+    def step(self, batches) -> None:
+        if self.engines[0].model == 0:
+            for e, b in zip(self.engines, batches):
+                e.step_forward(b)
+            for e, b in zip(self.engines, batches):
+                e.step_scatter(b)
+        else:
+            for e, b in zip(self.engines, batches):
+                e.step(b)
+
+    def weights(self) -> np.ndarray:
+        F = self.engines[0].F
+        rows = [e.shard_weights()[: e.Fs].cpu().numpy() for e in self.engines]
+        return np.concatenate(rows)[:F], self.engines[0].shard_weights()[self.engines[0].Fs].cpu().numpy()
+
+    def close(self) -> None:
+        for e in self.engines:
+            e.close()

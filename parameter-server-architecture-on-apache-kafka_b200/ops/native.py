@@ -35,6 +35,12 @@ class PsbSolver(C.Structure):
                 ("max_iter", C.c_int), ("standardize", C.c_int), ("center", C.c_int), ("sgd_lr", C.c_float)]
 
 
+class PsbSparseComm(C.Structure):
+    _fields_ = [("shard", C.c_void_p * MAX_RANKS), ("phase", C.c_void_p * MAX_RANKS), ("ticket", C.c_void_p),
+                ("status", C.c_void_p), ("rank", C.c_int), ("num_ranks", C.c_int), ("rows_per_shard", C.c_int),
+                ("spin_limit", C.c_ulonglong)]
+
+
 class PsbComm(C.Structure):
     _fields_ = [("mode", C.c_int), ("rank", C.c_int), ("num_ranks", C.c_int), ("workers_per_rank", C.c_int),
                 ("clock", C.c_int), ("max_delay", C.c_int), ("lr", C.c_float), ("spin_limit", C.c_ulonglong),
@@ -73,6 +79,10 @@ def lib() -> C.CDLL:
                                   ip, fp, vp]
     L.psb_apply_delta.argtypes = [fp, fp, C.c_float, C.c_int, C.c_int, vp]
     L.psb_eval.argtypes = [vp, ip, C.c_int, fp, C.c_int, C.c_int, ip, fp, C.c_int, vp]
+    L.psb_eval_finalize.argtypes = [ip, fp, vp]
+    L.psb_sparse_step.argtypes = [C.POINTER(PsbSparseComm), C.c_int, C.c_uint, C.c_uint, vp, vp, vp, vp, C.c_int, C.c_int,
+                                  C.c_int, C.c_float, vp, vp, vp]
+    L.psb_sparse_eval.argtypes = [C.POINTER(PsbSparseComm), vp, vp, vp, vp, C.c_int, C.c_int, C.c_int, vp, vp]
     L.psb_ring_scatter.argtypes = [vp, C.c_int, C.c_int, vp, ip, C.c_int, C.c_int, vp]
     L.psb_ring_store_dense.argtypes = [vp, C.c_int, ip, ip, C.c_int, vp, ip, C.c_int, C.c_int, vp]
     L.psb_malloc.argtypes = [C.POINTER(C.c_void_p), C.c_size_t]
