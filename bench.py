@@ -42,6 +42,8 @@ def parse():
     p.add_argument("--consistency_model", type=int, default=0)
     p.add_argument("--ingest_rows", type=int, default=128, help="new rows per worker per step in the e2e run")
     p.add_argument("--no_e2e", action="store_true")
+    p.add_argument("--events_per_min", type=float, default=0.0,
+                   help="e2e run: per-worker arrival rate used for the dynamic buffer size bc x events/min (0: unthrottled -> max)")
     p.add_argument("--transport", default="p2p", choices=["p2p", "nccl"],
                    help="p2p: fused peer-memory push/apply/pull (product); nccl: all_reduce baseline")
     return p.parse_args()
@@ -205,10 +207,17 @@ def main():
         host_rows = [(r / r.norm(dim=1, keepdim=True).clamp_min(1e-6)).half().pin_memory() for r in host_rows]
         host_lab = [torch.randint(1, 6, (n_new,), generator=g, dtype=torch.int32).pin_memory() for _ in range(pool)]
         workers = np.repeat(np.arange(W, dtype=np.int32), a.ingest_rows)
-        now = np.zeros(n_new)
+        # arrival timestamps drive the dynamic buffer size: target = clamp(bc * events_per_minute, min, max)
+        gap_ms = 60000.0 / a.events_per_min if a.events_per_min > 0 else 0.0
+        tick = [0]
+
+        def stamps():
+            base = tick[0] * a.ingest_rows * gap_ms
+            tick[0] += 1
+            return base + np.tile(np.arange(a.ingest_rows) * gap_ms, W)
 
         def one(i):
-            eng.ingest(host_rows[i % pool], host_lab[i % pool], workers, now, wait=True)   # H2D + scatter
+            eng.ingest(host_rows[i % pool], host_lab[i % pool], workers, stamps(), wait=True)   # H2D + scatter
             eng.step()
             return eng.read_loss()                                                        # D2H of the result
 
@@ -227,7 +236,9 @@ def main():
         wall = (time.perf_counter() - wall0) * 1000.0
         barrier()
         ems = max_over_ranks(max(t0.elapsed_time(t1), wall))
-        e2e = {"value": samples / (ems / 1000.0), "unit": "samples/sec",
+        rows_eff = float(eng.win_host[:, 1].float().mean())            # dynamic buffer size actually trained on
+        e2e = {"value": W * world * rows_eff * a.steps / (ems / 1000.0), "unit": "samples/sec",
+               "buffer_rows_effective": rows_eff, "events_per_min_per_worker": a.events_per_min,
                "h2d_bytes_per_step": (eng.h2d_bytes - h0) // a.steps, "d2h_bytes_per_step": W * 4,
                "ms_per_step": ems / a.steps, "ingested_samples_per_sec": n_new * world * a.steps / (ems / 1000.0),
                "new_rows_per_worker_per_step": a.ingest_rows}
