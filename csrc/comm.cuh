@@ -93,14 +93,11 @@ __device__ __forceinline__ void comm_push(const CommCtx& cx, const float4* delta
 
     if (c.mode == PSB_COMM_SEQUENTIAL) {
         // 2. mailbox stores: my GPU's sum, cut into shards, into each owner's inbox[p][rank]
-        for (int s = 0; s < c.num_ranks; ++s) {
-            CommBlock owner(c.peers[s], L);
-            const int b = L.slice_begin(s), e = L.slice_end(s);
-            float4* box = owner.inbox(p, c.rank);
-            for (int i = b + threadIdx.x; i < e; i += blockDim.x) {
-                st_cg_v4(box + (i - b), ld_cg_v4(acc + i));
-                st_cg_v4(acc + i, make_float4(0.f, 0.f, 0.f, 0.f));      // ready for clock v+2
-            }
+        for (int i = threadIdx.x; i < L.n4; i += blockDim.x) {
+            const int s = i / L.slice4;
+            float4* box = CommBlock(c.peers[s], L).inbox(p, c.rank);
+            st_cg_v4(box + (i - s * L.slice4), ld_cg_v4(acc + i));
+            st_cg_v4(acc + i, make_float4(0.f, 0.f, 0.f, 0.f));          // ready for clock v+2
         }
         if (threadIdx.x == 0) *me.ticket(p) = 0u;
         fence_acq_rel_sys();
@@ -115,32 +112,37 @@ __device__ __forceinline__ void comm_push(const CommCtx& cx, const float4* delta
         unsigned mask = s_apply_mask;
         if (!mask) return;
         fence_acq_rel_sys();
-        // 4. apply the shards whose last arrival we saw, broadcast into everyone's next replica
+        // 4. apply the shards whose last arrival we saw, broadcast into everyone's next replica.
+        //    One flat loop over all parameters so that every thread has its N remote inbox loads of several
+        //    elements in flight at once (one NVLink round trip for the whole apply, not one per shard).
         const float4* w_old = me.rep(p);
-        for (int s = 0; s < c.num_ranks; ++s) {
+        for (int i = threadIdx.x; i < L.n4; i += blockDim.x) {
+            const int s = i / L.slice4;
             if (!(mask & (1u << s))) continue;
             CommBlock owner(c.peers[s], L);
-            const int b = L.slice_begin(s), e = L.slice_end(s);
-            for (int i = b + threadIdx.x; i < e; i += blockDim.x) {
-                float4 sum = make_float4(0.f, 0.f, 0.f, 0.f);
-                for (int q = 0; q < c.num_ranks; ++q) {
-                    const float4 g = ld_relaxed_sys_v4(owner.inbox(p, q) + (i - b));
-                    sum.x += g.x, sum.y += g.y, sum.z += g.z, sum.w += g.w;
-                }
-                const float4 w = ld_cg_v4(w_old + i);
-                const float4 nw = make_float4(fmaf(c.lr, sum.x, w.x), fmaf(c.lr, sum.y, w.y), fmaf(c.lr, sum.z, w.z),
-                                              fmaf(c.lr, sum.w, w.w));
-                for (int q = 0; q < c.num_ranks; ++q) st_cg_v4(CommBlock(c.peers[q], L).rep(p ^ 1) + i, nw);
-            }
+            const int off = i - s * L.slice4;
+            float4 g[PSB_MAX_RANKS];
+#pragma unroll
+            for (int q = 0; q < PSB_MAX_RANKS; ++q)
+                g[q] = q < c.num_ranks ? ld_relaxed_sys_v4(owner.inbox(p, q) + off) : make_float4(0.f, 0.f, 0.f, 0.f);
+            float4 sum = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+            for (int q = 0; q < PSB_MAX_RANKS; ++q) sum.x += g[q].x, sum.y += g[q].y, sum.z += g[q].z, sum.w += g[q].w;
+            const float4 w = ld_cg_v4(w_old + i);
+            const float4 nw = make_float4(fmaf(c.lr, sum.x, w.x), fmaf(c.lr, sum.y, w.y), fmaf(c.lr, sum.z, w.z),
+                                          fmaf(c.lr, sum.w, w.w));
+#pragma unroll
+            for (int q = 0; q < PSB_MAX_RANKS; ++q)
+                if (q < c.num_ranks) st_cg_v4(CommBlock(c.peers[q], L).rep(p ^ 1) + i, nw);
         }
         fence_acq_rel_sys();
         __syncthreads();
         if (threadIdx.x < c.num_ranks && (mask & (1u << threadIdx.x))) {
             const int s = threadIdx.x;
-            *CommBlock(c.peers[s], L).arrivals(p) = 0u;
-            fence_acq_rel_sys();
+            st_relaxed_sys(CommBlock(c.peers[s], L).arrivals(p), 0u);
+            fence_acq_rel_sys();                 // one release fence, then N independent flag stores in flight
             for (int q = 0; q < c.num_ranks; ++q)
-                st_release_sys(CommBlock(c.peers[q], L).version() + s, (unsigned)c.clock + 1u);
+                st_relaxed_sys(CommBlock(c.peers[q], L).version() + s, (unsigned)c.clock + 1u);
         }
     } else {
         // async: apply == reduction, straight into the owners' authoritative shards
