@@ -216,11 +216,16 @@ def main():
             tick[0] += 1
             return base + np.tile(np.arange(a.ingest_rows) * gap_ms, W)
 
+        # Software pipeline through the public API: the host->device copy of batch i+1 (ingest_begin) is in
+        # flight while step i trains; ingest_commit scatters it into the rings between two steps.  Every step
+        # still pays its own H2D (pinned host -> device) and its own D2H read of the losses.
         def one(i):
-            eng.ingest(host_rows[i % pool], host_lab[i % pool], workers, stamps(), wait=True)   # H2D + scatter
+            eng.ingest_commit()                                                            # batch i -> rings
+            eng.ingest_begin(host_rows[(i + 1) % pool], host_lab[(i + 1) % pool], workers, stamps())   # H2D of i+1
             eng.step()
             return eng.read_loss()                                                        # D2H of the result
 
+        eng.ingest_begin(host_rows[0], host_lab[0], workers, stamps())
         for i in range(a.warmup):
             one(i)
         barrier()

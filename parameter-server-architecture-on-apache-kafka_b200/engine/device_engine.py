@@ -78,9 +78,14 @@ class DeviceEngine:
         self.stage_host = torch.zeros((self.stage_rows, F), dtype=torch.float16).pin_memory()
         self.stage_lab_host = torch.zeros(self.stage_rows, dtype=torch.int32).pin_memory()
         self.stage_ws_host = torch.zeros((self.stage_rows, 2), dtype=torch.int32).pin_memory()
-        self.stage_dev = torch.zeros((self.stage_rows, F), dtype=torch.float16, device=dev)
-        self.stage_lab_dev = torch.zeros(self.stage_rows, dtype=torch.int32, device=dev)
-        self.stage_ws_dev = torch.zeros((self.stage_rows, 2), dtype=torch.int32, device=dev)
+        # two device staging sets: the H2D of batch k+1 overlaps the step that trains on batch k
+        self.stage_dev = [torch.zeros((self.stage_rows, F), dtype=torch.float16, device=dev) for _ in range(2)]
+        self.stage_lab_dev = [torch.zeros(self.stage_rows, dtype=torch.int32, device=dev) for _ in range(2)]
+        self.stage_ws_dev = [torch.zeros((self.stage_rows, 2), dtype=torch.int32, device=dev) for _ in range(2)]
+        self.stage_win_dev = [torch.zeros((self.W, 2), dtype=torch.int32, device=dev) for _ in range(2)]
+        self.stage_n = [0, 0]
+        self.stage_slot = 0
+        self.h2d_done = [torch.cuda.Event(), torch.cuda.Event()]
         self.ingest_stream = torch.cuda.Stream(device=dev)
         self.ingest_done = torch.cuda.Event()
         self.h2d_bytes = 0
@@ -154,6 +159,7 @@ class DeviceEngine:
         assert n <= self.stage_rows, "ingest batch larger than the staging ring"
         if now_ms is None:
             now_ms = np.zeros(n, dtype=np.float64)
+        self._tables_free()
         native.buffers_on_batch(self.buffers, workers[:n], now_ms[:n], self.stage_ws_host.numpy(),
                                 self.win_host.numpy())
         for w, c in zip(*np.unique(np.asarray(workers[:n]), return_counts=True)):
@@ -164,24 +170,64 @@ class DeviceEngine:
                      win: torch.Tensor, wait: bool = True) -> None:
         """Same as ingest() with the (worker, slot) table and the new windows precomputed (bench hot path)."""
         n = rows_f16.shape[0]
+        self._tables_free()
         self.stage_ws_host[:n].copy_(worker_slot)
         self.win_host.copy_(win)
         self._ingest_staged(rows_f16, labels, n, wait)
 
+    def _tables_free(self) -> None:
+        """The pinned (worker, slot) and window tables are shared by both staging sets: wait until the copies
+        that read them have completed before the host rewrites them."""
+        self.h2d_done[0].synchronize()
+        self.h2d_done[1].synchronize()
+
     def _ingest_staged(self, rows_f16, labels, n, wait) -> None:
+        self._h2d(rows_f16, labels, n)
+        self.ingest_commit(wait)
+
+    def _h2d(self, rows_f16, labels, n) -> int:
+        """Async copies of one batch (rows, labels, slot table, new windows) into a free staging set."""
+        j = self.stage_slot
         s = self.ingest_stream
-        s.wait_stream(torch.cuda.current_stream())          # the previous step must be done with the ring
         with torch.cuda.stream(s):
-            self.stage_dev[:n].copy_(rows_f16[:n], non_blocking=True)
-            self.stage_lab_dev[:n].copy_(labels[:n], non_blocking=True)
-            self.stage_ws_dev[:n].copy_(self.stage_ws_host[:n], non_blocking=True)
-            self.win.copy_(self.win_host, non_blocking=True)
-            native.ring_store_dense(self.stage_dev, self.stage_lab_dev, self.stage_ws_dev, n, self.X, self.labels,
-                                    self.cap, self.F, stream=s)
-            self.ingest_done.record(s)
-        self.kernel_launches += 1
+            self.stage_dev[j][:n].copy_(rows_f16[:n], non_blocking=True)
+            self.stage_lab_dev[j][:n].copy_(labels[:n], non_blocking=True)
+            self.stage_ws_dev[j][:n].copy_(self.stage_ws_host[:n], non_blocking=True)
+            self.stage_win_dev[j].copy_(self.win_host, non_blocking=True)
+            self.h2d_done[j].record(s)
+        self.stage_n[j] = n
         self.rows_ingested += n
         self.h2d_bytes += n * self.F * 2 + n * 4 + n * 8 + self.W * 8
+        return j
+
+    def ingest_begin(self, rows_f16: torch.Tensor, labels: torch.Tensor, workers: np.ndarray,
+                     now_ms: Optional[np.ndarray] = None) -> None:
+        """First half of ingest(): slot assignment + host->device copies into the staging area.  Does not
+        touch the rings, so it may run while a step is training on them (pipelined ingestion)."""
+        n = rows_f16.shape[0]
+        assert n <= self.stage_rows, "ingest batch larger than the staging ring"
+        if now_ms is None:
+            now_ms = np.zeros(n, dtype=np.float64)
+        self._tables_free()
+        native.buffers_on_batch(self.buffers, workers[:n], now_ms[:n], self.stage_ws_host.numpy(),
+                                self.win_host.numpy())
+        for w, c in zip(*np.unique(np.asarray(workers[:n]), return_counts=True)):
+            self.buffers[int(w)].total += int(c)
+        self._h2d(rows_f16, labels, n)
+
+    def ingest_commit(self, wait: bool = True) -> None:
+        """Second half: scatter the staged batch into the rings (after the running step, before the next)."""
+        j = self.stage_slot
+        n = self.stage_n[j]
+        s = self.ingest_stream
+        s.wait_stream(torch.cuda.current_stream())          # the previous step must be done with the rings
+        with torch.cuda.stream(s):
+            self.win.copy_(self.stage_win_dev[j], non_blocking=True)
+            native.ring_store_dense(self.stage_dev[j], self.stage_lab_dev[j], self.stage_ws_dev[j], n, self.X,
+                                    self.labels, self.cap, self.F, stream=s)
+            self.ingest_done.record(s)
+        self.kernel_launches += 1
+        self.stage_slot ^= 1
         if wait:
             torch.cuda.current_stream().wait_event(self.ingest_done)
 

@@ -1,0 +1,39 @@
+"""ncu target covering every hot kernel once: tcgen05 worker step (296 workers), SIMT worker step, tcgen05 and
+SIMT evaluation, ring ingestion, sharded sparse step + eval.  Usage: python tools/profile_all.py"""
+import os
+import sys
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import numpy as np
+import torch
+
+from bench import synth_buffers
+from psb200.config import PSConfig
+from psb200.engine.device_engine import DeviceEngine
+from psb200.engine.sparse_engine import SparseShardedEngine
+from psb200.ops import native
+from tools.bench_sparse import Batch
+
+dev = torch.device("cuda", 0)
+cap, F = 1024, 1024
+for W, impl in ((296, native.IMPL_TC), (148, native.IMPL_SIMT)):
+    X, y = synth_buffers(torch, W, cap, F, 0.45, 1, dev)
+    eng = DeviceEngine(PSConfig(num_workers=W, max_buffer_size=cap), W, impl=impl, stage_rows=W * 128)
+    eng.fill(X, y)
+    eng.test_X, eng.test_y = X[:5].reshape(-1, F)[:4877].contiguous(), y[:5].reshape(-1)[:4877].contiguous()
+    rows = X[0, :128].repeat(W, 1).cpu().pin_memory()
+    labs = y[0, :128].repeat(W).cpu().pin_memory()
+    workers = np.repeat(np.arange(W, dtype=np.int32), 128)
+    for _ in range(3):
+        eng.ingest(rows, labs, workers, np.zeros(W * 128))
+        eng.step()
+        eng.evaluate()
+    print("dense impl", impl, "W", W, "loss", float(eng.read_loss().mean()), "status", eng.status())
+    eng.close()
+    del X, y
+sp = SparseShardedEngine(1 << 24, 5, 0, 1, 1, 0.5, -1, dev)
+b = Batch(16384, 1 << 24, 128, 3, dev)
+for _ in range(3):
+    sp.step(b)
+print("sparse loss", sp.mean_loss(b), "f1/acc", sp.evaluate(b))
+sp.close()
