@@ -220,6 +220,7 @@ class DeviceEngine:
         j = self.stage_slot
         n = self.stage_n[j]
         s = self.ingest_stream
+        torch.cuda.nvtx.range_push("psb.ingest_commit")
         s.wait_stream(torch.cuda.current_stream())          # the previous step must be done with the rings
         with torch.cuda.stream(s):
             self.win.copy_(self.stage_win_dev[j], non_blocking=True)
@@ -230,9 +231,18 @@ class DeviceEngine:
         self.stage_slot ^= 1
         if wait:
             torch.cuda.current_stream().wait_event(self.ingest_done)
+        torch.cuda.nvtx.range_pop()
 
     # ------------------------------------------------------------------ the step
     def step(self, mode: Optional[int] = None) -> None:
+        """Enqueue one parameter-server clock (one kernel).  NVTX range 'psb.step' for timeline tools."""
+        torch.cuda.nvtx.range_push("psb.step")
+        try:
+            self._step(mode)
+        finally:
+            torch.cuda.nvtx.range_pop()
+
+    def _step(self, mode: Optional[int] = None) -> None:
         mode = self.comm_mode if mode is None else mode
         comm = self._comm(mode)
         native.worker_step(self.solver, comm, self.W, self.impl, self.X, self.labels, self.win,
@@ -275,11 +285,13 @@ class DeviceEngine:
     def evaluate(self, weights: Optional[torch.Tensor] = None, impl: Optional[int] = None):
         """Weighted F1 / accuracy of the weights on the loaded test set (device finalise, 8-byte D2H)."""
         w = self.weights() if weights is None else weights
+        torch.cuda.nvtx.range_push("psb.eval")
         native.evaluate(self.test_X, self.test_y, self.test_X.shape[0], w, self.F, self.layout.R, self.conf,
                         self.metrics_dev, self.impl if impl is None else impl)
         self.kernel_launches += 2
         self.metrics_host.copy_(self.metrics_dev, non_blocking=True)
         torch.cuda.current_stream().synchronize()
+        torch.cuda.nvtx.range_pop()
         return float(self.metrics_host[0]), float(self.metrics_host[1])
 
     def close(self) -> None:
