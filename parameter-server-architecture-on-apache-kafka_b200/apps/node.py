@@ -42,6 +42,8 @@ def build_parser():
 
 def main(argv: Optional[List[str]] = None) -> int:
     ns = cli.parse(build_parser(), argv)
+    from ..utils.logging_config import configure
+    configure()
     import torch
     import torch.distributed as dist
     from ..engine.device_engine import DeviceEngine
@@ -172,7 +174,10 @@ def main(argv: Optional[List[str]] = None) -> int:
             if worker_log is not None:
                 seen = [b.ring_total() for b in eng.buffers]
                 for j in range(W):
-                    worker_log.println(worker_row(ts, rank * W + j, clock, float(loss[j]), -1.0, -1.0, seen[j]))
+                    f1w, accw = (-1.0, -1.0)
+                    if ns.worker_metrics:                   # the reference scores every local fit on the test set
+                        f1w, accw = eng.evaluate(eng.worker_local_weights(j))
+                    worker_log.println(worker_row(ts, rank * W + j, clock, float(loss[j]), f1w, accw, seen[j]))
             if rank == 0 and clock % max(1, cfg.eval_every) == 0:
                 f1, acc = eng.evaluate()
                 server_log.println(server_row(int(time.time() * 1000), clock, f1, acc))

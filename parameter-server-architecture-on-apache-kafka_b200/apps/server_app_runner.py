@@ -19,6 +19,8 @@ from .server_app import ServerApp
 
 def main(argv: Optional[List[str]] = None) -> int:
     ns = cli.parse(cli.server_parser(), argv)
+    from ..utils.logging_config import configure
+    configure()
     cfg = cli.config_from_args(ns, "server")
     broker = ns.rendezvous or (RENDEZVOUS_REMOTE if cfg.remote else RENDEZVOUS_LOCAL)
     if cfg.verbose:

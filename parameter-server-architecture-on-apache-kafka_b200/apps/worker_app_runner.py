@@ -19,6 +19,8 @@ from .worker_app import WorkerApp
 
 def main(argv: Optional[List[str]] = None) -> int:
     ns = cli.parse(cli.worker_parser(), argv)
+    from ..utils.logging_config import configure
+    configure()
     cfg = cli.config_from_args(ns, "worker")
     broker = ns.rendezvous or (RENDEZVOUS_REMOTE if cfg.remote else RENDEZVOUS_LOCAL)
     if cfg.verbose:

@@ -269,6 +269,14 @@ class DeviceEngine:
         ptr = L.psb_comm_shard_weights(self.block, self.F, self.world)
         return _view(ptr, self.nv, self.device).view(self.layout.device_rows, 8)
 
+    def worker_local_weights(self, j: int) -> torch.Tensor:
+        """Weights of worker j's locally fitted model of the LAST step (pulled weights + its delta) — what the
+        reference evaluates for the worker log row (LogisticRegressionTaskSpark.java:186).  Sequential mode."""
+        nv = self.nv
+        delta = self.scratch[j, 5 * nv: 6 * nv]              # solver scratch vector 5 = delta (csrc/worker_common.cuh)
+        w0 = self.scratch[j, 6 * nv: 7 * nv]                 # vector 6 = the weights this step started from
+        return (w0 + delta).view(self.layout.device_rows, 8)
+
     def reset_clock_words(self, clock: int) -> None:
         """After a resume: every version / clock word of this rank's block restarts at `clock`."""
         words = torch.full((2 * 32,), int(clock), dtype=torch.int32, device=self.device)

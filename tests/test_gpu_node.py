@@ -57,3 +57,23 @@ def test_node_streams_a_csv_file_through_the_producer_thread(tmp_path):
     wrows = parse_log(str(tmp_path / "logs-worker.csv"), "worker")
     assert len(srows) >= 2 and wrows[:, 6].max() == 750          # each of the 2 workers saw half of the 1500 rows
     assert srows[-1, 4] > srows[0, 4] - 0.05
+
+
+def test_worker_metrics_and_dynamic_buffer(tmp_path):
+    """--worker_metrics fills the worker rows' F1/accuracy; arrival timestamps size the device buffer."""
+    r = _node(tmp_path, "--max_clock", "3", "--worker_metrics")
+    assert r.returncode == 0, r.stderr[-3000:]
+    w = parse_log(str(tmp_path / "logs-worker.csv"), "worker")
+    assert np.all((w[:, 4] >= 0) & (w[:, 4] <= 1)) and np.all((w[:, 5] >= 0) & (w[:, 5] <= 1))
+    from psb200.config import PSConfig
+    from psb200.engine.device_engine import DeviceEngine
+    eng = DeviceEngine(PSConfig(num_workers=2, max_buffer_size=1024, min_buffer_size=128), 2, impl=0, stage_rows=4096)
+    rows = torch.zeros((2000, 1024), dtype=torch.float16).pin_memory()
+    labs = torch.ones(2000, dtype=torch.int32).pin_memory()
+    workers = (np.arange(2000) % 2).astype(np.int32)
+    eng.ingest(rows, labs, workers, np.arange(2000) // 2 * 30.0)        # 2000 events/min per worker -> 0.3*2000 = 600
+    torch.cuda.synchronize()
+    assert eng.win_host[:, 1].tolist() == [600, 600] and eng.win.cpu()[:, 1].tolist() == [600, 600]
+    eng.ingest(rows[:400], labs[:400], workers[:400], 30000.0 + np.arange(400) // 2 * 1000.0)   # 60/min -> shrinks
+    assert all(128 <= c < 600 for c in eng.win_host[:, 1].tolist())
+    eng.close()
