@@ -141,6 +141,26 @@ int psb_sparse_step(const PsbSparseComm* comm, int mode, unsigned int wait_phase
 int psb_sparse_eval(const PsbSparseComm* comm, const long long* d_indptr, const int* d_indices, const float* d_values,
                     const int* d_labels, int n, int num_features, int num_class_rows, int* d_conf, void* stream);
 
+/* Slab exchange variant of the sharded step: every NVLink transfer is a contiguous slab (request lists,
+ * reply rows = the pull, update rows = the push) instead of one small request per non-zero.
+ * req[s]: int[2][N][cap] on rank s; req_cnt[s]: uint[2][N] on rank s; rep[q] / upd[s]: float[N][cap][8];
+ * cnt: uint[N] zeroed once; pos: int[nnz] local.  stage_mask bits: 1 bucket, 2 serve, 4 step, 8 apply
+ * (15 = whole step; single bits let one device emulate several ranks in launch order). */
+typedef struct PsbSlabComm {
+    PsbSparseComm base;
+    void* req[PSB_MAX_RANKS];
+    void* req_cnt[PSB_MAX_RANKS];
+    void* rep[PSB_MAX_RANKS];
+    void* upd[PSB_MAX_RANKS];
+    void* cnt;
+    void* pos;
+    int cap;
+    int parity;
+} PsbSlabComm;
+int psb_sparse_step_slab(const PsbSlabComm* comm, int step_index, const long long* d_indptr, const int* d_indices,
+                         const float* d_values, const int* d_labels, int batch, long long nnz, int num_features,
+                         int num_class_rows, float scale, float* d_loss, int stage_mask, void* stream);
+
 /* ---------------------------------------------------------------- evaluation */
 /* argmax(X W + b) -> confusion matrix -> weighted F1, accuracy (Metrics.java:15-24).
  *   d_X fp16 dense [n][F]; d_conf: int[64] scratch (8x8, zeroed by the call);

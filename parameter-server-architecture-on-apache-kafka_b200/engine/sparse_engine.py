@@ -182,3 +182,106 @@ class VirtualSparseCluster:
     def close(self) -> None:
         for e in self.engines:
             e.close()
+
+
+class SlabSparseEngine(SparseShardedEngine):
+    """The sharded sparse step with contiguous NVLink transfers (``psb_sparse_step_slab``): request lists to the
+    owners, reply slabs back (pull), update slabs out (push), owner-side apply.  Sequentially consistent by
+    construction (all pulls of a step precede every apply).  ``max_nnz`` bounds the non-zeros of one batch."""
+
+    STAGES = (1, 2, 4, 8)
+
+    def __init__(self, num_features: int, num_classes: int = 5, rank: int = 0, world: int = 1,
+                 num_workers_total: Optional[int] = None, eta: float = 0.5, max_nnz: int = 1 << 21,
+                 device: Optional[torch.device] = None):
+        super().__init__(num_features, num_classes, rank, world, num_workers_total, eta, 0, device)
+        self.cap = int(max_nnz)
+        N = world
+        self._raw = {"req": native.device_malloc(2 * N * self.cap * 4), "req_cnt": native.device_malloc(1024),
+                     "rep": native.device_malloc(N * self.cap * 32), "upd": native.device_malloc(N * self.cap * 32)}
+        _view(self._raw["req_cnt"], 256, self.device, torch.int32).zero_()
+        self.cnt = torch.zeros(16, dtype=torch.int32, device=self.device)
+        self.pos = torch.zeros(self.cap, dtype=torch.int32, device=self.device)
+        self.peer = {k: [0] * N for k in self._raw}
+        for k, v in self._raw.items():
+            self.peer[k][rank] = v
+        torch.cuda.synchronize(self.device)
+
+    def connect(self) -> None:
+        import torch.distributed as dist
+        super().connect()
+        if self.world == 1:
+            return
+        mine = {k: native.ipc_export(v) for k, v in self._raw.items()}
+        handles = [None] * self.world
+        dist.all_gather_object(handles, mine)
+        for q in range(self.world):
+            if q != self.rank:
+                for k in self._raw:
+                    self.peer[k][q] = native.ipc_import(handles[q][k])
+        dist.barrier()
+
+    def set_slab_peers(self, engines) -> None:
+        for k in self._raw:
+            self.peer[k] = [e._raw[k] for e in engines]
+
+    def _slab_comm(self) -> native.PsbSlabComm:
+        c = native.PsbSlabComm()
+        c.base = self._comm()
+        for q in range(self.world):
+            c.req[q], c.req_cnt[q] = self.peer["req"][q], self.peer["req_cnt"][q]
+            c.rep[q], c.upd[q] = self.peer["rep"][q], self.peer["upd"][q]
+        c.cnt, c.pos, c.cap = self.cnt.data_ptr(), self.pos.data_ptr(), self.cap
+        return c
+
+    def launch_stage(self, batch: DeviceCSR, stage_mask: int) -> None:
+        if batch.nnz > self.cap:
+            raise ValueError(f"batch has {batch.nnz} non-zeros, the slabs hold {self.cap}")
+        if stage_mask & 1:
+            self.loss.zero_()
+        scale = -self.eta / (batch.n * self.num_workers)
+        comm = self._slab_comm()
+        native.check(native.lib().psb_sparse_step_slab(
+            native.C.byref(comm), self.step_index, batch.indptr.data_ptr(), batch.indices.data_ptr(),
+            batch.values.data_ptr(), batch.labels.data_ptr(), batch.n, batch.nnz, self.F, self.R, scale,
+            self.loss.data_ptr(), stage_mask, native._stream()), "psb_sparse_step_slab")
+        self.kernel_launches += bin(stage_mask).count("1")
+        if stage_mask & 8:
+            self.step_index += 1
+
+    def step(self, batch: DeviceCSR) -> None:
+        self.launch_stage(batch, 15)
+
+    def close(self) -> None:
+        if self.shard:
+            torch.cuda.synchronize(self.device)
+            if self._imported:
+                for q in range(self.world):
+                    if q != self.rank:
+                        for k in self._raw:
+                            native.lib().psb_ipc_close(self.peer[k][q])
+            for v in self._raw.values():
+                native.device_free(v)
+        super().close()
+
+
+class VirtualSlabCluster:
+    """N slab engines on ONE device: every stage is launched for all ranks before the next stage."""
+
+    def __init__(self, num_features: int, num_ranks: int, eta: float = 0.5, max_nnz: int = 1 << 16):
+        self.engines = [SlabSparseEngine(num_features, 5, r, num_ranks, num_ranks, eta, max_nnz) for r in range(num_ranks)]
+        shards, ctrls = [e.shard for e in self.engines], [e.ctrl for e in self.engines]
+        for e in self.engines:
+            e.set_peers(shards, ctrls)
+            e.set_slab_peers(self.engines)
+
+    def step(self, batches) -> None:
+        for stage in SlabSparseEngine.STAGES:
+            for e, b in zip(self.engines, batches):
+                e.launch_stage(b, stage)
+
+    weights = VirtualSparseCluster.weights
+
+    def close(self) -> None:
+        for e in self.engines:
+            e.close()

@@ -41,6 +41,12 @@ class PsbSparseComm(C.Structure):
                 ("spin_limit", C.c_ulonglong)]
 
 
+class PsbSlabComm(C.Structure):
+    _fields_ = [("base", PsbSparseComm), ("req", C.c_void_p * MAX_RANKS), ("req_cnt", C.c_void_p * MAX_RANKS),
+                ("rep", C.c_void_p * MAX_RANKS), ("upd", C.c_void_p * MAX_RANKS), ("cnt", C.c_void_p),
+                ("pos", C.c_void_p), ("cap", C.c_int), ("parity", C.c_int)]
+
+
 class PsbComm(C.Structure):
     _fields_ = [("mode", C.c_int), ("rank", C.c_int), ("num_ranks", C.c_int), ("workers_per_rank", C.c_int),
                 ("clock", C.c_int), ("max_delay", C.c_int), ("lr", C.c_float), ("spin_limit", C.c_ulonglong),
@@ -83,6 +89,8 @@ def lib() -> C.CDLL:
     L.psb_sparse_step.argtypes = [C.POINTER(PsbSparseComm), C.c_int, C.c_uint, C.c_uint, vp, vp, vp, vp, C.c_int, C.c_int,
                                   C.c_int, C.c_float, vp, vp, vp]
     L.psb_sparse_eval.argtypes = [C.POINTER(PsbSparseComm), vp, vp, vp, vp, C.c_int, C.c_int, C.c_int, vp, vp]
+    L.psb_sparse_step_slab.argtypes = [C.POINTER(PsbSlabComm), C.c_int, vp, vp, vp, vp, C.c_int, C.c_longlong, C.c_int,
+                                       C.c_int, C.c_float, vp, C.c_int, vp]
     L.psb_ring_scatter.argtypes = [vp, C.c_int, C.c_int, vp, ip, C.c_int, C.c_int, vp]
     L.psb_ring_store_dense.argtypes = [vp, C.c_int, ip, ip, C.c_int, vp, ip, C.c_int, C.c_int, vp]
     L.psb_malloc.argtypes = [C.POINTER(C.c_void_p), C.c_size_t]

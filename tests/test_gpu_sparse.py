@@ -56,3 +56,31 @@ def test_sparse_steps_match_dense_sgd(model, ranks):
         assert abs(acc - ref.accuracy) < 0.01 and abs(f1 - ref.f1) < 0.01
     finally:
         vc.close()
+
+
+@pytest.mark.parametrize("ranks", [1, 4])
+def test_slab_exchange_matches_dense_sgd(ranks):
+    from psb200.engine.sparse_engine import DeviceCSR, VirtualSlabCluster
+    F, B, eta = 5000, 256, 0.7
+    vc = VirtualSlabCluster(F, ranks, eta, max_nnz=B * 40)
+    try:
+        W, b = np.zeros((F, 8)), np.zeros(8)
+        for step in range(3):
+            batches = [random_csr(B, F, 40, seed=50 * step + r) for r in range(ranks)]
+            dev = [DeviceCSR(bt, vc.engines[0].device) for bt in batches]
+            vc.step(dev)
+            losses = [e.mean_loss(d) for e, d in zip(vc.engines, dev)]
+            dW, db, ref_losses = np.zeros_like(W), np.zeros_like(b), []
+            for bt in batches:
+                X = bt.to_dense(np.float64)
+                loss, r = _softmax_residual(X, bt.labels.astype(np.int64), W, b)
+                ref_losses.append(loss.mean())
+                dW[:, :6] += -eta / (B * ranks) * (X.T @ r)
+                db[:6] += -eta / (B * ranks) * r.sum(axis=0)
+            W, b = W + dW, b + db
+            assert np.allclose(losses, ref_losses, rtol=2e-4, atol=2e-4)
+        Wd, bd = vc.weights()
+        assert np.abs(Wd - W).max() < 2e-4 * max(1.0, np.abs(W).max()) and np.abs(bd - b).max() < 2e-4
+        assert all(e.status() == 0 for e in vc.engines)
+    finally:
+        vc.close()

@@ -11,7 +11,7 @@ import numpy as np
 import torch
 import torch.distributed as dist
 
-from psb200.engine.sparse_engine import SparseShardedEngine
+from psb200.engine.sparse_engine import SlabSparseEngine, SparseShardedEngine
 from psb200.ops import native
 
 
@@ -36,6 +36,8 @@ def main():
     p.add_argument("--steps", type=int, default=20)
     p.add_argument("--warmup", type=int, default=3)
     p.add_argument("--consistency_model", type=int, default=-1)
+    p.add_argument("--path", default="direct", choices=["direct", "slab"],
+                   help="direct: one P2P request per non-zero; slab: request lists + contiguous reply/update slabs")
     p.add_argument("--baseline", action="store_true", help="also time the NCCL dense all_reduce baseline")
     a = p.parse_args()
     world, rank, local = int(os.environ.get("WORLD_SIZE", 1)), int(os.environ.get("RANK", 0)), int(os.environ.get("LOCAL_RANK", 0))
@@ -66,19 +68,22 @@ def main():
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item()) / a.steps
 
-    eng = SparseShardedEngine(F, 5, rank, world, world, 0.5, a.consistency_model, dev)
+    if a.path == "slab":
+        eng = SlabSparseEngine(F, 5, rank, world, world, 0.5, a.batch * a.nnz, dev)
+    else:
+        eng = SparseShardedEngine(F, 5, rank, world, world, 0.5, a.consistency_model, dev)
     eng.connect()
     ms = timed(lambda i: eng.step(batches[i % 4]))
     loss = eng.mean_loss(batches[(a.steps - 1) % 4])
     status = eng.status()
     bytes_pp = 2 * batches[0].nnz * 32                         # pull + push bytes per GPU per step
-    out = {"config": "sharded sparse LR", "impl": "fused-p2p", "n_gpus": world, "features": F, "batch_per_gpu": a.batch,
+    out = {"config": "sharded sparse LR", "impl": "fused-p2p-" + a.path, "n_gpus": world, "features": F, "batch_per_gpu": a.batch,
            "nnz_per_row": a.nnz, "consistency_model": a.consistency_model, "ms_per_step": ms,
            "samples_per_sec": a.batch * world / (ms / 1e3),
            "pull_push_GBps_per_gpu": bytes_pp / (ms / 1e3) / 1e9,
            "nvlink_GBps_per_gpu_per_direction": bytes_pp / 2 * (world - 1) / world / (ms / 1e3) / 1e9,
            "model_MiB_per_shard": eng.shard_bytes / 2 ** 20, "loss": loss, "status": status,
-           "kernels_per_step": 1 if a.consistency_model != 0 else 2}
+           "kernels_per_step": 4 if a.path == "slab" else (1 if a.consistency_model != 0 else 2)}
     if rank == 0:
         print(json.dumps(out))
     eng.close()
