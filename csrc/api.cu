@@ -135,6 +135,15 @@ int psb_ring_store_dense(const void* d_rows, int src_half, const int* d_labels_i
                                        num_features, (cudaStream_t)stream);
 }
 
+// Random 32-byte row traffic (sharded sparse path): ask L2 to fetch 32-byte sectors instead of promoting every
+// miss to 64/128 bytes.  A hint; returns the granularity the device reports afterwards.
+int psb_set_l2_fetch_granularity(int bytes) {
+    PSB_CHECK_CUDA(cudaDeviceSetLimit(cudaLimitMaxL2FetchGranularity, (size_t)bytes));
+    size_t got = 0;
+    PSB_CHECK_CUDA(cudaDeviceGetLimit(&got, cudaLimitMaxL2FetchGranularity));
+    return (int)got;
+}
+
 // ------------------------------------------------------------------ peer memory plumbing
 int psb_malloc(void** d_ptr_out, size_t bytes) {
     PSB_REQUIRE(d_ptr_out && bytes > 0, "psb_malloc: bad arguments");

@@ -214,6 +214,9 @@ void psb_producer_release(void* h, int batch);
 long long psb_producer_rows_sent(void* h);
 void psb_producer_stop(void* h);
 
+/* L2 fetch-granularity hint for random 32-byte row traffic (sparse path); returns the value in effect */
+int psb_set_l2_fetch_granularity(int bytes);
+
 /* Peer memory: raw cudaMalloc (IPC-exportable, unlike a caching-allocator block) and IPC export /
  * import of a device allocation (transport set-up; replaces ServerApp.createTopics, ServerApp.java:31-42) */
 int psb_malloc(void** d_ptr_out, size_t bytes);

@@ -38,6 +38,7 @@ def main():
     p.add_argument("--consistency_model", type=int, default=-1)
     p.add_argument("--path", default="direct", choices=["direct", "slab"],
                    help="direct: one P2P request per non-zero; slab: request lists + contiguous reply/update slabs")
+    p.add_argument("--l2_fetch", type=int, default=0, help="cudaLimitMaxL2FetchGranularity hint (32/64/128; 0 = leave)")
     p.add_argument("--baseline", action="store_true", help="also time the NCCL dense all_reduce baseline")
     a = p.parse_args()
     world, rank, local = int(os.environ.get("WORLD_SIZE", 1)), int(os.environ.get("RANK", 0)), int(os.environ.get("LOCAL_RANK", 0))
@@ -47,6 +48,7 @@ def main():
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=dev)
     F = a.features
+    l2 = native.lib().psb_set_l2_fetch_granularity(a.l2_fetch) if a.l2_fetch else None
     batches = [Batch(a.batch, F, a.nnz, 100 * rank + i, dev) for i in range(4)]
 
     def timed(fn):
@@ -83,7 +85,7 @@ def main():
            "pull_push_GBps_per_gpu": bytes_pp / (ms / 1e3) / 1e9,
            "nvlink_GBps_per_gpu_per_direction": bytes_pp / 2 * (world - 1) / world / (ms / 1e3) / 1e9,
            "model_MiB_per_shard": eng.shard_bytes / 2 ** 20, "loss": loss, "status": status,
-           "kernels_per_step": 4 if a.path == "slab" else (1 if a.consistency_model != 0 else 2)}
+           "l2_fetch_granularity": l2, "kernels_per_step": 4 if a.path == "slab" else (1 if a.consistency_model != 0 else 2)}
     if rank == 0:
         print(json.dumps(out))
     eng.close()
