@@ -261,6 +261,8 @@ extern "C" int psb_buffer_on_event(void* bp, double now_ms, int* head, int* coun
     return slot;
 }
 
+extern "C" long long psb_buffer_inserted(void* bp) { return ((Buffer*)bp)->inserted; }
+
 // Batch form used by the ingestion hot path: n events -> (worker, slot) table + the new (head, count)
 // window of every worker that received a row.  `buffers` is an array of psb_buffer_create handles.
 extern "C" int psb_buffers_on_batch(void** buffers, int num_buffers, const int* workers, const double* now_ms, int n,

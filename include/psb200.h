@@ -197,6 +197,7 @@ int psb_tracker_clocks(void* t, int* clocks);
 void* psb_buffer_create(int min_size, int max_size, float bc, int window);
 void psb_buffer_destroy(void* b);
 int psb_buffer_on_event(void* b, double now_ms, int* head, int* count, int* target);
+long long psb_buffer_inserted(void* b);   /* rows ever inserted == numTuplesSeen of the worker log */
 /* n events at once: fills worker_slot[n][2] and updates win[num_buffers][2] for the touched workers */
 int psb_buffers_on_batch(void** buffers, int num_buffers, const int* workers, const double* now_ms, int n,
                          int* worker_slot, int* win);

@@ -162,8 +162,6 @@ class DeviceEngine:
         self._tables_free()
         native.buffers_on_batch(self.buffers, workers[:n], now_ms[:n], self.stage_ws_host.numpy(),
                                 self.win_host.numpy())
-        for w, c in zip(*np.unique(np.asarray(workers[:n]), return_counts=True)):
-            self.buffers[int(w)].total += int(c)
         self._ingest_staged(rows_f16, labels, n, wait)
 
     def ingest_slots(self, rows_f16: torch.Tensor, labels: torch.Tensor, worker_slot: torch.Tensor,
@@ -211,8 +209,6 @@ class DeviceEngine:
         self._tables_free()
         native.buffers_on_batch(self.buffers, workers[:n], now_ms[:n], self.stage_ws_host.numpy(),
                                 self.win_host.numpy())
-        for w, c in zip(*np.unique(np.asarray(workers[:n]), return_counts=True)):
-            self.buffers[int(w)].total += int(c)
         self._h2d(rows_f16, labels, n)
 
     def ingest_commit(self, wait: bool = True) -> None:

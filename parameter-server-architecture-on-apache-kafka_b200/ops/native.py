@@ -107,6 +107,8 @@ def lib() -> C.CDLL:
     L.psb_buffer_create.argtypes = [C.c_int, C.c_int, C.c_float, C.c_int]
     L.psb_buffer_destroy.argtypes = [vp]
     L.psb_buffer_on_event.argtypes = [vp, C.c_double, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int)]
+    L.psb_buffer_inserted.restype = C.c_longlong
+    L.psb_buffer_inserted.argtypes = [vp]
     L.psb_buffers_on_batch.argtypes = [vp, C.c_int, vp, vp, C.c_int, vp, vp]
     L.psb_producer_start.restype = C.c_void_p
     L.psb_producer_start.argtypes = [C.c_char_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
@@ -189,17 +191,15 @@ class NativeBuffer:
         if not self.h:
             raise NativeError("psb_buffer_create failed")
         self.head = self.count = self.target = 0
-        self.total = 0
 
     def ring_total(self) -> int:
         """rows ever inserted (numTuplesSeen of the reference worker log)"""
-        return self.total
+        return int(lib().psb_buffer_inserted(self.h))
 
     def on_event(self, now_ms: float) -> int:
         h, c, t = C.c_int(), C.c_int(), C.c_int()
         slot = lib().psb_buffer_on_event(self.h, float(now_ms), C.byref(h), C.byref(c), C.byref(t))
         self.head, self.count, self.target = h.value, c.value, t.value
-        self.total += 1
         return slot
 
     def __del__(self):
