@@ -1,0 +1,62 @@
+"""C++ host runtime vs its Python statement: buffer policy, tracker, CSV tokenizer."""
+import os
+import random
+
+import numpy as np
+import pytest
+
+from psb200.consistency import ConsistencyScheduler, ProtocolViolation
+from psb200.data import ReviewGenerator, read_csv, write_csv
+from psb200.engine.buffer import DynamicBuffer
+from psb200.ops import native
+
+
+def test_native_buffer_matches_python_policy():
+    rng = random.Random(4)
+    py, cc = DynamicBuffer(16, 128, 0.3), native.NativeBuffer(16, 128, 0.3)
+    t = 0.0
+    for i in range(3000):
+        if i % 400 == 0:
+            gap = rng.choice([5.0, 50.0, 400.0, 2000.0])
+        t += gap
+        a, b = py.on_event(t), cc.on_event(t)
+        assert a == b and (py.ring.head, py.ring.count, py.target) == (cc.head, cc.count, cc.target)
+    assert cc.ring_total() == py.ring.total == 3000
+
+
+def test_native_buffer_batch_form():
+    bufs = [native.NativeBuffer(4, 32, 0.3) for _ in range(3)]
+    ref = [DynamicBuffer(4, 32, 0.3) for _ in range(3)]
+    workers = np.array([0, 1, 2, 0, 0, 1] * 20, dtype=np.int32)
+    now = np.arange(len(workers)) * 700.0
+    ws = np.zeros((len(workers), 2), dtype=np.int32)
+    win = np.zeros((3, 2), dtype=np.int32)
+    native.buffers_on_batch(bufs, workers, now, ws, win)
+    for i, w in enumerate(workers):
+        assert ws[i, 0] == w and ws[i, 1] == ref[w].on_event(now[i])
+    for w in range(3):
+        assert (win[w, 0], win[w, 1]) == (ref[w].ring.head, ref[w].ring.count)
+
+
+@pytest.mark.parametrize("model", [0, 3, -1])
+def test_native_tracker_matches_python_and_rejects_violations(model):
+    t, s = native.NativeTracker(3, model), ConsistencyScheduler(3, model)
+    assert sorted(t.on_gradient(1, 0)) == sorted(s.on_gradient(1, 0))
+    with pytest.raises(native.NativeError, match="Expected value 1, actual value 0"):
+        t.on_gradient(1, 0)
+    with pytest.raises(ProtocolViolation):
+        s.on_gradient(1, 0)
+    assert t.clocks() == s.tracker.clocks
+
+
+def test_csv_tokenizer_matches_numpy_reader(tmp_path):
+    b = ReviewGenerator(num_features=128, vocab=800, mean_len=30).train_split(300)
+    path = os.path.join(tmp_path, "d.csv")
+    write_csv(path, b)
+    a, r = native.csv_to_csr(path), read_csv(path)
+    assert np.array_equal(a.indptr, r.indptr) and np.array_equal(a.indices, r.indices)
+    assert np.allclose(a.values, r.values, atol=1e-7) and np.array_equal(a.labels, r.labels)
+    with open(path, "a") as f:                       # exponent notation and a CRLF line go through strtof
+        f.write(",".join(["1e-3"] + ["0"] * 126 + ["-2.5E-1"]) + ",4\r\n")
+    a = native.csv_to_csr(path)
+    assert len(a) == 301 and np.allclose(a.row(300)[1], [1e-3, -0.25]) and a.row(300)[2] == 4
