@@ -77,3 +77,15 @@ def test_worker_metrics_and_dynamic_buffer(tmp_path):
     eng.ingest(rows[:400], labs[:400], workers[:400], 30000.0 + np.arange(400) // 2 * 1000.0)   # 60/min -> shrinks
     assert all(128 <= c < 600 for c in eng.win_host[:, 1].tolist())
     eng.close()
+
+
+def test_server_app_runner_with_cuda_backend(tmp_path):
+    """The reference-style entry point with the sm_100a kernels doing the math (in-process, sequential)."""
+    cmd = [sys.executable, "-m", "psb200.apps.server_app_runner", "-training", "synthetic:1200", "-test",
+           "synthetic:500", "-p", "0", "--num_workers", "2", "--in_process", "--max_clock", "4", "-l", "--backend", "cuda",
+           "-max", "256"]
+    r = subprocess.run(cmd, env=ENV, cwd=tmp_path, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stderr[-3000:]
+    s = parse_log(str(tmp_path / "logs-server.csv"), "server")
+    w = parse_log(str(tmp_path / "logs-worker.csv"), "worker")
+    assert len(s) == 4 and len(w) >= 6 and np.all(np.isfinite(w[:, 3])) and s[-1, 4] > 0.2
