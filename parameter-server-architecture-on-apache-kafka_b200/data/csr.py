@@ -1,11 +1,10 @@
-"""Sparse row containers shared by the producer, the ring buffer and the kernels.
+"""Sparse row containers shared by the producer, the engines and the kernels.
 
 ``CSRBatch`` is the interchange format (indptr / indices / values / labels).
-``pack_rows`` lays rows out the way the device ring stores them (see
-``include/psb200.h``: ``PSB_ROW_*``): fixed-capacity ELL slots whose entries are
-(int32 index, fp32 value) pairs grouped by *owner* = ``index % NOWN``; the per-row
-group offsets let each warp of the gradient pass walk only the features it owns,
-so the transposed product X^T R needs no atomics.
+``pack_stage_rows`` lays rows out the way the sparse ingestion kernel reads them (``psb_ring_scatter``,
+``csrc/ps_ring.cu``): one fixed-stride record per row — nnz, label, worker, slot, then nnz (int32 index,
+fp32 value) pairs — which the kernel expands into the dense fp16 ring slot.  For rows below ~25 % density
+this is fewer PCIe bytes than shipping the dense fp16 row.
 
 Reference for what a row is: ``LabeledData.java:14-28`` (sparse map + label) and
 ``CsvProducer.java:52-58`` (non-zero filter).
@@ -17,8 +16,7 @@ from typing import Tuple
 
 import numpy as np
 
-NOWN = 16               # gradient owners per row == warps of the worker CTA
-HDR_WORDS = 12          # 48-byte slot header: nnz, label, id(lo,hi), 16 x u16 group start offsets
+STAGE_HDR_WORDS = 4     # nnz, label, worker, slot
 
 
 @dataclass
@@ -78,64 +76,39 @@ class CSRBatch:
                         np.concatenate([a.labels, b.labels]), a.num_features)
 
 
-def slot_words(row_capacity: int) -> int:
-    """32-bit words per ring slot: header + 2 words per entry."""
-    return HDR_WORDS + 2 * row_capacity
+def stage_stride_words(max_nnz: int) -> int:
+    """32-bit words per staged row: 4 header words + 2 per entry."""
+    return STAGE_HDR_WORDS + 2 * max_nnz
 
 
-def pack_rows(batch: CSRBatch, row_capacity: int, first_id: int = 1) -> np.ndarray:
-    """Pack rows into device slot images: uint32[n, slot_words].
-
-    Header words: [0]=nnz, [1]=label, [2]=insertion id low, [3]=insertion id high,
-    [4..11] = 16 uint16 group start offsets (owner g covers entries off[g]..off[g+1], off[16]=nnz).
-    Entry e: word 12+2e = int32 feature index, word 13+2e = fp32 value bits.
-    """
+def pack_stage_rows(batch: CSRBatch, worker_slot: np.ndarray, max_nnz: int = 0) -> np.ndarray:
+    """Rows -> uint32[n, stride] records for ``psb_ring_scatter``; worker_slot is int[n, 2]."""
     n = len(batch)
-    sw = slot_words(row_capacity)
-    out = np.zeros((n, sw), dtype=np.uint32)
     lens = np.diff(batch.indptr)
-    if n and lens.max() > row_capacity:
-        raise ValueError(f"row with {int(lens.max())} non-zeros exceeds the slot capacity {row_capacity}")
-    for i in range(n):
-        a, b = batch.indptr[i], batch.indptr[i + 1]
-        idx = batch.indices[a:b]
-        val = batch.values[a:b]
-        own = idx % NOWN
-        order = np.lexsort((idx, own))
-        idx, val, own = idx[order], val[order], own[order]
-        off = np.zeros(NOWN + 1, dtype=np.uint16)
-        off[1:] = np.cumsum(np.bincount(own, minlength=NOWN))
-        ins = first_id + i
-        out[i, 0] = b - a
-        out[i, 1] = np.uint32(batch.labels[i])
-        out[i, 2] = ins & 0xFFFFFFFF
-        out[i, 3] = (ins >> 32) & 0xFFFFFFFF
-        # 16 group start offsets fit words 4..11; the 17th (== nnz) is word 0
-        out[i, 4:12] = off[:NOWN].view(np.uint32)
-        e = HDR_WORDS + 2 * np.arange(b - a)
-        out[i, e] = idx.astype(np.int32).view(np.uint32)
-        out[i, e + 1] = val.astype(np.float32).view(np.uint32)
+    max_nnz = max_nnz or (int(lens.max()) if n else 1)
+    if n and lens.max() > max_nnz:
+        raise ValueError(f"row with {int(lens.max())} non-zeros exceeds the staging capacity {max_nnz}")
+    out = np.zeros((n, stage_stride_words(max_nnz)), dtype=np.uint32)
+    out[:, 0] = lens
+    out[:, 1] = batch.labels.astype(np.uint32)
+    out[:, 2:4] = np.asarray(worker_slot, dtype=np.int32).view(np.uint32)
+    rows = np.repeat(np.arange(n), lens)
+    within = np.arange(batch.nnz) - np.repeat(batch.indptr[:-1], lens)
+    out[rows, STAGE_HDR_WORDS + 2 * within] = batch.indices.astype(np.int32).view(np.uint32)
+    out[rows, STAGE_HDR_WORDS + 2 * within + 1] = batch.values.astype(np.float32).view(np.uint32)
     return out
 
 
-def unpack_rows(slots: np.ndarray, num_features: int) -> CSRBatch:
-    slots = np.asarray(slots, dtype=np.uint32)
-    n = slots.shape[0]
-    nnz = slots[:, 0].astype(np.int64)
+def unpack_stage_rows(stage: np.ndarray, num_features: int) -> Tuple[CSRBatch, np.ndarray]:
+    """Inverse of pack_stage_rows: (batch, worker_slot)."""
+    stage = np.asarray(stage, dtype=np.uint32)
+    n = stage.shape[0]
+    lens = stage[:, 0].astype(np.int64)
     indptr = np.zeros(n + 1, dtype=np.int64)
-    np.cumsum(nnz, out=indptr[1:])
-    indices = np.zeros(indptr[-1], dtype=np.int32)
-    values = np.zeros(indptr[-1], dtype=np.float32)
-    for i in range(n):
-        e = HDR_WORDS + 2 * np.arange(nnz[i])
-        idx = slots[i, e].view(np.int32)
-        val = slots[i, e + 1].view(np.float32)
-        order = np.argsort(idx, kind="stable")
-        indices[indptr[i]:indptr[i + 1]] = idx[order]
-        values[indptr[i]:indptr[i + 1]] = val[order]
-    return CSRBatch(indptr, indices, values, slots[:, 1].astype(np.int32), num_features)
-
-
-def insertion_ids(slots: np.ndarray) -> np.ndarray:
-    slots = np.asarray(slots, dtype=np.uint32)
-    return slots[:, 2].astype(np.int64) | (slots[:, 3].astype(np.int64) << 32)
+    np.cumsum(lens, out=indptr[1:])
+    rows = np.repeat(np.arange(n), lens)
+    within = np.arange(indptr[-1]) - np.repeat(indptr[:-1], lens)
+    indices = stage[rows, STAGE_HDR_WORDS + 2 * within].view(np.int32)
+    values = stage[rows, STAGE_HDR_WORDS + 2 * within + 1].view(np.float32)
+    batch = CSRBatch(indptr, indices.copy(), values.copy(), stage[:, 1].astype(np.int32), num_features)
+    return batch, stage[:, 2:4].view(np.int32).copy()

@@ -164,6 +164,32 @@ class DeviceEngine:
                                 self.win_host.numpy())
         self._ingest_staged(rows_f16, labels, n, wait)
 
+    def ingest_sparse(self, batch: CSRBatch, workers: np.ndarray, now_ms: Optional[np.ndarray] = None) -> None:
+        """ingest() for sparse rows: ships (index, value) records instead of dense fp16 rows and lets
+        ``psb_ring_scatter`` expand them on the device — fewer PCIe bytes below ~25 % density."""
+        from ..data.csr import pack_stage_rows
+        n = len(batch)
+        if now_ms is None:
+            now_ms = np.zeros(n, dtype=np.float64)
+        self._tables_free()
+        native.buffers_on_batch(self.buffers, workers[:n], now_ms[:n], self.stage_ws_host.numpy(),
+                                self.win_host.numpy())
+        stage = torch.from_numpy(pack_stage_rows(batch, self.stage_ws_host.numpy()[:n]).view(np.int32)).pin_memory()
+        s = self.ingest_stream
+        s.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(s):
+            stage_dev = stage.to(self.device, non_blocking=True)
+            self.win.copy_(self.win_host, non_blocking=True)
+            native.ring_scatter(stage_dev, n, stage.shape[1], self.X, self.labels, self.cap, self.F, stream=s)
+            self.ingest_done.record(s)
+            self.h2d_done[self.stage_slot].record(s)
+        stage_dev.record_stream(s)
+        self.kernel_launches += 1
+        self.rows_ingested += n
+        self.h2d_bytes += stage.numel() * 4 + self.W * 8
+        torch.cuda.current_stream().wait_event(self.ingest_done)
+        self._keep = (stage, stage_dev)          # pinned source must outlive the async copy
+
     def ingest_slots(self, rows_f16: torch.Tensor, labels: torch.Tensor, worker_slot: torch.Tensor,
                      win: torch.Tensor, wait: bool = True) -> None:
         """Same as ingest() with the (worker, slot) table and the new windows precomputed (bench hot path)."""

@@ -89,3 +89,21 @@ def test_server_app_runner_with_cuda_backend(tmp_path):
     s = parse_log(str(tmp_path / "logs-server.csv"), "server")
     w = parse_log(str(tmp_path / "logs-worker.csv"), "worker")
     assert len(s) == 4 and len(w) >= 6 and np.all(np.isfinite(w[:, 3])) and s[-1, 4] > 0.2
+
+
+def test_sparse_and_dense_ingestion_fill_identical_rings():
+    from psb200.config import PSConfig
+    from psb200.data import random_csr
+    from psb200.engine.device_engine import DeviceEngine
+    cfg = PSConfig(num_workers=3, max_buffer_size=128, min_buffer_size=16, num_features=256)
+    b = random_csr(200, 256, 30, seed=8)
+    workers = (np.arange(200) % 3).astype(np.int32)
+    engs = [DeviceEngine(cfg, 3, impl=0, stage_rows=256) for _ in range(2)]
+    engs[0].ingest(torch.from_numpy(b.to_dense(np.float16)).pin_memory(),
+                   torch.from_numpy(b.labels.astype(np.int32)).pin_memory(), workers)
+    engs[1].ingest_sparse(b, workers)
+    torch.cuda.synchronize()
+    assert torch.equal(engs[0].X, engs[1].X) and torch.equal(engs[0].labels, engs[1].labels)
+    assert torch.equal(engs[0].win.cpu(), engs[1].win.cpu())
+    for e in engs:
+        e.close()

@@ -4,9 +4,8 @@ import os
 import numpy as np
 from sklearn.metrics import accuracy_score, f1_score
 
-from psb200.data import (CSRBatch, ReviewGenerator, TEST_SUPPORTS, header, pack_rows, random_csr, read_csv,
-                         unpack_rows, write_csv)
-from psb200.data.csr import insertion_ids
+from psb200.data import (CSRBatch, ReviewGenerator, TEST_SUPPORTS, header, pack_stage_rows, random_csr, read_csv,
+                         stage_stride_words, unpack_stage_rows, write_csv)
 from psb200.utils.metrics import evaluate
 
 
@@ -38,17 +37,14 @@ def test_csv_roundtrip(tmp_path):
     assert np.allclose(r.to_dense(), b.to_dense(), atol=1e-6)
 
 
-def test_slot_packing_groups_by_owner():
+def test_stage_packing_roundtrip():
     b = random_csr(30, 256, 20, seed=3)
-    slots = pack_rows(b, 32, first_id=7)
-    assert np.array_equal(insertion_ids(slots), np.arange(7, 37))
-    u = unpack_rows(slots, 256)
-    assert np.allclose(u.to_dense(), b.to_dense()) and np.array_equal(u.labels, b.labels)
-    for i in range(30):
-        off = list(slots[i, 4:12].view(np.uint16)) + [slots[i, 0]]
-        idx = slots[i, 12:12 + 2 * slots[i, 0]:2].view(np.int32)
-        for g in range(16):
-            assert np.all(idx[off[g]:off[g + 1]] % 16 == g)
+    ws = np.stack([np.arange(30) % 4, np.arange(30) * 3 % 64], axis=1).astype(np.int32)
+    stage = pack_stage_rows(b, ws, max_nnz=24)
+    assert stage.shape == (30, stage_stride_words(24)) and np.all(stage[:, 0] == 20)
+    u, ws2 = unpack_stage_rows(stage, 256)
+    assert np.array_equal(ws2, ws) and np.array_equal(u.labels, b.labels)
+    assert np.allclose(u.to_dense(), b.to_dense())
 
 
 def test_synthetic_shape():
