@@ -69,7 +69,6 @@ class PSConfig:
     verbose: bool = False
     logging: bool = False
     max_clock: int = -1                # stop after this many server clocks (-1: run until producer EOF + drain)
-    row_capacity: int = 0              # ELL slot capacity (0: min(num_features, 1024))
     eval_every: int = 1
     inject_delay: str = ""             # "rank:ms[,rank:ms]" straggler injection
 
