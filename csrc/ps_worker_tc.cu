@@ -71,6 +71,17 @@ __device__ __forceinline__ bool wait_or_fail(uint64_t* bar, uint32_t parity, vol
     return true;
 }
 
+// What one pass over the buffer does.  a: A stream + logits GEMM; b: B stream + gradient GEMM;
+// fused: standardisation statistics ride on the A stream (first evaluation only);
+// zstore: the epilogue also stores the raw logits (no intercept) of every valid row there;
+// zsrc: residuals come from cached logits instead of TMEM (gradient-only pass);
+// logits_only: the epilogue stops after storing the logits (direction pass).
+struct PassCfg {
+    bool a, b, fused, logits_only;
+    float* zstore;
+    const float* zsrc;
+};
+
 struct TcEval {
     const CUtensorMap* tmX;
     const int* labels;        // this worker's [cap]
@@ -79,6 +90,8 @@ struct TcEval {
     uint32_t tmem;
     TcShared sh;
     unsigned int zuse[2], ruse[2], guse;   // per-thread running barrier use counts (persist across evaluations)
+    float* Zx;                             // cached logits of the current point / of the direction, [cap][8] each
+    float* Zd;                             // (null: no caching, every trial is a full evaluation)
 #ifdef PSB_TC_PROFILE
     long long prof[4];                     // cycles: [0] wait full(A) [1] wait r_full [2] wait full(B) [3] role total
 #endif
@@ -118,7 +131,8 @@ struct TcEval {
     // ---- TMA producer (one thread).  with_b: stream every slab twice, A(s) then B(s).
     // fused: the statistics warps also read every A chunk, so a slot whose previous occupant was an A chunk
     // of this pass is refilled only after their sdone arrival as well.
-    __device__ void produce(bool with_b, bool fused = false) const {
+    __device__ void produce(const PassCfg& cfg) const {
+        const bool with_a = cfg.a, with_b = cfg.b, fused = cfg.fused;
         const int nkb = F / kBlockK, S = num_active_slabs();
         unsigned int pc = *sh.chunk_base;
         const unsigned int base = pc;
@@ -141,8 +155,9 @@ struct TcEval {
         };
         for (int q = 0; q < S; ++q) {
             const int b = active_slab(q);
-            for (int c = 0; c < nkb; ++c)
-                if (!load(b, c, with_b ? tc::kL2EvictLast : tc::kL2EvictFirst)) return;
+            if (with_a)
+                for (int c = 0; c < nkb; ++c)
+                    if (!load(b, c, with_b ? tc::kL2EvictLast : tc::kL2EvictFirst)) return;
             if (with_b)
                 for (int c = 0; c < nkb; ++c)
                     if (!load(b, c, tc::kL2EvictFirst)) return;
@@ -225,7 +240,7 @@ struct TcEval {
 
     // ---- MMA issuer: the whole warp walks the ring in stream order (warp-uniform state), one elected
     //      lane issues the tcgen05 instructions
-    __device__ void mma_loop() {
+    __device__ void mma_loop(const PassCfg& cfg) {
         const int nkb = F / kBlockK, S = __shfl_sync(0xffffffffu, num_active_slabs(), 0);
         constexpr uint32_t idesc1 = tc::idesc_f16(128, 16, 0, 0);    // GEMM1: A K-major, B K-major
         constexpr uint32_t idesc2 = tc::idesc_f16(128, 16, 1, 1);    // GEMM2: A MN-major, B MN-major
@@ -291,39 +306,83 @@ struct TcEval {
             }
             return true;
         };
+        // Logits-only pass: Z buffer q&1 is rewritten by GEMM1(q+2), so before issuing GEMM1(q) wait until the
+        // epilogue has read slab q-2 out of it.  Two barriers (r_full[q&1]) so that a barrier never completes
+        // two phases between two waits of this warp (mbarrier waits carry one parity bit).
+        auto z_read = [&](int q) -> bool {
+            if (!wait_or_fail(sh.r_full + (q & 1), ruse[q & 1] & 1, sh.fail)) return false;
+            ++ruse[q & 1];
+            return true;
+        };
         for (int q = 0; q < S; ++q) {
 #ifdef PSB_TC_PROFILE
             const long long tg = clock64();
 #endif
-            if (!gemm1(q)) return;
+            if (!cfg.b && q >= 2 && !z_read(q - 2)) return;
+            if (cfg.a && !gemm1(q)) return;
 #ifdef PSB_TC_PROFILE
             prof[1] += clock64() - tg;
 #endif
-            if (!gemm2(q)) return;
+            if (cfg.b && !gemm2(q)) return;
+            if (cfg.b && !cfg.a) {           // gradient-only pass: tell the residual warps that Rsp(q) has been consumed
+                if (tc::elect_one()) tc::umma_commit(sh.z_full + (q & 1));
+                __syncwarp();
+            }
         }
-        if (tc::elect_one()) tc::umma_commit(sh.g_full);
+        if (!cfg.b) {
+            if (S >= 2 && !z_read(S - 2)) return;
+            if (S >= 1 && !z_read(S - 1)) return;
+        }
+        if (cfg.b && tc::elect_one()) tc::umma_commit(sh.g_full);
         __syncwarp();
     }
 
     // ---- epilogue warps (4 warps; wi = TMEM sub-partition = warp % 4); thread = row of the slab
-    __device__ void epilogue(int wi, int lane, float* g, float invn, bool fused) {
+    __device__ void epilogue(int wi, int lane, float* g, float invn, const PassCfg& cfg) {
+        const bool fused = cfg.fused;
         const int nkb = F / kBlockK, S = num_active_slabs();
         float lsum = 0.f, rs[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
         const float* bias = sh.sred + 16;            // intercepts staged behind the reduction words
         for (int q = 0; q < S; ++q) {
             const int b = active_slab(q), zb = q & 1;
-            if (!wait_or_fail(sh.z_full + zb, zuse[zb] & 1, sh.fail)) return;
-            ++zuse[zb];
-            tc::tc_fence_after();
-            float v[16];
-            tc::tmem_ld_32x32b_x16(tmem + kColZ + 16 * zb + ((uint32_t)(wi * 32) << 16), v);
             const int r = wi * 32 + lane;
             const int slot = b * kSlabRows + r;
-            float rr[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-            if (row_valid(slot)) {
-                float z[8];
+            const bool valid = row_valid(slot);
+            float z[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+            if (cfg.a) {
+                if (!wait_or_fail(sh.z_full + zb, zuse[zb] & 1, sh.fail)) return;
+                ++zuse[zb];
+                tc::tc_fence_after();
+                float v[16];
+                tc::tmem_ld_32x32b_x16(tmem + kColZ + 16 * zb + ((uint32_t)(wi * 32) << 16), v);
 #pragma unroll
                 for (int c = 0; c < 8; ++c) z[c] = v[c] + v[8 + c];
+                if (cfg.zstore && valid) {
+                    float4* zo = (float4*)cfg.zstore + 2 * slot;
+                    zo[0] = make_float4(z[0], z[1], z[2], z[3]);
+                    zo[1] = make_float4(z[4], z[5], z[6], z[7]);
+                }
+            } else {
+                // gradient-only pass: nothing paces these warps but the single Rsp buffer — wait until GEMM2(q-1)
+                // has consumed it (the MMA warp commits z_full[(q-1)&1] behind that GEMM)
+                if (q >= 1) {
+                    if (!wait_or_fail(sh.z_full + ((q - 1) & 1), zuse[(q - 1) & 1] & 1, sh.fail)) return;
+                    ++zuse[(q - 1) & 1];
+                }
+            }
+            if (!cfg.a && valid) {
+                const float4* zi = (const float4*)cfg.zsrc + 2 * slot;
+                const float4 z0 = zi[0], z1 = zi[1];
+                z[0] = z0.x, z[1] = z0.y, z[2] = z0.z, z[3] = z0.w, z[4] = z1.x, z[5] = z1.y, z[6] = z1.z, z[7] = z1.w;
+            }
+            if (cfg.logits_only) {               // direction pass: the logits are all we wanted
+                tc::tc_fence_before();
+                __syncwarp();
+                if (lane == 0) tc::mbar_arrive(sh.r_full + zb);      // "Z buffer zb read" for the MMA warp
+                continue;
+            }
+            float rr[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+            if (valid) {
                 lsum += softmax_residual(z, bias, labels[slot], R, rr);
 #pragma unroll
                 for (int c = 0; c < 8; ++c) rs[c] += rr[c];
@@ -340,6 +399,11 @@ struct TcEval {
             tc::tc_fence_before();
             __syncwarp();
             if (lane == 0) tc::mbar_arrive(sh.r_full);
+        }
+        if (cfg.logits_only) return;
+        if (!cfg.a && S >= 1) {                  // consume the last "Rsp consumed" commit of a gradient-only pass
+            if (!wait_or_fail(sh.z_full + ((S - 1) & 1), zuse[(S - 1) & 1] & 1, sh.fail)) return;
+            ++zuse[(S - 1) & 1];
         }
         for (int o = 16; o; o >>= 1) {
             lsum += __shfl_xor_sync(0xffffffffu, lsum, o);
@@ -374,58 +438,140 @@ struct TcEval {
         __syncthreads();
     }
 
-    // ---- loss + gradient at x (scaled space); all threads enter, all get the same loss
-    __device__ double eval(const float* x, float* g) { return eval_impl(x, g, false); }
-
-    // fused: x holds the UNSCALED start weights w0 (1/std is not known yet: the statistics warps compute it
-    // during this very pass); the gradient is still returned in the scaled space.
-    __device__ double eval_impl(const float* x, float* g, bool fused) {
+    // ---- one configured pass over the buffer; all threads enter, all get the same loss.
+    // x: the point whose weights feed the logits GEMM (when cfg.a) and whose intercepts enter the softmax.
+    // In the fused pass x holds the UNSCALED start weights w0 (1/std is being computed during the pass).
+    __device__ double run_pass(const float* x, float* g, const PassCfg& cfg) {
         const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-        // Wsp = (x * inv) split into fp16 hi | lo, K-major SWIZZLE_128B, 16 rows per 64-feature chunk
-        for (int f = tid; f < F; f += blockDim.x) {
-            const float4 a = ((const float4*)x)[2 * f], b = ((const float4*)x)[2 * f + 1];
-            const float sc = fused ? 1.f : sh.inv[f];
-            const float w[8] = {a.x * sc, a.y * sc, a.z * sc, a.w * sc, b.x * sc, b.y * sc, b.z * sc, b.w * sc};
-            const int kb = f >> 6, k = f & 63, j = k >> 3, e = k & 7;
-            unsigned char* chunk = sh.sB + (size_t)kb * kBChunkBytes;
+        if (cfg.a) {
+            // Wsp = (x * inv) split into fp16 hi | lo, K-major SWIZZLE_128B, 16 rows per 64-feature chunk
+            for (int f = tid; f < F; f += blockDim.x) {
+                const float4 a = ((const float4*)x)[2 * f], b = ((const float4*)x)[2 * f + 1];
+                const float sc = cfg.fused ? 1.f : sh.inv[f];
+                const float w[8] = {a.x * sc, a.y * sc, a.z * sc, a.w * sc, b.x * sc, b.y * sc, b.z * sc, b.w * sc};
+                const int kb = f >> 6, k = f & 63, j = k >> 3, e = k & 7;
+                unsigned char* chunk = sh.sB + (size_t)kb * kBChunkBytes;
 #pragma unroll
-            for (int c = 0; c < 8; ++c) {
-                __half hi, lo;
-                tc::split_half(w[c], hi, lo);
-                *(__half*)(chunk + tc::sw128_off(c, j) + e * 2) = hi;
-                *(__half*)(chunk + 1024 + tc::sw128_off(c, j) + e * 2) = lo;
+                for (int c = 0; c < 8; ++c) {
+                    __half hi, lo;
+                    tc::split_half(w[c], hi, lo);
+                    *(__half*)(chunk + tc::sw128_off(c, j) + e * 2) = hi;
+                    *(__half*)(chunk + 1024 + tc::sw128_off(c, j) + e * 2) = lo;
+                }
             }
         }
         if (tid < 16) sh.sred[tid] = 0.f;
         if (tid < 8) sh.sred[16 + tid] = x[F * 8 + tid];          // intercepts (unscaled)
-        if (fused)
+        if (cfg.fused)
             for (int f = tid; f < F; f += blockDim.x) sh.inv[f] = 0.f, ((float*)(sh.sR + kRBytes))[f] = 0.f;
         tc::fence_proxy_async_smem();
         __syncthreads();
         const float invn = 1.f / (float)count;
         if (warp == 0) {
-            if (lane == 0) produce(true, fused);
+            if (lane == 0) produce(cfg);
             __syncwarp();
         } else if (warp == 1) {
 #ifdef PSB_TC_PROFILE
             const long long tm0 = clock64();
 #endif
-            mma_loop();
+            mma_loop(cfg);
 #ifdef PSB_TC_PROFILE
             prof[3] += clock64() - tm0;
 #endif
             __syncwarp();
         } else if (warp < 6) {
-            epilogue(warp & 3, lane, g, invn, fused);
-        } else if (fused) {
+            epilogue(warp & 3, lane, g, invn, cfg);
+        } else if (cfg.fused) {
             stats_fused(warp - 6, lane);
         }
         __syncthreads();
-        if (tid == 0) *sh.chunk_base += 2u * (unsigned)num_active_slabs() * (F / kBlockK);
-        if (tid < 8) g[F * 8 + tid] = sh.sred[1 + tid] * invn;
+        if (tid == 0)
+            *sh.chunk_base += (unsigned)((cfg.a ? 1 : 0) + (cfg.b ? 1 : 0)) * (unsigned)num_active_slabs() * (F / kBlockK);
+        if (cfg.b && tid < 8) g[F * 8 + tid] = sh.sred[1 + tid] * invn;
         const double loss = (double)sh.sred[0] * (double)invn;
         __syncthreads();
         return loss;
+    }
+
+    // classic interface: loss + gradient at x (scaled space), one A+B pass
+    __device__ double eval(const float* x, float* g) {
+        const PassCfg cfg = {true, true, false, false, Zx, nullptr};   // keeps the logit cache current when there is one
+        return run_pass(x, g, cfg);
+    }
+    __device__ double eval_store(const float* x, float* g, float* zbuf) {     // A+B pass, logits parked in zbuf
+        const PassCfg cfg = {true, true, false, false, zbuf, nullptr};
+        return run_pass(x, g, cfg);
+    }
+    __device__ double eval_first_fused(const float* w0, float* g) {
+        const PassCfg cfg = {true, true, true, false, Zx, nullptr};
+        return run_pass(w0, g, cfg);
+    }
+
+    // ---- cached-logit interface used by local_solve_cached (solver.cuh)
+    __device__ void logits_of_direction(const float* d) {          // Zd = X (d * inv): A stream only
+        const PassCfg cfg = {true, false, false, true, Zd, nullptr};
+        run_pass(d, nullptr, cfg);
+    }
+    // the Zd buffer holds the logits of x + t1 d: turn it into z(d) = (Zt - Zx) / t1 (logits are linear)
+    __device__ void derive_direction_logits(double t1) {
+        const float it = (float)(1.0 / t1);
+        for (int i = threadIdx.x; i < count; i += blockDim.x) {
+            int slot = start + i;
+            if (slot >= cap) slot -= cap;
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+                const float4 a = ((const float4*)Zx)[2 * slot + h];
+                float4 b = ((float4*)Zd)[2 * slot + h];
+                b.x = (b.x - a.x) * it, b.y = (b.y - a.y) * it, b.z = (b.z - a.z) * it, b.w = (b.w - a.w) * it;
+                ((float4*)Zd)[2 * slot + h] = b;
+            }
+        }
+        __syncthreads();
+    }
+    __device__ void gradient_at(const float* x, float* g) {        // residuals from Zx, G = X^T R: B stream only
+        const PassCfg cfg = {false, true, false, false, nullptr, Zx};
+        run_pass(x, g, cfg);
+    }
+    // phi(t) and phi'(t) of the line search from the cached logits: z = Zx + t Zd (+ intercepts of x + t d)
+    __device__ void trial(double t, const float* x, const float* d, double& f, double& dd) {
+        const float ft = (float)t;
+        float bias[8], bd[8];
+#pragma unroll
+        for (int c = 0; c < 8; ++c) bd[c] = d[F * 8 + c], bias[c] = fmaf(ft, bd[c], x[F * 8 + c]);
+        float lsum = 0.f, dsum = 0.f;
+        for (int i = threadIdx.x; i < count; i += blockDim.x) {
+            int slot = start + i;
+            if (slot >= cap) slot -= cap;
+            const float4 a0 = ((const float4*)Zx)[2 * slot], a1 = ((const float4*)Zx)[2 * slot + 1];
+            const float4 d0 = ((const float4*)Zd)[2 * slot], d1 = ((const float4*)Zd)[2 * slot + 1];
+            const float zd[8] = {d0.x, d0.y, d0.z, d0.w, d1.x, d1.y, d1.z, d1.w};
+            const float z[8] = {fmaf(ft, zd[0], a0.x), fmaf(ft, zd[1], a0.y), fmaf(ft, zd[2], a0.z), fmaf(ft, zd[3], a0.w),
+                                fmaf(ft, zd[4], a1.x), fmaf(ft, zd[5], a1.y), fmaf(ft, zd[6], a1.z), fmaf(ft, zd[7], a1.w)};
+            float rr[8];
+            lsum += softmax_residual(z, bias, labels[slot], R, rr);
+#pragma unroll
+            for (int c = 0; c < 8; ++c) dsum = fmaf(rr[c], zd[c] + bd[c], dsum);
+        }
+        const double n = (double)count;
+        f = block_sum((double)lsum, sh.red) / n;
+        dd = block_sum((double)dsum, sh.red) / n;
+#ifdef PSB_TC_DEBUG
+        if (blockIdx.x == 0 && threadIdx.x == 0) printf("trial t=%g f=%g dd=%g\n", t, f, dd);
+#endif
+    }
+    __device__ void advance(double alpha) {                        // Zx <- Zx + alpha Zd
+        const float fa = (float)alpha;
+        for (int i = threadIdx.x; i < count; i += blockDim.x) {
+            int slot = start + i;
+            if (slot >= cap) slot -= cap;
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+                float4 a = ((float4*)Zx)[2 * slot + h];
+                const float4 b = ((const float4*)Zd)[2 * slot + h];
+                a.x = fmaf(fa, b.x, a.x), a.y = fmaf(fa, b.y, a.y), a.z = fmaf(fa, b.z, a.z), a.w = fmaf(fa, b.w, a.w);
+                ((float4*)Zx)[2 * slot + h] = a;
+            }
+        }
     }
 };
 }  // namespace
@@ -467,7 +613,7 @@ psb_worker_tc_kernel(const __grid_constant__ CUtensorMap tmX, PsbSolver sv, Comm
         s_fail = 0, s_chunk_base = 0, s_need_redo = 0;
         tc::tma_prefetch_desc(&tmX);
         for (int s = 0; s < kNS; ++s) tc::mbar_init(sh.full + s, 1), tc::mbar_init(sh.empty + s, 1);
-        for (int i = 0; i < 2; ++i) tc::mbar_init(sh.z_full + i, 1), tc::mbar_init(sh.r_full + i, 4);   // r_full[1] unused
+        for (int i = 0; i < 2; ++i) tc::mbar_init(sh.z_full + i, 1), tc::mbar_init(sh.r_full + i, 4);
         tc::mbar_init(sh.g_full, 1);
         for (int s = 0; s < kNS; ++s) tc::mbar_init(sh.sdone + s, 1);
         tc::mbar_init(sh.inv_ready, 2);
@@ -513,6 +659,11 @@ psb_worker_tc_kernel(const __grid_constant__ CUtensorMap tmX, PsbSolver sv, Comm
         ev.start = start, ev.count = count, ev.cap = cap, ev.F = F, ev.R = R, ev.kNS = kNS;
         ev.tmem = tmem, ev.sh = sh;
         ev.zuse[0] = ev.zuse[1] = ev.ruse[0] = ev.ruse[1] = ev.guse = 0;
+        // logit cache in two spare solver vectors (the L-BFGS pairs of index PSB_HIST-1 are never reached when
+        // max_iter <= PSB_HIST-1): [cap][8] floats each must fit one parameter vector
+        const bool cached = sv.solver == PSB_SOLVER_LBFGS && cap * 8 <= nv && sv.max_iter <= PSB_HIST - 1;
+        ev.Zx = cached ? ws.vec[7 + PSB_HIST - 1] : nullptr;
+        ev.Zd = cached ? ws.vec[7 + 2 * PSB_HIST - 1] : nullptr;
 #ifdef PSB_TC_PROFILE
         ev.prof[0] = ev.prof[1] = ev.prof[2] = ev.prof[3] = 0;
 #endif
@@ -525,7 +676,7 @@ psb_worker_tc_kernel(const __grid_constant__ CUtensorMap tmX, PsbSolver sv, Comm
         bool have_f0 = false;
         double f0 = 0.0;
         if (sv.standardize) {
-            f0 = ev.eval_impl(w0, v.g, true);
+            f0 = ev.eval_first_fused(w0, v.g);
             have_f0 = !s_need_redo;
         } else {
             ev.unit_scale();
@@ -534,7 +685,13 @@ psb_worker_tc_kernel(const __grid_constant__ CUtensorMap tmX, PsbSolver sv, Comm
         to_scaled_space(v.x, w0, sh.inv, F);
         __syncthreads();
 
-        SolveResult res = local_solve(ev, v, sv.solver, sv.max_iter, sv.sgd_lr, sh.red, have_f0, f0);
+        SolveResult res;
+        if (cached) {
+            if (!have_f0) f0 = ev.eval(v.x, v.g);                    // (also fills the logit cache)
+            res = local_solve_cached(ev, v, sv.max_iter, sh.red, f0);
+        } else {
+            res = local_solve(ev, v, sv.solver, sv.max_iter, sv.sgd_lr, sh.red, have_f0, f0);
+        }
         const long long t_solve = clock64();
 
         float* delta = v.tmp;

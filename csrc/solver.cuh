@@ -88,17 +88,17 @@ __device__ __forceinline__ Bracket ls_phi(Eval& ev, SolveVecs& v, double t, doub
     return b;
 }
 
-// Returns true and the accepted step (whose gradient is in v.gt, value in f_out) or false.
-template <class Eval>
-__device__ bool strong_wolfe(Eval& ev, SolveVecs& v, double f0, double dd0, double init, double* red, int& evals,
-                             double& alpha, double& f_out) {
+// Strong-Wolfe line search on a scalar function phi(t) -> Bracket{t, phi'(t), phi(t)}.
+// Returns true and the accepted step (value in f_out) or false.
+template <class Phi>
+__device__ bool strong_wolfe_phi(Phi& phi, double f0, double dd0, double init, double& alpha, double& f_out) {
     if (dd0 > 0.0) return false;
     double t = init;
     Bracket low = {0.0, dd0, f0};
     Bracket lo, hi;
     bool zoom = false;
     for (int i = 0; i < PSB_LS_MAX_ITER; ++i) {
-        Bracket c = ls_phi(ev, v, t, red, evals);
+        Bracket c = phi(t);
         if (isinf(c.f) || isnan(c.f)) {
             t *= 0.5;
             continue;
@@ -121,7 +121,7 @@ __device__ bool strong_wolfe(Eval& ev, SolveVecs& v, double f0, double dd0, doub
     if (!zoom) return false;
     for (int i = 0; i < PSB_LS_MAX_ZOOM; ++i) {
         const double tz = lo.t > hi.t ? ls_interp(hi, lo) : ls_interp(lo, hi);
-        Bracket c = ls_phi(ev, v, tz, red, evals);
+        Bracket c = phi(tz);
         if (c.f > f0 + PSB_LS_C1 * c.t * dd0 || c.f >= lo.f) {
             hi = c;
         } else {
@@ -134,6 +134,133 @@ __device__ bool strong_wolfe(Eval& ev, SolveVecs& v, double f0, double dd0, doub
         }
     }
     return false;
+}
+
+// The classic form: every trial is a full loss/gradient evaluation at x + t d (gradient left in v.gt).
+template <class Eval>
+__device__ bool strong_wolfe(Eval& ev, SolveVecs& v, double f0, double dd0, double init, double* red, int& evals,
+                             double& alpha, double& f_out) {
+    auto phi = [&](double t) { return ls_phi(ev, v, t, red, evals); };
+    return strong_wolfe_phi(phi, f0, dd0, init, alpha, f_out);
+}
+
+// d = -H g by the two-loop recursion over the `hist` newest pairs (newest at index 0).  False on a bad pair.
+__device__ inline bool lbfgs_direction(SolveVecs& v, int hist, double* red) {
+    double a[PSB_HIST], rho[PSB_HIST];
+    vec_scale_copy(v.d, v.g, 1.0, v.n4);
+    __syncthreads();
+    double diag = 1.0;
+    if (hist > 0) {
+        const double sy = block_dot(v.s[0], v.y[0], v.n4, red);
+        const double yy = block_dot(v.y[0], v.y[0], v.n4, red);
+        if (sy < 0.0 || isnan(sy)) return false;
+        diag = sy / yy;
+    }
+    for (int i = 0; i < hist; ++i) {
+        rho[i] = block_dot(v.s[i], v.y[i], v.n4, red);
+        a[i] = block_dot(v.s[i], v.d, v.n4, red) / rho[i];
+        vec_axpy_to(v.d, v.d, -a[i], v.y[i], v.n4);
+        __syncthreads();
+    }
+    vec_scale_copy(v.d, v.d, diag, v.n4);
+    __syncthreads();
+    for (int i = hist - 1; i >= 0; --i) {
+        const double beta = block_dot(v.y[i], v.d, v.n4, red) / rho[i];
+        vec_axpy_to(v.d, v.d, a[i] - beta, v.s[i], v.n4);
+        __syncthreads();
+    }
+    vec_scale_copy(v.d, v.d, -1.0, v.n4);
+    __syncthreads();
+    return true;
+}
+
+// L-BFGS for evaluators that cache the logits.  The logits are linear in the parameters,
+// z(x + t d) = z(x) + t z(d), which makes every line-search trial after the first one free:
+//   * the first trial of an iteration is a full evaluation at x + t1 d (loss, gradient, and its logits Zt);
+//     when the line search accepts it — the common case — the iteration costs exactly what the classic
+//     solver pays, and Zt simply becomes the cached logits of the new point;
+//   * when it is rejected, z(d) = (Zt - Zx) / t1 comes out of the two cached logit sets without touching the
+//     data, every further trial is an O(rows x classes) update (Eval::trial), and only the accepted point
+//     pays one more pass for its gradient (Eval::gradient_at) — none at all in the last iteration.
+// Same line search on the same phi as local_solve, so the same iterates up to rounding.
+// On entry: v.x = start point, v.g = gradient there, f0 = loss there, logits of v.x cached by the evaluator.
+template <class Eval>
+__device__ SolveResult local_solve_cached(Eval& ev, SolveVecs& v, int max_iter, double* red, double f0) {
+    SolveResult r;
+    r.evals = 1, r.iterations = 0, r.status = 0;
+    double f = f0;
+    int hist = 0;
+    const double tol = 1e-6;
+    for (int it = 0; it < max_iter; ++it) {
+        const double gnorm = sqrt(block_dot(v.g, v.g, v.n4, red));
+        if (gnorm <= fmax(tol * fabs(f), 1e-8)) {
+            r.status = 1;
+            break;
+        }
+        bool ok = lbfgs_direction(v, hist, red);
+        double alpha = 0.0, f_new = f, t_first = 0.0;
+        bool derived = false;
+        int calls = 0;
+        if (ok) {
+            const double dd0 = block_dot(v.g, v.d, v.n4, red);
+            const double dn = sqrt(block_dot(v.d, v.d, v.n4, red));
+            auto phi = [&](double t) {
+                ++r.evals;
+                Bracket b;
+                b.t = t;
+                if (calls++ == 0) {                                       // full evaluation, logits parked in Zd
+                    vec_axpy_to(v.xt, v.x, t, v.d, v.n4);
+                    __syncthreads();
+                    b.f = ev.eval_store(v.xt, v.gt, ev.Zd);
+                    b.dd = block_dot(v.gt, v.d, v.n4, red);
+                    t_first = t;
+                    if (isinf(b.f) || isnan(b.f)) calls = 0;              // unusable logits: evaluate fully again
+                } else {
+                    if (!derived) {
+                        ev.derive_direction_logits(t_first);              // Zd <- (Zt - Zx) / t_first
+                        derived = true;
+                    }
+                    ev.trial(t, v.x, v.d, b.f, b.dd);                     // no pass over the data
+                }
+                return b;
+            };
+            ok = strong_wolfe_phi(phi, f, dd0, it == 0 ? 1.0 / dn : 1.0, alpha, f_new);
+            if (ok && alpha * gnorm < 1e-10) ok = false;
+        }
+        if (!ok) {
+            r.status = 2;
+            break;
+        }
+        const bool need_grad = it + 1 < max_iter;
+        if (!derived) {                                                   // the fully evaluated trial was accepted
+            float* z = ev.Zx;
+            ev.Zx = ev.Zd, ev.Zd = z;                                     // its logits are the new point's logits
+        } else {
+            vec_axpy_to(v.xt, v.x, alpha, v.d, v.n4);
+            ev.advance(alpha);                                            // cached logits move to x + alpha d
+            __syncthreads();
+            if (need_grad) ev.gradient_at(v.xt, v.gt);                    // one pass: gradient at the new point
+        }
+        if (need_grad) {
+            for (int i = (hist < PSB_HIST - 2 ? hist : PSB_HIST - 2); i > 0; --i) {   // shift pairs, newest first
+                float* ps = v.s[i];
+                float* py = v.y[i];
+                v.s[i] = v.s[i - 1], v.y[i] = v.y[i - 1], v.s[i - 1] = ps, v.y[i - 1] = py;
+            }
+            vec_sub_to(v.s[0], v.xt, v.x, v.n4);
+            vec_sub_to(v.y[0], v.gt, v.g, v.n4);
+            __syncthreads();
+            if (hist < PSB_HIST - 1) ++hist;
+            float* p = v.g;
+            v.g = v.gt, v.gt = p;
+        }
+        float* p = v.x;
+        v.x = v.xt, v.xt = p;
+        f = f_new;
+        r.iterations = it + 1;
+    }
+    r.loss = f;
+    return r;
 }
 
 // On entry v.x holds the start point.  On exit v.x holds the result.
@@ -160,35 +287,7 @@ __device__ SolveResult local_solve(Eval& ev, SolveVecs& v, int solver, int max_i
             r.status = 1;
             break;
         }
-        // ---- two-loop recursion: d = -H g
-        double a[PSB_HIST], rho[PSB_HIST];
-        vec_scale_copy(v.d, v.g, 1.0, v.n4);
-        __syncthreads();
-        bool bad = false;
-        double diag = 1.0;
-        if (hist > 0) {
-            const double sy = block_dot(v.s[0], v.y[0], v.n4, red);
-            const double yy = block_dot(v.y[0], v.y[0], v.n4, red);
-            if (sy < 0.0 || isnan(sy)) bad = true;
-            diag = sy / yy;
-        }
-        if (!bad) {
-            for (int i = 0; i < hist; ++i) {
-                rho[i] = block_dot(v.s[i], v.y[i], v.n4, red);
-                a[i] = block_dot(v.s[i], v.d, v.n4, red) / rho[i];
-                vec_axpy_to(v.d, v.d, -a[i], v.y[i], v.n4);
-                __syncthreads();
-            }
-            vec_scale_copy(v.d, v.d, diag, v.n4);
-            __syncthreads();
-            for (int i = hist - 1; i >= 0; --i) {
-                const double beta = block_dot(v.y[i], v.d, v.n4, red) / rho[i];
-                vec_axpy_to(v.d, v.d, a[i] - beta, v.s[i], v.n4);
-                __syncthreads();
-            }
-            vec_scale_copy(v.d, v.d, -1.0, v.n4);
-            __syncthreads();
-        }
+        const bool bad = !lbfgs_direction(v, hist, red);
         double alpha = 0.0, f_new = f;
         bool ok = !bad;
         if (ok) {
