@@ -74,10 +74,9 @@ __device__ __forceinline__ bool wait_or_fail(uint64_t* bar, uint32_t parity, vol
 // What one pass over the buffer does.  a: A stream + logits GEMM; b: B stream + gradient GEMM;
 // fused: standardisation statistics ride on the A stream (first evaluation only);
 // zstore: the epilogue also stores the raw logits (no intercept) of every valid row there;
-// zsrc: residuals come from cached logits instead of TMEM (gradient-only pass);
-// logits_only: the epilogue stops after storing the logits (direction pass).
+// zsrc: residuals come from cached logits instead of TMEM (gradient-only pass).
 struct PassCfg {
-    bool a, b, fused, logits_only;
+    bool a, b, fused;
     float* zstore;
     const float* zsrc;
 };
@@ -306,19 +305,10 @@ struct TcEval {
             }
             return true;
         };
-        // Logits-only pass: Z buffer q&1 is rewritten by GEMM1(q+2), so before issuing GEMM1(q) wait until the
-        // epilogue has read slab q-2 out of it.  Two barriers (r_full[q&1]) so that a barrier never completes
-        // two phases between two waits of this warp (mbarrier waits carry one parity bit).
-        auto z_read = [&](int q) -> bool {
-            if (!wait_or_fail(sh.r_full + (q & 1), ruse[q & 1] & 1, sh.fail)) return false;
-            ++ruse[q & 1];
-            return true;
-        };
         for (int q = 0; q < S; ++q) {
 #ifdef PSB_TC_PROFILE
             const long long tg = clock64();
 #endif
-            if (!cfg.b && q >= 2 && !z_read(q - 2)) return;
             if (cfg.a && !gemm1(q)) return;
 #ifdef PSB_TC_PROFILE
             prof[1] += clock64() - tg;
@@ -328,10 +318,6 @@ struct TcEval {
                 if (tc::elect_one()) tc::umma_commit(sh.z_full + (q & 1));
                 __syncwarp();
             }
-        }
-        if (!cfg.b) {
-            if (S >= 2 && !z_read(S - 2)) return;
-            if (S >= 1 && !z_read(S - 1)) return;
         }
         if (cfg.b && tc::elect_one()) tc::umma_commit(sh.g_full);
         __syncwarp();
@@ -375,12 +361,6 @@ struct TcEval {
                 const float4 z0 = zi[0], z1 = zi[1];
                 z[0] = z0.x, z[1] = z0.y, z[2] = z0.z, z[3] = z0.w, z[4] = z1.x, z[5] = z1.y, z[6] = z1.z, z[7] = z1.w;
             }
-            if (cfg.logits_only) {               // direction pass: the logits are all we wanted
-                tc::tc_fence_before();
-                __syncwarp();
-                if (lane == 0) tc::mbar_arrive(sh.r_full + zb);      // "Z buffer zb read" for the MMA warp
-                continue;
-            }
             float rr[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
             if (valid) {
                 lsum += softmax_residual(z, bias, labels[slot], R, rr);
@@ -400,7 +380,6 @@ struct TcEval {
             __syncwarp();
             if (lane == 0) tc::mbar_arrive(sh.r_full);
         }
-        if (cfg.logits_only) return;
         if (!cfg.a && S >= 1) {                  // consume the last "Rsp consumed" commit of a gradient-only pass
             if (!wait_or_fail(sh.z_full + ((S - 1) & 1), zuse[(S - 1) & 1] & 1, sh.fail)) return;
             ++zuse[(S - 1) & 1];
@@ -495,23 +474,19 @@ struct TcEval {
 
     // classic interface: loss + gradient at x (scaled space), one A+B pass
     __device__ double eval(const float* x, float* g) {
-        const PassCfg cfg = {true, true, false, false, Zx, nullptr};   // keeps the logit cache current when there is one
+        const PassCfg cfg = {true, true, false, Zx, nullptr};   // keeps the logit cache current when there is one
         return run_pass(x, g, cfg);
     }
     __device__ double eval_store(const float* x, float* g, float* zbuf) {     // A+B pass, logits parked in zbuf
-        const PassCfg cfg = {true, true, false, false, zbuf, nullptr};
+        const PassCfg cfg = {true, true, false, zbuf, nullptr};
         return run_pass(x, g, cfg);
     }
     __device__ double eval_first_fused(const float* w0, float* g) {
-        const PassCfg cfg = {true, true, true, false, Zx, nullptr};
+        const PassCfg cfg = {true, true, true, Zx, nullptr};
         return run_pass(w0, g, cfg);
     }
 
     // ---- cached-logit interface used by local_solve_cached (solver.cuh)
-    __device__ void logits_of_direction(const float* d) {          // Zd = X (d * inv): A stream only
-        const PassCfg cfg = {true, false, false, true, Zd, nullptr};
-        run_pass(d, nullptr, cfg);
-    }
     // the Zd buffer holds the logits of x + t1 d: turn it into z(d) = (Zt - Zx) / t1 (logits are linear)
     __device__ void derive_direction_logits(double t1) {
         const float it = (float)(1.0 / t1);
@@ -529,7 +504,7 @@ struct TcEval {
         __syncthreads();
     }
     __device__ void gradient_at(const float* x, float* g) {        // residuals from Zx, G = X^T R: B stream only
-        const PassCfg cfg = {false, true, false, false, nullptr, Zx};
+        const PassCfg cfg = {false, true, false, nullptr, Zx};
         run_pass(x, g, cfg);
     }
     // phi(t) and phi'(t) of the line search from the cached logits: z = Zx + t Zd (+ intercepts of x + t d)
