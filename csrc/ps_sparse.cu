@@ -91,15 +91,14 @@ __global__ void __launch_bounds__(256) psb_sparse_step_kernel(SparseComm c, int 
                 sum += p[cc];
             }
             const int y = labels[row];
-            float py = 0.f;
+            float ey = 1.f;
 #pragma unroll
             for (int cc = 0; cc < 8; ++cc) {
-                const float q = p[cc] / sum;
-                if (cc == y) py = q;
-                r[cc] = q - (cc == y ? 1.f : 0.f);
+                if (cc == y) ey = p[cc];
+                r[cc] = p[cc] / sum - (cc == y ? 1.f : 0.f);
             }
             if (lane == 0) {
-                lsum += -__logf(fmaxf(py, 1e-30f));
+                lsum += __logf(sum) - __logf(fmaxf(ey, 1e-37f));
                 if (Rbuf) {
                     ((float4*)Rbuf)[2 * row] = make_float4(r[0], r[1], r[2], r[3]);
                     ((float4*)Rbuf)[2 * row + 1] = make_float4(r[4], r[5], r[6], r[7]);
@@ -345,15 +344,14 @@ __global__ void __launch_bounds__(256) psb_slab_step_kernel(SlabComm c, unsigned
             sum += p[cc];
         }
         const int y = labels[row];
-        float py = 0.f;
+        float ey = 1.f;
 #pragma unroll
         for (int cc = 0; cc < 8; ++cc) {
-            const float qv = p[cc] / sum;
-            if (cc == y) py = qv;
-            r[cc] = qv - (cc == y ? 1.f : 0.f);
+            if (cc == y) ey = p[cc];
+            r[cc] = p[cc] / sum - (cc == y ? 1.f : 0.f);
         }
         if (lane == 0) {
-            lsum += -__logf(fmaxf(py, 1e-30f));
+            lsum += __logf(sum) - __logf(fmaxf(ey, 1e-37f));
 #pragma unroll
             for (int cc = 0; cc < 8; ++cc) bg[cc] += r[cc];
         }

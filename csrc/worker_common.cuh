@@ -21,11 +21,12 @@ struct WorkerScratch {
 // z: raw logits without intercept (8 values, pads ignored); b: intercepts; returns -log p[label] and the
 // residual r = p - onehot(label) (pads 0).  Softmax over the R class rows only (class 0 included: Q4).
 __device__ __forceinline__ float softmax_residual(const float* z, const float* b, int label, int R, float* r) {
-    float v[8], m = -INFINITY;
+    float v[8], m = -INFINITY, vy = 0.f;
 #pragma unroll
     for (int c = 0; c < 8; ++c) {
         v[c] = c < R ? z[c] + b[c] : -INFINITY;
         m = fmaxf(m, v[c]);
+        if (c == label) vy = v[c];
     }
     float sum = 0.f;
 #pragma unroll
@@ -34,14 +35,9 @@ __device__ __forceinline__ float softmax_residual(const float* z, const float* b
         sum += v[c];
     }
     const float is = 1.f / sum;
-    float py = 0.f;
 #pragma unroll
-    for (int c = 0; c < 8; ++c) {
-        const float p = v[c] * is;
-        if (c == label) py = p;
-        r[c] = p - (c == label ? 1.f : 0.f);
-    }
-    return -__logf(fmaxf(py, 1e-30f));
+    for (int c = 0; c < 8; ++c) r[c] = v[c] * is - (c == label ? 1.f : 0.f);
+    return __logf(sum) - (vy - m);          // log-sum-exp form: exact even when p[label] underflows
 }
 
 // inv[f] = 1/std_f over the window (unbiased, zeros included) or 0 when the variance is 0 (Q5);

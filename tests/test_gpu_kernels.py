@@ -188,3 +188,25 @@ def test_apply_delta_and_q1_compat():
     r2 = ref.copy()
     r2[64 * 8 + 5] = w.cpu().numpy()[64 * 8 + 5]
     assert np.allclose(w2.cpu().numpy(), r2, atol=1e-7)
+
+
+@pytest.mark.parametrize("impl", IMPLS)
+@pytest.mark.parametrize("scale", [5.0, 20.0])
+def test_lbfgs2_many_line_search_trials(impl, scale):
+    """Far-off start weights make the strong-Wolfe search take several trials per iteration (6 and 10 loss
+    evaluations per solve in the oracle); the tcgen05 kernel serves all but the first trial of an iteration
+    from cached logits and must still walk the oracle's path."""
+    native = _native()
+    F, cap, n = 1024, 128, 128
+    lay = LogRegLayout(F, 5)
+    gen = ReviewGenerator(F, 5, mean_len=400.0)
+    b = _half_batch(gen.train_split(256)).slice(np.arange(n))
+    W0 = lay.random(3, scale)
+    delta, loss, info = _run_step(native, [b], W0, F, cap, "lbfgs2", impl, standardize=False, center=False)
+    t = LogisticRegressionTask(F, 5, None, "lbfgs2", standardize=False, center=False)
+    t.set_weights(W0)
+    d = t.calculate_gradients(b, eval_test=False)
+    assert t.last_info.num_evals > 4                           # the scenario this test is about
+    assert info[0, 0] == t.last_info.num_evals and info[0, 1] == 2 and info[0, 2] == 0
+    assert abs(loss[0] - t.loss) < 5e-3 * max(1.0, abs(t.loss))
+    assert np.abs(delta[0] - d).max() < 2e-2 * np.abs(d).max()
