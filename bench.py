@@ -140,6 +140,7 @@ def main():
     dev = torch.device("cuda", local)
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        os.environ.setdefault("NCCL_DEBUG", "WARN")          # keep stdout to the one JSON line
         dist.init_process_group("nccl", device_id=dev)
     native.lib()
     impl = {"simt": native.IMPL_SIMT, "tc": native.IMPL_TC}.get(a.kernel)
@@ -267,7 +268,7 @@ def main():
                        "cycles64_stats_solve_push_total": [float(info[:, k].mean()) for k in (4, 5, 6, 7)],
                        "mean_loss": float(np.nanmean(loss))},
         }
-        print(json.dumps(out))
+        print(json.dumps(out), flush=True)
     eng.close()
     if world > 1:
         dist.destroy_process_group()
