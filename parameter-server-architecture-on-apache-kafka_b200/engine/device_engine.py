@@ -190,15 +190,6 @@ class DeviceEngine:
         torch.cuda.current_stream().wait_event(self.ingest_done)
         self._keep = (stage, stage_dev)          # pinned source must outlive the async copy
 
-    def ingest_slots(self, rows_f16: torch.Tensor, labels: torch.Tensor, worker_slot: torch.Tensor,
-                     win: torch.Tensor, wait: bool = True) -> None:
-        """Same as ingest() with the (worker, slot) table and the new windows precomputed (bench hot path)."""
-        n = rows_f16.shape[0]
-        self._tables_free()
-        self.stage_ws_host[:n].copy_(worker_slot)
-        self.win_host.copy_(win)
-        self._ingest_staged(rows_f16, labels, n, wait)
-
     def _tables_free(self) -> None:
         """The pinned (worker, slot) and window tables are shared by both staging sets: wait until the copies
         that read them have completed before the host rewrites them."""
