@@ -64,6 +64,21 @@ unsigned int* psb_comm_status(void* d_block, int num_features, int num_ranks) {
     return CommBlock(d_block, CommLayout::make(num_features, num_ranks)).status();
 }
 
+// Reads the block's status word (synchronises the stream): 0, or PSB_E_TIMEOUT with the reason in psb_last_error().
+int psb_comm_check(void* d_block, int num_features, int num_ranks, void* stream) {
+    PSB_REQUIRE(d_block, "psb_comm_check: null block");
+    unsigned int st = 0;
+    PSB_CHECK_CUDA(cudaMemcpyAsync(&st, CommBlock(d_block, CommLayout::make(num_features, num_ranks)).status(), 4,
+                                   cudaMemcpyDeviceToHost, (cudaStream_t)stream));
+    PSB_CHECK_CUDA(cudaStreamSynchronize((cudaStream_t)stream));
+    if (st == 0) return 0;
+    psb_set_error("in-kernel wait gave up (status %u: %s)", st,
+                  st == PSB_ERR_PULL_TIMEOUT ? "the weights of this clock never arrived — a peer stopped pushing"
+                  : st == PSB_ERR_GATE_TIMEOUT ? "the bounded-delay clock gate never opened — a peer fell behind and stopped"
+                                               : "unknown");
+    return PSB_E_TIMEOUT;
+}
+
 size_t psb_worker_scratch_bytes(int num_features) {
     return (size_t)PSB_SCRATCH_VECS * (num_features + 1) * PSB_CLASS_PAD * sizeof(float);
 }

@@ -81,6 +81,9 @@ float* psb_comm_replica(void* d_block, int num_features, int num_ranks, int pari
 float* psb_comm_shard_weights(void* d_block, int num_features, int num_ranks);
 unsigned int* psb_comm_status(void* d_block, int num_features, int num_ranks);   /* [0]=error flag, [1..]=debug */
 
+/* 0, or PSB_E_TIMEOUT when an in-kernel wait of this rank gave up (synchronises `stream`) */
+int psb_comm_check(void* d_block, int num_features, int num_ranks, void* stream);
+
 size_t psb_worker_scratch_bytes(int num_features);                               /* per worker */
 
 /* One parameter-server iteration for `num_workers` local workers (one CTA each):

@@ -299,6 +299,10 @@ class DeviceEngine:
         _view(st + 768, 64, self.device, torch.int32).copy_(words)
         torch.cuda.synchronize(self.device)
 
+    def check(self) -> None:
+        """Raises NativeError (PSB_E_TIMEOUT) if an in-kernel wait of this rank gave up; synchronises."""
+        native.check(native.lib().psb_comm_check(self.block, self.F, self.world, native._stream()), "psb_comm_check")
+
     def status(self) -> int:
         ptr = native.lib().psb_comm_status(self.block, self.F, self.world)
         return int(_view(ptr, 1, self.device, torch.int32).item())

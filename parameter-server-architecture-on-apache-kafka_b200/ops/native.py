@@ -79,6 +79,7 @@ def lib() -> C.CDLL:
     for name in ("psb_comm_shard_weights", "psb_comm_status"):
         getattr(L, name).restype = C.c_void_p
         getattr(L, name).argtypes = [vp, C.c_int, C.c_int]
+    L.psb_comm_check.argtypes = [vp, C.c_int, C.c_int, vp]
     L.psb_worker_scratch_bytes.restype = C.c_size_t
     L.psb_worker_scratch_bytes.argtypes = [C.c_int]
     L.psb_worker_step.argtypes = [C.POINTER(PsbSolver), C.POINTER(PsbComm), C.c_int, C.c_int, vp, ip, ip, fp, fp, fp,

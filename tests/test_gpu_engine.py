@@ -99,3 +99,22 @@ def test_cuda_backend_tracks_numpy_backend():
     assert logs[0].shape == logs[1].shape == (6, 6)
     assert np.abs(logs[0][:, 4] - logs[1][:, 4]).max() < 0.01          # F1 within a point at every clock
     assert np.abs(logs[0][:, 5] - logs[1][:, 5]).max() < 0.01
+
+
+def test_missing_peer_raises_timeout_instead_of_hanging():
+    """A rank whose peer never pushes: the in-kernel wait gives up after its cycle budget and the host sees
+    PSB_E_TIMEOUT with a readable reason (failure detection)."""
+    from psb200.engine.device_engine import DeviceEngine
+    from psb200.ops import native
+    cfg = PSConfig(num_workers=2, num_features=256, max_buffer_size=128, min_buffer_size=16)
+    a = DeviceEngine(cfg, 1, 0, 2, impl=0, spin_limit_cycles=20_000_000)       # ~10 ms budget
+    b = DeviceEngine(cfg, 1, 1, 2, impl=0)
+    a.set_peers([a.block, b.block]), b.set_peers([a.block, b.block])
+    rows = torch.zeros((1, 128, 256), dtype=torch.float16, device="cuda")
+    rows[:, :, 0] = 1.0
+    a.fill(rows, torch.ones((1, 128), dtype=torch.int32, device="cuda"))
+    a.step()                      # clock 0: pushes, nobody else does
+    a.step()                      # clock 1: waits for weights that never come
+    with pytest.raises(native.NativeError, match="never arrived"):
+        a.check()
+    a.close(), b.close()
