@@ -41,6 +41,8 @@ def parse():
     p.add_argument("--solver", default="lbfgs2", choices=["lbfgs2", "sgd"])
     p.add_argument("--consistency_model", type=int, default=0)
     p.add_argument("--ingest_rows", type=int, default=128, help="new rows per worker per step in the e2e run")
+    p.add_argument("--ingest_format", choices=["bitmap", "dense"], default="bitmap",
+                   help="e2e wire format of the fresh rows: presence bitmap + fp16 non-zeros (lossless) or dense fp16")
     p.add_argument("--no_e2e", action="store_true")
     p.add_argument("--events_per_min", type=float, default=0.0,
                    help="e2e run: per-worker arrival rate used for the dynamic buffer size bc x events/min (0: unthrottled -> max)")
@@ -206,6 +208,8 @@ def main():
                      for _ in range(pool)]
         host_rows = [(r / r.norm(dim=1, keepdim=True).clamp_min(1e-6)).half().pin_memory() for r in host_rows]
         host_lab = [torch.randint(1, 6, (n_new,), generator=g, dtype=torch.int32).pin_memory() for _ in range(pool)]
+        if a.ingest_format == "bitmap":           # what the producer hands over: bitmap-packed rows in pinned memory
+            host_rows = [native.PackedRows(n_new, F).pack_dense(r, l) for r, l in zip(host_rows, host_lab)]
         workers = np.repeat(np.arange(W, dtype=np.int32), a.ingest_rows)
         # arrival timestamps drive the dynamic buffer size: target = clamp(bc * events_per_minute, min, max)
         gap_ms = 60000.0 / a.events_per_min if a.events_per_min > 0 else 0.0
@@ -216,16 +220,18 @@ def main():
             tick[0] += 1
             return base + np.tile(np.arange(a.ingest_rows) * gap_ms, W)
 
-        # Software pipeline through the public API: the host->device copy of batch i+1 (ingest_begin) is in
-        # flight while step i trains; ingest_commit scatters it into the rings between two steps.  Every step
-        # still pays its own H2D (pinned host -> device) and its own D2H read of the losses.
+        # Software pipeline through the public API: the host->device copies of batches i+1 and i+2
+        # (ingest_begin, copy stream, three staging sets) are in flight while step i trains; ingest_commit stores
+        # batch i into the rings between two steps.  Every step still pays its own H2D (pinned host -> device)
+        # and its own D2H read of the losses.
         def one(i):
             eng.ingest_commit()                                                            # batch i -> rings
-            eng.ingest_begin(host_rows[(i + 1) % pool], host_lab[(i + 1) % pool], workers, stamps())   # H2D of i+1
-            eng.step()
+            eng.step()                                                                     # enqueue clock i
+            eng.ingest_begin(host_rows[(i + 2) % pool], host_lab[(i + 2) % pool], workers, stamps())   # H2D of i+2
             return eng.read_loss()                                                        # D2H of the result
 
         eng.ingest_begin(host_rows[0], host_lab[0], workers, stamps())
+        eng.ingest_begin(host_rows[1], host_lab[1], workers, stamps())
         for i in range(a.warmup):
             one(i)
         barrier()
@@ -246,7 +252,7 @@ def main():
                "buffer_rows_effective": rows_eff, "events_per_min_per_worker": a.events_per_min,
                "h2d_bytes_per_step": (eng.h2d_bytes - h0) // a.steps, "d2h_bytes_per_step": W * 4,
                "ms_per_step": ems / a.steps, "ingested_samples_per_sec": n_new * world * a.steps / (ems / 1000.0),
-               "new_rows_per_worker_per_step": a.ingest_rows}
+               "new_rows_per_worker_per_step": a.ingest_rows, "ingest_format": a.ingest_format}
 
     clocks = sampler.stop() if rank == 0 else None       # sampled across both timed regions
     if rank == 0:

@@ -21,6 +21,8 @@ int psb_launch_eval_tc(const void*, const int*, int, const float*, int, int, int
 int psb_launch_eval_finalize(const int*, float*, cudaStream_t);
 int psb_launch_ring_scatter(const uint32_t*, int, int, void*, int*, int, int, cudaStream_t);
 int psb_launch_ring_store_dense(const void*, int, const int*, const int*, int, void*, int*, int, int, cudaStream_t);
+int psb_launch_ring_store_bitmap(const uint32_t*, const int*, const void*, const int*, const int*, int, void*, int*, int, int,
+                                 cudaStream_t);
 int psb_launch_apply_delta(float*, const float*, float, int, int, cudaStream_t);
 
 extern "C" {
@@ -148,6 +150,16 @@ int psb_ring_store_dense(const void* d_rows, int src_half, const int* d_labels_i
     PSB_REQUIRE(num_features % 8 == 0, "num_features must be a multiple of 8");
     return psb_launch_ring_store_dense(d_rows, src_half, d_labels_in, d_worker_slot, n, d_X, d_labels, cap,
                                        num_features, (cudaStream_t)stream);
+}
+
+int psb_ring_store_bitmap(const uint32_t* d_bitmap, const int* d_row_off, const void* d_values, const int* d_labels_in,
+                          const int* d_worker_slot, int n, void* d_X, int* d_labels, int cap, int num_features,
+                          void* stream) {
+    PSB_REQUIRE(d_bitmap && d_row_off && d_values && d_labels_in && d_worker_slot && d_X && d_labels,
+                "psb_ring_store_bitmap: null pointer");
+    PSB_REQUIRE(num_features % 32 == 0, "psb_ring_store_bitmap: num_features must be a multiple of 32");
+    return psb_launch_ring_store_bitmap(d_bitmap, d_row_off, d_values, d_labels_in, d_worker_slot, n, d_X, d_labels, cap,
+                                        num_features, (cudaStream_t)stream);
 }
 
 // Random 32-byte row traffic (sharded sparse path): ask L2 to fetch 32-byte sectors instead of promoting every

@@ -213,7 +213,8 @@ namespace {
 struct Buffer {
     int min_size, max_size, window;
     float bc;
-    std::deque<double> deltas;
+    std::vector<double> deltas;          // circular: the last `window` inter-arrival times
+    int n_deltas = 0, pos = 0;
     double total = 0.0, last = -1.0;
     bool has_last = false;
     int head = 0, count = 0;
@@ -225,6 +226,7 @@ extern "C" void* psb_buffer_create(int min_size, int max_size, float bc, int win
     if (min_size < 1 || max_size < min_size) return nullptr;
     Buffer* b = new Buffer();
     b->min_size = min_size, b->max_size = max_size, b->bc = bc, b->window = window > 0 ? window : 500;
+    b->deltas.assign((size_t)b->window, 0.0);
     return b;
 }
 extern "C" void psb_buffer_destroy(void* b) { delete (Buffer*)b; }
@@ -236,25 +238,25 @@ extern "C" int psb_buffer_on_event(void* bp, double now_ms, int* head, int* coun
         b->has_last = true;
     } else {
         const double d = now_ms - b->last;
-        b->deltas.push_back(d);
+        if (b->n_deltas == b->window) b->total -= b->deltas[b->pos];
+        else ++b->n_deltas;
+        b->deltas[b->pos] = d;
         b->total += d;
-        if ((int)b->deltas.size() > b->window) {
-            b->total -= b->deltas.front();
-            b->deltas.pop_front();
-        }
+        if (++b->pos == b->window) b->pos = 0;
     }
     b->last = now_ms;
-    const double mean = b->deltas.empty() ? 1000.0 : b->total / (double)b->deltas.size();
     int calc;
-    if (mean <= 0.0) {
+    if (b->n_deltas == 0) {
+        calc = (int)floor((double)b->bc * 60.0 + 0.5);      // no history yet: mean inter-arrival taken as 1000 ms
+    } else if (b->total <= 0.0) {
         calc = b->max_size;                       // Q8: infinite rate clamps to max (reference: min)
     } else {
-        const double v = (double)b->bc * (60000.0 / mean);
-        calc = std::isfinite(v) ? (int)floor(v + 0.5) : b->max_size;
+        const double v = (double)b->bc * (60000.0 / (b->total / (double)b->n_deltas));
+        calc = std::isfinite(v) ? (v >= 2.0e9 ? b->max_size : (int)floor(v + 0.5)) : b->max_size;
     }
     const int tgt = std::max(b->min_size, std::min(b->max_size, calc));
     const int slot = b->head;
-    b->head = (b->head + 1) % b->max_size;
+    if (++b->head == b->max_size) b->head = 0;
     b->count = std::min(b->count + 1, tgt);
     b->inserted++;
     *head = b->head, *count = b->count, *target = tgt;
@@ -430,4 +432,68 @@ extern "C" void psb_producer_stop(void* h) {
     P->stop.store(1);
     if (P->th.joinable()) P->th.join();
     delete P;
+}
+
+// ------------------------------------------------------------------ bitmap packing (host side of psb_ring_store_bitmap)
+extern "C" long long psb_pack_bitmap_dense(const uint16_t* rows, long long n_rows, int F, uint32_t* out_bitmap,
+                                           int* out_row_off, uint16_t* out_values) {
+    if (!rows || !out_bitmap || !out_row_off || !out_values || F % 32 != 0) {
+        psb_set_error("psb_pack_bitmap_dense: null pointer or num_features not a multiple of 32");
+        return -1;
+    }
+    const int words = F / 32;
+    long long k = 0;
+    for (long long r = 0; r < n_rows; ++r) {
+        const uint16_t* row = rows + (size_t)r * F;
+        out_row_off[r] = (int)k;
+        for (int w = 0; w < words; ++w) {
+            uint32_t bits = 0;
+            for (int b = 0; b < 32; ++b) {
+                const uint16_t h = row[w * 32 + b];
+                if (h & 0x7fffu) {                       // +0.0 and -0.0 are both "absent"
+                    bits |= 1u << b;
+                    out_values[k++] = h;
+                }
+            }
+            out_bitmap[(size_t)r * words + w] = bits;
+        }
+    }
+    out_row_off[n_rows] = (int)k;
+    return k;
+}
+
+extern "C" long long psb_pack_bitmap_csr(const long long* indptr, const int* indices, const float* values,
+                                         long long n_rows, int F, uint32_t* out_bitmap, int* out_row_off,
+                                         uint16_t* out_values) {
+    if (!indptr || !indices || !values || !out_bitmap || !out_row_off || !out_values || F % 32 != 0) {
+        psb_set_error("psb_pack_bitmap_csr: null pointer or num_features not a multiple of 32");
+        return -1;
+    }
+    const int words = F / 32;
+    std::vector<uint16_t> dense((size_t)F);
+    long long k = 0;
+    for (long long r = 0; r < n_rows; ++r) {
+        // column order of the source is not trusted: go through a dense scratch row (F is small)
+        std::fill(dense.begin(), dense.end(), (uint16_t)0);
+        for (long long e = indptr[r]; e < indptr[r + 1]; ++e) {
+            const int c = indices[e];
+            if (c < 0 || c >= F) continue;
+            const __half h = __float2half(values[e]);
+            memcpy(&dense[c], &h, 2);
+        }
+        out_row_off[r] = (int)k;
+        for (int w = 0; w < words; ++w) {
+            uint32_t bits = 0;
+            for (int b = 0; b < 32; ++b) {
+                const uint16_t h = dense[w * 32 + b];
+                if (h & 0x7fffu) {
+                    bits |= 1u << b;
+                    out_values[k++] = h;
+                }
+            }
+            out_bitmap[(size_t)r * words + w] = bits;
+        }
+    }
+    out_row_off[n_rows] = (int)k;
+    return k;
 }

@@ -54,6 +54,53 @@ __global__ void __launch_bounds__(256) psb_ring_store_dense_kernel(const float* 
     }
 }
 
+// Bitmap-packed rows (the sparse wire format of ingestion): per row F/32 presence words, an offset into one
+// contiguous fp16 value stream, values in feature order.  One warp expands one row: lane l owns presence
+// word l of every 32-word group, a warp scan of the popcounts gives it its position in the value stream, and
+// it writes its 32 features (64 bytes) of the dense ring row.  Lossless with respect to the fp16 ring.
+__global__ void __launch_bounds__(256) psb_ring_store_bitmap_kernel(const uint32_t* __restrict__ bitmap,
+                                                                   const int* __restrict__ row_off,
+                                                                   const __half* __restrict__ values,
+                                                                   const int* __restrict__ labels_in,
+                                                                   const int* __restrict__ worker_slot, int n,
+                                                                   __half* __restrict__ X, int* __restrict__ labels,
+                                                                   int cap, int F) {
+    const int lane = threadIdx.x & 31, wpb = blockDim.x >> 5;
+    const int words = F >> 5;
+    for (int r = blockIdx.x * wpb + (threadIdx.x >> 5); r < n; r += gridDim.x * wpb) {
+        const int worker = worker_slot[2 * r], slot = worker_slot[2 * r + 1];
+        __half* dst = X + ((size_t)worker * cap + slot) * F;
+        int base = row_off[r];
+        for (int w0 = 0; w0 < words; w0 += 32) {
+            const int w = w0 + lane;
+            const uint32_t bits = w < words ? bitmap[(size_t)r * words + w] : 0u;
+            const int cnt = __popc(bits);
+            int incl = cnt;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const int t = __shfl_up_sync(0xffffffffu, incl, o);
+                if (lane >= o) incl += t;
+            }
+            const __half* v = values + base + (incl - cnt);
+            if (w < words) {
+                __align__(16) __half out[32];
+                int k = 0;
+#pragma unroll
+                for (int b = 0; b < 32; ++b) {
+                    const bool on = (bits >> b) & 1u;
+                    out[b] = on ? v[k] : __float2half_rn(0.f);
+                    k += on;
+                }
+                uint4* d16 = (uint4*)(dst + (size_t)w * 32);
+#pragma unroll
+                for (int q = 0; q < 4; ++q) d16[q] = ((const uint4*)out)[q];
+            }
+            base += __shfl_sync(0xffffffffu, incl, 31);
+        }
+        if (lane == 0) labels[(size_t)worker * cap + slot] = labels_in[r];
+    }
+}
+
 __global__ void psb_apply_delta_kernel(float* __restrict__ w, const float* __restrict__ delta, float lr, int n4,
                                        int skip_index) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -83,6 +130,16 @@ int psb_launch_ring_store_dense(const void* d_rows, int src_half, const int* d_l
     else
         psb_ring_store_dense_kernel<<<grid, 256, 0, stream>>>((const float*)d_rows, d_labels_in, d_ws, n,
                                                                (__half*)d_X, d_labels, cap, F);
+    PSB_CHECK_CUDA(cudaGetLastError());
+    return 0;
+}
+int psb_launch_ring_store_bitmap(const uint32_t* d_bitmap, const int* d_row_off, const void* d_values,
+                                 const int* d_labels_in, const int* d_ws, int n, void* d_X, int* d_labels, int cap, int F,
+                                 cudaStream_t stream) {
+    if (n <= 0) return 0;
+    const int blocks = (n + 7) / 8;
+    psb_ring_store_bitmap_kernel<<<blocks < 2368 ? blocks : 2368, 256, 0, stream>>>(
+        d_bitmap, d_row_off, (const __half*)d_values, d_labels_in, d_ws, n, (__half*)d_X, d_labels, cap, F);
     PSB_CHECK_CUDA(cudaGetLastError());
     return 0;
 }

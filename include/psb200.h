@@ -184,7 +184,23 @@ int psb_ring_scatter(const uint32_t* d_stage, int n, int stride_words, void* d_X
 int psb_ring_store_dense(const void* d_rows, int src_half, const int* d_labels_in, const int* d_worker_slot, int n,
                          void* d_X, int* d_labels, int cap, int num_features, void* stream);
 
+/* Bitmap-packed rows -> ring slots: d_bitmap [n][F/32] presence words (bit b of word w = feature 32w+b),
+ * d_row_off [n] = index of the row's first value in d_values (fp16, feature order).  The sparse wire format
+ * of LabeledData (LabeledData.java:14-28) without the keys: 128 B + 2 B per non-zero at F = 1024. */
+int psb_ring_store_bitmap(const uint32_t* d_bitmap, const int* d_row_off, const void* d_values,
+                          const int* d_labels_in, const int* d_worker_slot, int n, void* d_X, int* d_labels,
+                          int cap, int num_features, void* stream);
+
 /* ---------------------------------------------------------------- host runtime (C++) */
+/* CSR (sorted or unsorted column indices, fp32 values) -> bitmap-packed rows with fp16 values (host side of
+ * psb_ring_store_bitmap).  out_bitmap [n][F/32], out_row_off [n+1], out_values: uint16 fp16 bits, capacity
+ * indptr[n].  Explicit zeros and out-of-range columns are dropped.  Returns the number of values written. */
+long long psb_pack_bitmap_csr(const long long* indptr, const int* indices, const float* values, long long n_rows,
+                              int num_features, uint32_t* out_bitmap, int* out_row_off, uint16_t* out_values);
+/* the same from dense fp16 rows [n][F] (uint16 bit patterns; -0.0 counts as zero) */
+long long psb_pack_bitmap_dense(const uint16_t* rows, long long n_rows, int num_features, uint32_t* out_bitmap,
+                                int* out_row_off, uint16_t* out_values);
+
 /* CSV -> CSR tokenizer (CsvProducer.java:46-58).  Two-pass: count, then fill. */
 int psb_csv_count(const char* path, int has_header, long long* n_rows, long long* n_nnz, int* n_cols);
 int psb_csv_parse(const char* path, int has_header, long long* indptr, int* indices, float* values,

@@ -36,7 +36,7 @@ from ..ops import native
 class DeviceEngine:
     def __init__(self, cfg: PSConfig, workers_per_rank: int, rank: int = 0, world: int = 1, impl: int = native.IMPL_SIMT,
                  device: Optional[torch.device] = None, w0: Optional[np.ndarray] = None, stage_rows: int = 0,
-                 spin_limit_cycles: int = 20_000_000_000):
+                 stage_sets: int = 3, spin_limit_cycles: int = 20_000_000_000):
         if not torch.cuda.is_available():
             raise native.NativeError("DeviceEngine needs a CUDA device")
         native.lib()
@@ -70,22 +70,29 @@ class DeviceEngine:
         self.peers[rank] = self.block
         native.check(native.lib().psb_comm_init_block(self.block, self.w0.data_ptr(), F, world, rank,
                                                       native._stream()), "psb_comm_init_block")
-        # ingestion: host-side window bookkeeping + pinned staging + side stream
+        # ingestion: host-side window bookkeeping + a ring of staging sets.  begin() fills set `head` over the
+        # copy stream, commit() drains set `tail` into the rings over the ingest stream; with S sets the H2D of
+        # batch k+S-1 overlaps the step that trains on batch k.
         self.buffers = [native.NativeBuffer(cfg.min_buffer_size, cap, cfg.buffer_size_coefficient)
                         for _ in range(self.W)]
+        self._buf_handles = None
         self.rows_ingested = 0
         self.stage_rows = stage_rows or self.W * 128
-        self.stage_host = torch.zeros((self.stage_rows, F), dtype=torch.float16).pin_memory()
-        self.stage_lab_host = torch.zeros(self.stage_rows, dtype=torch.int32).pin_memory()
-        self.stage_ws_host = torch.zeros((self.stage_rows, 2), dtype=torch.int32).pin_memory()
-        # two device staging sets: the H2D of batch k+1 overlaps the step that trains on batch k
-        self.stage_dev = [torch.zeros((self.stage_rows, F), dtype=torch.float16, device=dev) for _ in range(2)]
-        self.stage_lab_dev = [torch.zeros(self.stage_rows, dtype=torch.int32, device=dev) for _ in range(2)]
-        self.stage_ws_dev = [torch.zeros((self.stage_rows, 2), dtype=torch.int32, device=dev) for _ in range(2)]
-        self.stage_win_dev = [torch.zeros((self.W, 2), dtype=torch.int32, device=dev) for _ in range(2)]
-        self.stage_n = [0, 0]
-        self.stage_slot = 0
-        self.h2d_done = [torch.cuda.Event(), torch.cuda.Event()]
+        S = self.stage_sets = max(2, int(stage_sets))
+        self.stage_ws_host = [torch.zeros((self.stage_rows, 2), dtype=torch.int32).pin_memory() for _ in range(S)]
+        self.stage_win_host = [torch.zeros((self.W, 2), dtype=torch.int32).pin_memory() for _ in range(S)]
+        self.stage_dev = [torch.zeros((self.stage_rows, F), dtype=torch.float16, device=dev) for _ in range(S)]
+        self.stage_lab_dev = [torch.zeros(self.stage_rows, dtype=torch.int32, device=dev) for _ in range(S)]
+        self.stage_ws_dev = [torch.zeros((self.stage_rows, 2), dtype=torch.int32, device=dev) for _ in range(S)]
+        self.stage_win_dev = [torch.zeros((self.W, 2), dtype=torch.int32, device=dev) for _ in range(S)]
+        self.stage_bitmap_dev = self.stage_off_dev = None            # allocated on the first packed batch
+        self.stage_csr_dev = [None] * S                              # (device rows, stride) of an ingest_sparse batch
+        self.stage_kind = ["dense"] * S
+        self.stage_n = [0] * S
+        self.stage_head = self.stage_tail = self.stage_pending = 0
+        self.h2d_done = [torch.cuda.Event() for _ in range(S)]       # copies of set j have landed
+        self.store_done = [torch.cuda.Event() for _ in range(S)]     # set j has been drained into the rings
+        self.copy_stream = torch.cuda.Stream(device=dev)
         self.ingest_stream = torch.cuda.Stream(device=dev)
         self.ingest_done = torch.cuda.Event()
         self.h2d_bytes = 0
@@ -141,6 +148,7 @@ class DeviceEngine:
         self.labels[:, :n].copy_(labels)
         self.buffers = [native.NativeBuffer(self.cfg.min_buffer_size, self.cap, self.cfg.buffer_size_coefficient)
                         for _ in range(self.W)]
+        self._buf_handles = None
         for b in self.buffers:                      # replay n unthrottled arrivals so the host mirror agrees
             for _ in range(n):
                 b.on_event(0.0)
@@ -148,100 +156,119 @@ class DeviceEngine:
         self.win_host[:, 1] = n
         self.win.copy_(self.win_host)
 
-    def ingest(self, rows_f16: torch.Tensor, labels: torch.Tensor, workers: np.ndarray,
+    def ingest(self, rows_f16, labels: Optional[torch.Tensor], workers: np.ndarray,
                now_ms: Optional[np.ndarray] = None, wait: bool = True) -> None:
-        """Stream `n` new rows (pinned fp16 [n, F] + int32 labels) to their workers' rings.
+        """Stream `n` new rows (pinned fp16 [n, F] + int32 labels, or a ``native.PackedRows``) to their workers' rings.
 
         Host: slot per row from the dynamic-buffer policy; device: one H2D of the rows, one of the
-        (worker, slot) table, one scatter kernel — all on the ingestion stream.
+        (worker, slot) table, one store kernel — on the copy / ingestion streams.
         """
-        n = rows_f16.shape[0]
-        assert n <= self.stage_rows, "ingest batch larger than the staging ring"
-        if now_ms is None:
-            now_ms = np.zeros(n, dtype=np.float64)
-        self._tables_free()
-        native.buffers_on_batch(self.buffers, workers[:n], now_ms[:n], self.stage_ws_host.numpy(),
-                                self.win_host.numpy())
-        self._ingest_staged(rows_f16, labels, n, wait)
-
-    def ingest_sparse(self, batch: CSRBatch, workers: np.ndarray, now_ms: Optional[np.ndarray] = None) -> None:
-        """ingest() for sparse rows: ships (index, value) records instead of dense fp16 rows and lets
-        ``psb_ring_scatter`` expand them on the device — fewer PCIe bytes below ~25 % density."""
-        from ..data.csr import pack_stage_rows
-        n = len(batch)
-        if now_ms is None:
-            now_ms = np.zeros(n, dtype=np.float64)
-        self._tables_free()
-        native.buffers_on_batch(self.buffers, workers[:n], now_ms[:n], self.stage_ws_host.numpy(),
-                                self.win_host.numpy())
-        stage = torch.from_numpy(pack_stage_rows(batch, self.stage_ws_host.numpy()[:n]).view(np.int32)).pin_memory()
-        s = self.ingest_stream
-        s.wait_stream(torch.cuda.current_stream())
-        with torch.cuda.stream(s):
-            stage_dev = stage.to(self.device, non_blocking=True)
-            self.win.copy_(self.win_host, non_blocking=True)
-            native.ring_scatter(stage_dev, n, stage.shape[1], self.X, self.labels, self.cap, self.F, stream=s)
-            self.ingest_done.record(s)
-            self.h2d_done[self.stage_slot].record(s)
-        stage_dev.record_stream(s)
-        self.kernel_launches += 1
-        self.rows_ingested += n
-        self.h2d_bytes += stage.numel() * 4 + self.W * 8
-        torch.cuda.current_stream().wait_event(self.ingest_done)
-        self._keep = (stage, stage_dev)          # pinned source must outlive the async copy
-
-    def _tables_free(self) -> None:
-        """The pinned (worker, slot) and window tables are shared by both staging sets: wait until the copies
-        that read them have completed before the host rewrites them."""
-        self.h2d_done[0].synchronize()
-        self.h2d_done[1].synchronize()
-
-    def _ingest_staged(self, rows_f16, labels, n, wait) -> None:
-        self._h2d(rows_f16, labels, n)
+        self.ingest_begin(rows_f16, labels, workers, now_ms)
         self.ingest_commit(wait)
 
-    def _h2d(self, rows_f16, labels, n) -> int:
-        """Async copies of one batch (rows, labels, slot table, new windows) into a free staging set."""
-        j = self.stage_slot
-        s = self.ingest_stream
-        with torch.cuda.stream(s):
-            self.stage_dev[j][:n].copy_(rows_f16[:n], non_blocking=True)
-            self.stage_lab_dev[j][:n].copy_(labels[:n], non_blocking=True)
-            self.stage_ws_dev[j][:n].copy_(self.stage_ws_host[:n], non_blocking=True)
-            self.stage_win_dev[j].copy_(self.win_host, non_blocking=True)
-            self.h2d_done[j].record(s)
-        self.stage_n[j] = n
-        self.rows_ingested += n
-        self.h2d_bytes += n * self.F * 2 + n * 4 + n * 8 + self.W * 8
-        return j
+    def ingest_sparse(self, batch: CSRBatch, workers: np.ndarray, now_ms: Optional[np.ndarray] = None) -> None:
+        """ingest() for CSR rows: ships (index, value) records and lets ``psb_ring_scatter`` expand them on the
+        device (fewer PCIe bytes than dense fp16 below ~25 % density; see PackedRows for the denser case)."""
+        from ..data.csr import pack_stage_rows
+        n = len(batch)
+        j = self._begin_set(n, workers, now_ms)
+        stage = torch.from_numpy(pack_stage_rows(batch, self.stage_ws_host[j].numpy()[:n]).view(np.int32)).pin_memory()
+        with torch.cuda.stream(self.copy_stream):
+            stage_dev = stage.to(self.device, non_blocking=True)
+            self.stage_win_dev[j].copy_(self.stage_win_host[j], non_blocking=True)
+            self.h2d_done[j].record(self.copy_stream)
+        stage_dev.record_stream(self.ingest_stream)
+        self.stage_csr_dev[j] = (stage_dev, stage.shape[1], stage)     # pinned source must outlive the async copy
+        self._end_set(j, n, "csr", stage.numel() * 4 + self.W * 8)
+        self.ingest_commit()
 
-    def ingest_begin(self, rows_f16: torch.Tensor, labels: torch.Tensor, workers: np.ndarray,
-                     now_ms: Optional[np.ndarray] = None) -> None:
-        """First half of ingest(): slot assignment + host->device copies into the staging area.  Does not
-        touch the rings, so it may run while a step is training on them (pipelined ingestion)."""
-        n = rows_f16.shape[0]
-        assert n <= self.stage_rows, "ingest batch larger than the staging ring"
+    def _begin_set(self, n: int, workers: np.ndarray, now_ms: Optional[np.ndarray]) -> int:
+        """Claim staging set `head`: assign ring slots to the n rows (dynamic-buffer policy) and snapshot the
+        windows they produce into the set's pinned tables."""
+        assert n <= self.stage_rows, "ingest batch larger than a staging set"
+        if self.stage_pending == self.stage_sets:
+            raise native.NativeError("ingest_begin: every staging set holds an uncommitted batch; call ingest_commit")
+        j = self.stage_head
+        self.h2d_done[j].synchronize()                      # the set's pinned tables are free again
         if now_ms is None:
             now_ms = np.zeros(n, dtype=np.float64)
-        self._tables_free()
-        native.buffers_on_batch(self.buffers, workers[:n], now_ms[:n], self.stage_ws_host.numpy(),
-                                self.win_host.numpy())
-        self._h2d(rows_f16, labels, n)
+        if self._buf_handles is None:
+            self._buf_handles = native.buffer_handles(self.buffers)
+        native.buffers_on_batch(self.buffers, workers[:n], now_ms[:n], self.stage_ws_host[j].numpy(),
+                                self.win_host.numpy(), handles=self._buf_handles)
+        self.stage_win_host[j].copy_(self.win_host)
+        self.copy_stream.wait_event(self.store_done[j])     # the set's device buffers have been drained
+        return j
+
+    def _end_set(self, j: int, n: int, kind: str, nbytes: int) -> None:
+        self.stage_n[j], self.stage_kind[j] = n, kind
+        self.stage_head = (j + 1) % self.stage_sets
+        self.stage_pending += 1
+        self.rows_ingested += n
+        self.h2d_bytes += nbytes
+
+    def ingest_begin(self, rows_f16, labels: Optional[torch.Tensor], workers: np.ndarray,
+                     now_ms: Optional[np.ndarray] = None) -> None:
+        """First half of ingest(): slot assignment + host->device copies into a staging set.  Does not touch
+        the rings, so it may run while a step is training on them; up to ``stage_sets`` batches may be begun
+        ahead of their ingest_commit (pipelined ingestion).
+
+        ``rows_f16`` is either pinned fp16 [n, F] (with ``labels``) or a ``native.PackedRows`` batch (bitmap +
+        fp16 values; ``labels`` ignored) — the packed form moves 128 B + 2 B per non-zero per row over PCIe."""
+        packed = isinstance(rows_f16, native.PackedRows)
+        n = rows_f16.n if packed else rows_f16.shape[0]
+        j = self._begin_set(n, workers, now_ms)
+        s = self.copy_stream
+        with torch.cuda.stream(s):
+            if packed:
+                pk = rows_f16
+                assert pk.F == self.F
+                if self.stage_bitmap_dev is None:
+                    self.stage_bitmap_dev = [torch.zeros((self.stage_rows, self.F // 32), dtype=torch.int32,
+                                                         device=self.device) for _ in range(self.stage_sets)]
+                    self.stage_off_dev = [torch.zeros(self.stage_rows + 1, dtype=torch.int32, device=self.device)
+                                          for _ in range(self.stage_sets)]
+                self.stage_dev[j].view(-1)[:pk.nnz].copy_(pk.values[:pk.nnz], non_blocking=True)
+                self.stage_bitmap_dev[j][:n].copy_(pk.bitmap[:n], non_blocking=True)
+                self.stage_off_dev[j][:n + 1].copy_(pk.row_off[:n + 1], non_blocking=True)
+                self.stage_lab_dev[j][:n].copy_(pk.labels[:n], non_blocking=True)
+                nbytes = pk.nbytes
+            else:
+                self.stage_dev[j][:n].copy_(rows_f16[:n], non_blocking=True)
+                self.stage_lab_dev[j][:n].copy_(labels[:n], non_blocking=True)
+                nbytes = n * self.F * 2 + n * 4
+            self.stage_ws_dev[j][:n].copy_(self.stage_ws_host[j][:n], non_blocking=True)
+            self.stage_win_dev[j].copy_(self.stage_win_host[j], non_blocking=True)
+            self.h2d_done[j].record(s)
+        self._end_set(j, n, "bitmap" if packed else "dense", nbytes + n * 8 + self.W * 8)
 
     def ingest_commit(self, wait: bool = True) -> None:
-        """Second half: scatter the staged batch into the rings (after the running step, before the next)."""
-        j = self.stage_slot
+        """Second half: store the oldest begun batch into the rings (after the running step, before the next)."""
+        if self.stage_pending == 0:
+            return
+        j = self.stage_tail
         n = self.stage_n[j]
         s = self.ingest_stream
         torch.cuda.nvtx.range_push("psb.ingest_commit")
         s.wait_stream(torch.cuda.current_stream())          # the previous step must be done with the rings
+        s.wait_event(self.h2d_done[j])
         with torch.cuda.stream(s):
             self.win.copy_(self.stage_win_dev[j], non_blocking=True)
-            native.ring_store_dense(self.stage_dev[j], self.stage_lab_dev[j], self.stage_ws_dev[j], n, self.X,
-                                    self.labels, self.cap, self.F, stream=s)
+            if self.stage_kind[j] == "bitmap":
+                native.ring_store_bitmap(self.stage_bitmap_dev[j], self.stage_off_dev[j], self.stage_dev[j],
+                                         self.stage_lab_dev[j], self.stage_ws_dev[j], n, self.X, self.labels, self.cap,
+                                         self.F, stream=s)
+            elif self.stage_kind[j] == "csr":
+                stage_dev, stride, _ = self.stage_csr_dev[j]
+                native.ring_scatter(stage_dev, n, stride, self.X, self.labels, self.cap, self.F, stream=s)
+            else:
+                native.ring_store_dense(self.stage_dev[j], self.stage_lab_dev[j], self.stage_ws_dev[j], n, self.X,
+                                        self.labels, self.cap, self.F, stream=s)
+            self.store_done[j].record(s)
             self.ingest_done.record(s)
         self.kernel_launches += 1
-        self.stage_slot ^= 1
+        self.stage_tail = (j + 1) % self.stage_sets
+        self.stage_pending -= 1
         if wait:
             torch.cuda.current_stream().wait_event(self.ingest_done)
         torch.cuda.nvtx.range_pop()

@@ -98,6 +98,11 @@ def lib() -> C.CDLL:
     L.psb_free.argtypes = [vp]
     L.psb_csv_count.argtypes = [C.c_char_p, C.c_int, C.POINTER(C.c_longlong), C.POINTER(C.c_longlong),
                                 C.POINTER(C.c_int)]
+    L.psb_ring_store_bitmap.argtypes = [vp, ip, vp, ip, ip, C.c_int, vp, ip, C.c_int, C.c_int, vp]
+    L.psb_pack_bitmap_csr.restype = C.c_longlong
+    L.psb_pack_bitmap_csr.argtypes = [vp, vp, vp, C.c_longlong, C.c_int, vp, vp, vp]
+    L.psb_pack_bitmap_dense.restype = C.c_longlong
+    L.psb_pack_bitmap_dense.argtypes = [vp, C.c_longlong, C.c_int, vp, vp, vp]
     L.psb_csv_parse.argtypes = [C.c_char_p, C.c_int, vp, vp, vp, vp, C.c_longlong, C.c_longlong]
     L.psb_tracker_create.restype = C.c_void_p
     L.psb_tracker_create.argtypes = [C.c_int, C.c_int]
@@ -163,6 +168,70 @@ def csv_to_csr(path: str, has_header: bool = True):
     return CSRBatch(indptr, indices[: n_nnz.value], values[: n_nnz.value], labels[: n_rows.value], n_cols.value)
 
 
+class PackedRows:
+    """Bitmap-packed rows in pinned host memory: the sparse wire format of ingestion (presence bitmap +
+    fp16 values in feature order; LabeledData.java:14-28 without the keys).  Lossless w.r.t. the fp16 rings."""
+
+    def __init__(self, max_rows: int, num_features: int, pin: bool = True):
+        import torch
+        assert num_features % 32 == 0, "bitmap packing needs num_features % 32 == 0"
+        self.max_rows, self.F, self.n, self.nnz = max_rows, num_features, 0, 0
+        mk = (lambda *a, **k: torch.zeros(*a, **k).pin_memory()) if pin and torch.cuda.is_available() else torch.zeros
+        self.bitmap = mk((max_rows, num_features // 32), dtype=torch.int32)
+        self.row_off = mk(max_rows + 1, dtype=torch.int32)
+        self.values = mk(max_rows * num_features, dtype=torch.float16)
+        self.labels = mk(max_rows, dtype=torch.int32)
+
+    def pack_dense(self, rows_f16, labels) -> "PackedRows":
+        """rows_f16: torch/numpy fp16 [n, F] on the host."""
+        n = int(rows_f16.shape[0])
+        assert n <= self.max_rows and int(rows_f16.shape[1]) == self.F
+        self.nnz = int(check(lib().psb_pack_bitmap_dense(_ptr(rows_f16), n, self.F, _ptr(self.bitmap),
+                                                         _ptr(self.row_off), _ptr(self.values)), "pack_bitmap_dense"))
+        self.n = n
+        self.labels[:n] = _as_int32_tensor(labels)[:n]
+        return self
+
+    def pack_csr(self, batch) -> "PackedRows":
+        n = len(batch)
+        assert n <= self.max_rows and batch.num_features <= self.F
+        indptr = np.ascontiguousarray(batch.indptr, dtype=np.int64)
+        indices = np.ascontiguousarray(batch.indices, dtype=np.int32)
+        values = np.ascontiguousarray(batch.values, dtype=np.float32)
+        self.nnz = int(check(lib().psb_pack_bitmap_csr(indptr.ctypes.data, indices.ctypes.data, values.ctypes.data, n,
+                                                       self.F, _ptr(self.bitmap), _ptr(self.row_off),
+                                                       _ptr(self.values)), "pack_bitmap_csr"))
+        self.n = n
+        self.labels[:n] = _as_int32_tensor(batch.labels)[:n]
+        return self
+
+    @property
+    def nbytes(self) -> int:
+        """Bytes that cross PCIe for this batch (bitmap + offsets + values + labels)."""
+        return self.n * (self.F // 8) + (self.n + 1) * 4 + self.nnz * 2 + self.n * 4
+
+    def to_dense(self) -> np.ndarray:
+        """Reference expansion on the host (tests)."""
+        out = np.zeros((self.n, self.F), dtype=np.float16)
+        bits = np.unpackbits(self.bitmap[: self.n].numpy().view(np.uint8), axis=1, bitorder="little").astype(bool)
+        out[bits] = self.values[: self.nnz].numpy()
+        return out
+
+
+def _as_int32_tensor(x):
+    import torch
+    if isinstance(x, np.ndarray):
+        return torch.from_numpy(np.ascontiguousarray(x, dtype=np.int32))
+    return x.to(torch.int32)
+
+
+def ring_store_bitmap(bitmap, row_off, values, labels_in, worker_slot, n: int, X, labels, cap: int, num_features: int,
+                      stream=None) -> None:
+    check(lib().psb_ring_store_bitmap(_ptr(bitmap), _ptr(row_off), _ptr(values), _ptr(labels_in), _ptr(worker_slot), n,
+                                      _ptr(X), _ptr(labels), cap, num_features, _stream(stream)),
+          "psb_ring_store_bitmap")
+
+
 class NativeTracker:
     def __init__(self, num_workers: int, consistency_model: int):
         self.n = num_workers
@@ -209,10 +278,16 @@ class NativeBuffer:
             self.h = None
 
 
-def buffers_on_batch(buffers, workers: np.ndarray, now_ms: np.ndarray, worker_slot: np.ndarray, win: np.ndarray):
+def buffer_handles(buffers):
+    """ctypes array of the buffers' handles (build once per buffer set, pass as ``handles=``)."""
+    return (C.c_void_p * len(buffers))(*[b.h for b in buffers])
+
+
+def buffers_on_batch(buffers, workers: np.ndarray, now_ms: np.ndarray, worker_slot: np.ndarray, win: np.ndarray,
+                     handles=None):
     """buffers: list of NativeBuffer; fills worker_slot[n,2] / win[W,2] (int32 numpy views, may be pinned)."""
     n = len(workers)
-    arr = (C.c_void_p * len(buffers))(*[b.h for b in buffers])
+    arr = handles if handles is not None else buffer_handles(buffers)
     workers = np.ascontiguousarray(workers, dtype=np.int32)
     now_ms = np.ascontiguousarray(now_ms, dtype=np.float64)
     check(lib().psb_buffers_on_batch(arr, len(buffers), workers.ctypes.data, now_ms.ctypes.data, n,

@@ -118,3 +118,65 @@ def test_missing_peer_raises_timeout_instead_of_hanging():
     with pytest.raises(native.NativeError, match="never arrived"):
         a.check()
     a.close(), b.close()
+
+
+def test_packed_ingest_equals_dense_ingest():
+    """ingest() with bitmap-packed rows leaves rings, labels and windows identical to the dense fp16 path,
+    through two pipelined batches (both staging sets)."""
+    from psb200.engine.device_engine import DeviceEngine
+    from psb200.ops import native
+    cfg = PSConfig(num_workers=3, num_features=256, max_buffer_size=128, min_buffer_size=16)
+    rng = np.random.default_rng(9)
+    engines = [DeviceEngine(cfg, 3, impl=0, stage_rows=96) for _ in range(2)]
+    for it in range(3):
+        n = 96 - 7 * it
+        rows = torch.from_numpy((rng.standard_normal((n, 256)) * (rng.random((n, 256)) < 0.4)).astype(np.float16)).pin_memory()
+        lab = torch.from_numpy(rng.integers(1, 6, n).astype(np.int32)).pin_memory()
+        workers = rng.integers(0, 3, n).astype(np.int32)
+        engines[0].ingest(rows, lab, workers)
+        engines[1].ingest(native.PackedRows(96, 256).pack_dense(rows, lab), None, workers)
+    torch.cuda.synchronize()
+    a, b = engines
+    assert torch.equal(a.X.view(torch.int16) * (a.X != 0), b.X.view(torch.int16) * (b.X != 0))
+    assert torch.equal(a.labels, b.labels) and torch.equal(a.win, b.win)
+    assert b.h2d_bytes < a.h2d_bytes
+    a.close(), b.close()
+
+
+def test_pipelined_ingest_three_sets_in_order():
+    """Three batches begun ahead of their commits (one per staging set) land in the rings in begin order;
+    a fourth begin without a commit is refused; CSR, dense and packed batches can be mixed."""
+    from psb200.data.synthetic import random_csr
+    from psb200.engine.device_engine import DeviceEngine
+    from psb200.ops import native
+    cfg = PSConfig(num_workers=2, num_features=256, max_buffer_size=128, min_buffer_size=16)
+    rng = np.random.default_rng(2)
+    piped = DeviceEngine(cfg, 2, impl=0, stage_rows=64, stage_sets=3)
+    plain = DeviceEngine(cfg, 2, impl=0, stage_rows=64, stage_sets=2)
+    batches = []
+    for it in range(7):
+        n = 64 - it
+        rows = torch.from_numpy((rng.standard_normal((n, 256)) * (rng.random((n, 256)) < 0.3)).astype(np.float16)).pin_memory()
+        lab = torch.from_numpy(rng.integers(1, 6, n).astype(np.int32)).pin_memory()
+        batches.append((rows, lab, rng.integers(0, 2, n).astype(np.int32)))
+    for rows, lab, wk in batches:
+        plain.ingest(rows, lab, wk)
+    csr = random_csr(20, 256, 25, seed=8)
+    wk_csr = rng.integers(0, 2, 20).astype(np.int32)
+    plain.ingest_sparse(csr, wk_csr)
+
+    for k in range(3):
+        rows, lab, wk = batches[k]
+        piped.ingest_begin(native.PackedRows(64, 256).pack_dense(rows, lab) if k == 1 else rows, lab, wk)
+    with pytest.raises(native.NativeError, match="uncommitted"):
+        piped.ingest_begin(*batches[3])
+    for k in range(3, 7):
+        piped.ingest_commit()
+        piped.ingest_begin(*batches[k])
+    for _ in range(4):
+        piped.ingest_commit()            # the fourth is a no-op
+    piped.ingest_sparse(csr, wk_csr)
+    torch.cuda.synchronize()
+    assert torch.equal(piped.X.view(torch.int16) * (piped.X != 0), plain.X.view(torch.int16) * (plain.X != 0))
+    assert torch.equal(piped.labels, plain.labels) and torch.equal(piped.win, plain.win)
+    piped.close(), plain.close()

@@ -172,6 +172,32 @@ def test_ring_scatter_and_store():
         assert labels[ws[i, 0], ws[i, 1]].item() == b.labels[i] == l2[ws[i, 0], ws[i, 1]].item()
 
 
+@pytest.mark.parametrize("F,density", [(1024, 0.45), (1024, 0.02), (256, 1.0), (2048, 0.3), (96, 0.5)])
+def test_ring_store_bitmap_matches_dense_store(F, density):
+    """Bitmap-packed rows expand to exactly the fp16 ring contents the dense store writes."""
+    native = _native()
+    dev = torch.device("cuda")
+    cap, W, n = 64, 5, 150
+    rng = np.random.default_rng(F)
+    rows = (rng.standard_normal((n, F)) * (rng.random((n, F)) < density)).astype(np.float16)
+    rows[11] = 0
+    labels_in = rng.integers(1, 6, n).astype(np.int32)
+    slots = rng.permutation(W * cap)[:n]
+    ws = np.stack([slots // cap, slots % cap], axis=1).astype(np.int32)
+    pk = native.PackedRows(n + 3, F).pack_dense(rows, labels_in)
+    X = torch.full((W, cap, F), 7.0, dtype=torch.float16, device=dev)       # stale slot contents must be overwritten
+    lab = torch.zeros((W, cap), dtype=torch.int32, device=dev)
+    native.ring_store_bitmap(pk.bitmap.to(dev), pk.row_off.to(dev), pk.values[:max(pk.nnz, 1)].to(dev), pk.labels.to(dev),
+                             torch.from_numpy(ws).to(dev), n, X, lab, cap, F)
+    X2 = torch.full_like(X, 7.0)
+    lab2 = torch.zeros_like(lab)
+    native.ring_store_dense(torch.from_numpy(rows).to(dev), torch.from_numpy(labels_in).to(dev),
+                            torch.from_numpy(ws).to(dev), n, X2, lab2, cap, F)
+    torch.cuda.synchronize()
+    assert torch.equal(X.view(torch.int16), X2.view(torch.int16).where(X2 != 0, torch.zeros_like(X2).view(torch.int16)))
+    assert torch.equal(lab, lab2)
+
+
 def test_apply_delta_and_q1_compat():
     native = _native()
     dev = torch.device("cuda")

@@ -60,3 +60,32 @@ def test_csv_tokenizer_matches_numpy_reader(tmp_path):
         f.write(",".join(["1e-3"] + ["0"] * 126 + ["-2.5E-1"]) + ",4\r\n")
     a = native.csv_to_csr(path)
     assert len(a) == 301 and np.allclose(a.row(300)[1], [1e-3, -0.25]) and a.row(300)[2] == 4
+
+
+def test_bitmap_packers_roundtrip_dense_and_csr():
+    """psb_pack_bitmap_dense / _csr: presence bitmap + fp16 values reproduce the fp16 rows bit for bit
+    (sparse wire format of ingestion; LabeledData.java:14-28)."""
+    from psb200.data.synthetic import random_csr
+    rng = np.random.default_rng(5)
+    F, n = 256, 37
+    dense = (rng.standard_normal((n, F)) * (rng.random((n, F)) < 0.3)).astype(np.float16)
+    dense[3] = 0                                    # an empty row
+    dense[4, 7] = np.float16(-0.0)                  # negative zero is "absent"
+    labels = rng.integers(1, 6, n).astype(np.int32)
+    pk = native.PackedRows(64, F, pin=False).pack_dense(dense, labels)
+    assert pk.n == n and pk.nnz == int((dense != 0).sum())
+    assert np.array_equal(pk.to_dense().view(np.uint16), np.where(dense == 0, np.float16(0), dense).view(np.uint16))
+    assert pk.row_off[:n + 1].tolist() == np.concatenate([[0], np.cumsum((dense != 0).sum(1))]).tolist()
+    assert pk.labels[:n].tolist() == labels.tolist()
+    assert pk.nbytes == n * F // 8 + (n + 1) * 4 + pk.nnz * 2 + n * 4
+
+    b = random_csr(29, F, 20, seed=3)
+    perm = b.indices.copy()                          # unsorted columns inside a row must not matter
+    for r in range(len(b)):
+        a0, a1 = b.indptr[r], b.indptr[r + 1]
+        o = rng.permutation(a1 - a0)
+        perm[a0:a1] = b.indices[a0:a1][o]
+        b.values[a0:a1] = b.values[a0:a1][o]
+    b.indices[:] = perm
+    pk2 = native.PackedRows(32, F, pin=False).pack_csr(b)
+    assert np.array_equal(pk2.to_dense(), b.to_dense(np.float16))
