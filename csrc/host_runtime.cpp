@@ -303,6 +303,9 @@ struct Producer {
     int* labels;
     int* workers;
     double* times;
+    uint32_t* pk_bitmap = nullptr;            // optional: every published batch is also bitmap-packed
+    int* pk_row_off = nullptr;                //   [num_batches][batch_rows + 1]
+    uint16_t* pk_values = nullptr;            //   [num_batches][batch_rows * F]
     std::vector<std::atomic<int>> ready;      // -1 free, >=0 rows published
     std::atomic<long long> rows_sent{0};      // global rows "sent" (all partitions)
     std::atomic<int> eof{0}, stop{0};
@@ -329,6 +332,11 @@ void producer_main(Producer* P) {
     double batch_t0 = 0.0;
     auto publish = [&] {
         if (fill == 0) return;
+        if (P->pk_bitmap)
+            psb_pack_bitmap_dense(P->rows + (size_t)batch * P->batch_rows * P->F, fill, P->F,
+                                  P->pk_bitmap + (size_t)batch * P->batch_rows * (P->F / 32),
+                                  P->pk_row_off + (size_t)batch * (P->batch_rows + 1),
+                                  P->pk_values + (size_t)batch * P->batch_rows * P->F);
         P->ready[batch].store(fill, std::memory_order_release);
         batch = (batch + 1) % P->num_batches, fill = 0;
     };
@@ -396,6 +404,19 @@ void producer_main(Producer* P) {
 extern "C" void* psb_producer_start(const char* path, int has_header, int num_workers_total, int worker_begin,
                                     int worker_count, int num_features, int p_ms, int batch_rows, int num_batches,
                                     void* h_rows_f16, int* h_labels, int* h_workers, double* h_times, int flush_ms) {
+    return psb_producer_start_packed(path, has_header, num_workers_total, worker_begin, worker_count, num_features, p_ms,
+                                     batch_rows, num_batches, h_rows_f16, h_labels, h_workers, h_times, flush_ms, nullptr,
+                                     nullptr, nullptr);
+}
+extern "C" void* psb_producer_start_packed(const char* path, int has_header, int num_workers_total, int worker_begin,
+                                           int worker_count, int num_features, int p_ms, int batch_rows,
+                                           int num_batches, void* h_rows_f16, int* h_labels, int* h_workers,
+                                           double* h_times, int flush_ms, uint32_t* h_bitmap, int* h_row_off,
+                                           void* h_values_f16) {
+    if ((h_bitmap || h_row_off || h_values_f16) && !(h_bitmap && h_row_off && h_values_f16 && num_features % 32 == 0)) {
+        psb_set_error("psb_producer_start_packed: packing needs all three buffers and num_features %% 32 == 0");
+        return nullptr;
+    }
     if (!path || num_workers_total < 1 || worker_count < 1 || batch_rows < 1 || num_batches < 2 || !h_rows_f16) {
         psb_set_error("psb_producer_start: bad arguments");
         return nullptr;
@@ -405,6 +426,7 @@ extern "C" void* psb_producer_start(const char* path, int has_header, int num_wo
     P->wcount = worker_count, P->F = num_features, P->p_ms = p_ms, P->batch_rows = batch_rows;
     P->num_batches = num_batches, P->flush_ms = flush_ms > 0 ? flush_ms : 50;
     P->rows = (uint16_t*)h_rows_f16, P->labels = h_labels, P->workers = h_workers, P->times = h_times;
+    P->pk_bitmap = h_bitmap, P->pk_row_off = h_row_off, P->pk_values = (uint16_t*)h_values_f16;
     P->th = std::thread(producer_main, P);
     return P;
 }

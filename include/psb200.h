@@ -229,6 +229,13 @@ int psb_buffers_on_batch(void** buffers, int num_buffers, const int* workers, co
 void* psb_producer_start(const char* path, int has_header, int num_workers_total, int worker_begin,
                          int worker_count, int num_features, int p_ms, int batch_rows, int num_batches,
                          void* h_rows_f16, int* h_labels, int* h_workers, double* h_times, int flush_ms);
+/* the same, and every published batch is also bitmap-packed by the producer thread (psb_pack_bitmap_dense) into
+ * h_bitmap [num_batches][batch_rows][F/32], h_row_off [num_batches][batch_rows + 1] (row_off[n] = number of
+ * values), h_values_f16 [num_batches][batch_rows * F] — ready for psb_ring_store_bitmap after the H2D. */
+void* psb_producer_start_packed(const char* path, int has_header, int num_workers_total, int worker_begin,
+                                int worker_count, int num_features, int p_ms, int batch_rows, int num_batches,
+                                void* h_rows_f16, int* h_labels, int* h_workers, double* h_times, int flush_ms,
+                                uint32_t* h_bitmap, int* h_row_off, void* h_values_f16);
 int psb_producer_poll(void* h, int* batch, int* n, int* eof);
 void psb_producer_release(void* h, int batch);
 long long psb_producer_rows_sent(void* h);

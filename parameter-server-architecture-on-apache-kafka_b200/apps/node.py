@@ -103,7 +103,8 @@ def main(argv: Optional[List[str]] = None) -> int:
         if not os.path.exists(cfg.training_data_file_path):
             raise FileNotFoundError(f"training data file not found: {cfg.training_data_file_path}")
         producer = native.StreamProducer(cfg.training_data_file_path, cfg.num_workers, rank * W, W, cfg.num_features,
-                                         cfg.producer_time_per_event, batch_rows=eng.stage_rows, num_batches=4)
+                                         cfg.producer_time_per_event, batch_rows=eng.stage_rows, num_batches=4,
+                                         packed=True)       # bitmap + fp16 non-zeros over PCIe when F % 32 == 0
         n_total, mine, cursor = 0, np.zeros(0, dtype=np.int64), 0
     else:
         n_total = len(train)
@@ -132,8 +133,8 @@ def main(argv: Optional[List[str]] = None) -> int:
                             raise FileNotFoundError(cfg.training_data_file_path)
                         producer_eof = producer_eof or eof == 1
                         break
-                    eng.ingest(producer.rows[b, :n], producer.labels[b, :n], producer.workers[b, :n].numpy(),
-                               producer.times[b, :n].numpy())
+                    eng.ingest(producer.packed(b, n) if producer.is_packed else producer.rows[b, :n],
+                               producer.labels[b, :n], producer.workers[b, :n].numpy(), producer.times[b, :n].numpy())
                     eng.ingest_done.synchronize()           # the pinned batch may be refilled after this
                     producer.release(b)
                     if p_ms <= 0:

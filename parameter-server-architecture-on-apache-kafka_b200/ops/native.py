@@ -119,6 +119,8 @@ def lib() -> C.CDLL:
     L.psb_producer_start.restype = C.c_void_p
     L.psb_producer_start.argtypes = [C.c_char_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
                                      vp, vp, vp, vp, C.c_int]
+    L.psb_producer_start_packed.restype = C.c_void_p
+    L.psb_producer_start_packed.argtypes = L.psb_producer_start.argtypes + [vp, vp, vp]
     L.psb_producer_poll.argtypes = [vp, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int)]
     L.psb_producer_release.argtypes = [vp, C.c_int]
     L.psb_producer_rows_sent.restype = C.c_longlong
@@ -298,7 +300,8 @@ class StreamProducer:
     """Host producer thread filling a ring of pinned batches (see psb_producer_start)."""
 
     def __init__(self, path: str, num_workers_total: int, worker_begin: int, worker_count: int, num_features: int,
-                 p_ms: int, batch_rows: int = 1024, num_batches: int = 4, has_header: bool = True, flush_ms: int = 50):
+                 p_ms: int, batch_rows: int = 1024, num_batches: int = 4, has_header: bool = True, flush_ms: int = 50,
+                 packed: bool = False):
         import torch
         pin = torch.cuda.is_available()
         mk = (lambda *s, dtype: torch.zeros(*s, dtype=dtype).pin_memory()) if pin else \
@@ -307,10 +310,18 @@ class StreamProducer:
         self.labels = mk(num_batches, batch_rows, dtype=torch.int32)
         self.workers = mk(num_batches, batch_rows, dtype=torch.int32)
         self.times = mk(num_batches, batch_rows, dtype=torch.float64)
-        self.h = lib().psb_producer_start(path.encode(), int(has_header), num_workers_total, worker_begin, worker_count,
-                                          num_features, int(p_ms), batch_rows, num_batches, self.rows.data_ptr(),
-                                          self.labels.data_ptr(), self.workers.data_ptr(), self.times.data_ptr(),
-                                          flush_ms)
+        self.is_packed = bool(packed) and num_features % 32 == 0
+        self.F, self.batch_rows = num_features, batch_rows
+        if self.is_packed:
+            self.bitmap = mk(num_batches, batch_rows, num_features // 32, dtype=torch.int32)
+            self.row_off = mk(num_batches, batch_rows + 1, dtype=torch.int32)
+            self.values = mk(num_batches, batch_rows * num_features, dtype=torch.float16)
+        pk = (self.bitmap.data_ptr(), self.row_off.data_ptr(), self.values.data_ptr()) if self.is_packed \
+            else (None, None, None)
+        self.h = lib().psb_producer_start_packed(
+            path.encode(), int(has_header), num_workers_total, worker_begin, worker_count, num_features, int(p_ms),
+            batch_rows, num_batches, self.rows.data_ptr(), self.labels.data_ptr(), self.workers.data_ptr(),
+            self.times.data_ptr(), flush_ms, *pk)
         if not self.h:
             raise NativeError("psb_producer_start: " + lib().psb_last_error().decode())
 
@@ -320,6 +331,16 @@ class StreamProducer:
         if lib().psb_producer_poll(self.h, C.byref(b), C.byref(n), C.byref(e)):
             return b.value, n.value, 0
         return None, 0, e.value
+
+    def packed(self, batch: int, n: int) -> "PackedRows":
+        """The bitmap-packed form of ready batch `batch` (views of the producer's pinned buffers, no copy)."""
+        assert self.is_packed, "StreamProducer(packed=True) required"
+        pk = PackedRows.__new__(PackedRows)
+        pk.max_rows, pk.F, pk.n = self.batch_rows, self.F, n
+        pk.bitmap, pk.row_off, pk.values, pk.labels = (self.bitmap[batch], self.row_off[batch], self.values[batch],
+                                                       self.labels[batch])
+        pk.nnz = int(self.row_off[batch, n])
+        return pk
 
     def release(self, batch: int) -> None:
         lib().psb_producer_release(self.h, batch)
