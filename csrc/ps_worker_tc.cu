@@ -185,6 +185,9 @@ struct TcEval {
                 if (!wait_or_fail(sh.full + slot, (pc / kNS) & 1, sh.fail)) return;
                 const unsigned char* tile = sh.ring + (size_t)slot * kChunkBytes + (j8 & 1) * 8;
                 float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f, q0 = 0.f, q1 = 0.f, q2 = 0.f, q3 = 0.f;
+#ifdef PSB_TC_EXPERIMENT_NO_STATS_LDS          // timing experiment only (wrong statistics)
+                if (pc == 0xffffffffu)
+#endif
 #pragma unroll 8
                 for (int i = 0; i < kSlabRows / 2; ++i) {
                     const int r = 2 * i + h;

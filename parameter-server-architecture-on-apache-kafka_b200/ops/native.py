@@ -15,7 +15,7 @@ from typing import Optional, Tuple
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libpsb200.so")
+LIB_PATH = os.environ.get("PSB200_LIB") or os.path.join(_HERE, "libpsb200.so")   # override: experiment builds
 
 CLASS_PAD = 8
 MAX_RANKS = 8
