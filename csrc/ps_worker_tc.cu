@@ -60,6 +60,7 @@ struct TcShared {
 };
 
 __device__ __forceinline__ bool wait_or_fail(uint64_t* bar, uint32_t parity, volatile int* fail) {
+    if (tc::mbar_try_wait(bar, parity)) return true;            // common case: no clock read, no fail poll
     const unsigned long long t0 = clock64();
     while (!tc::mbar_try_wait(bar, parity)) {
         if (*fail) return false;
@@ -130,26 +131,46 @@ struct TcEval {
     // ---- TMA producer (one thread).  with_b: stream every slab twice, A(s) then B(s).
     // fused: the statistics warps also read every A chunk, so a slot whose previous occupant was an A chunk
     // of this pass is refilled only after their sdone arrival as well.
-    __device__ void produce(const PassCfg& cfg) const {
+    __device__ void produce(const PassCfg& cfg) {
         const bool with_a = cfg.a, with_b = cfg.b, fused = cfg.fused;
         const int nkb = F / kBlockK, S = num_active_slabs();
-        unsigned int pc = *sh.chunk_base;
-        const unsigned int base = pc;
-        unsigned int sd_cnt[16];
-#pragma unroll
-        for (int i = 0; i < 16; ++i) sd_cnt[i] = 0;
+        // ring position as running (slot, use) counters: this thread is alone on its warp, so the latency of a
+        // runtime integer division per chunk (~100 cycles each) would pace the whole stream
+        const unsigned int pc0 = *sh.chunk_base;
+        int slot = (int)(pc0 % (unsigned)kNS);
+        unsigned int use = pc0 / (unsigned)kNS;
+        int idx = 0;                          // chunks issued in this pass
+        int lag_c = 0;                        // (idx - kNS) % nkb and whether chunk idx - kNS was an A chunk
+        bool lag_a = true;
+        unsigned int sd_par = 0u;             // per-slot parity of the statistics warps' sdone barrier
         auto load = [&](int b, int c, uint64_t policy) -> bool {
-            const int slot = pc % kNS;
-            const unsigned use = pc / kNS;
+#if PSB_TC_PROFILE == 2
+            const long long te = clock64();
+#endif
             if (use > 0 && !wait_or_fail(sh.empty + slot, (use - 1) & 1, sh.fail)) return false;
-            if (fused && pc >= base + (unsigned)kNS && (((pc - kNS - base) / nkb) & 1u) == 0u) {
-                if (!wait_or_fail(sh.sdone + slot, sd_cnt[slot] & 1, sh.fail)) return false;
-                ++sd_cnt[slot];
+#if PSB_TC_PROFILE == 2
+            const long long ts = clock64();
+            prof[0] += ts - te;
+#endif
+            if (fused && idx >= kNS) {        // previous occupant of the slot: chunk idx - kNS of this pass
+                if (lag_a) {
+                    if (!wait_or_fail(sh.sdone + slot, (sd_par >> slot) & 1u, sh.fail)) return false;
+                    sd_par ^= 1u << slot;
+                }
+                if (++lag_c == nkb) lag_c = 0, lag_a = !lag_a;
             }
+#if PSB_TC_PROFILE == 2
+            prof[1] += clock64() - ts;
+#endif
+#ifdef PSB_TC_EXPERIMENT_NO_TMA                // timing experiment only: no data movement, barriers still cycle
+            tc::mbar_arrive(sh.full + slot);
+#else
             tc::mbar_arrive_expect_tx(sh.full + slot, kChunkBytes);
             tc::tma_load_2d_hint(sh.ring + (size_t)slot * kChunkBytes, tmX, c * kBlockK, row_base + b * kSlabRows,
                                  sh.full + slot, policy);
-            ++pc;
+#endif
+            ++idx;
+            if (++slot == kNS) slot = 0, ++use;
             return true;
         };
         for (int q = 0; q < S; ++q) {
@@ -171,7 +192,10 @@ struct TcEval {
     //      same chunk parity, so a warp that follows all of them is never more than one mbarrier phase ahead.
     __device__ void stats_fused(int wi, int lane) const {
         const int nkb = F / kBlockK, S = num_active_slabs();
-        const unsigned int base = *sh.chunk_base;
+        // this warp's chunks are base + wi, base + wi + 2, ... through every A(q) B(q): one stride-2 walk of the ring
+        const unsigned int pc0 = *sh.chunk_base + (unsigned)wi;
+        int slot = (int)(pc0 % (unsigned)kNS);
+        uint32_t phase = (pc0 / (unsigned)kNS) & 1u;
         float* ssum = (float*)(sh.sR + kRBytes);
         float* ssq = sh.inv;
         const int h = lane >> 4, j8 = lane & 15;
@@ -180,13 +204,11 @@ struct TcEval {
             const bool full_slab = row_valid(b * kSlabRows) && row_valid(b * kSlabRows + kSlabRows - 1) &&
                                    slab_rows_contiguous(b);
             for (int c = wi; c < nkb; c += 2) {
-                const unsigned int pc = base + (unsigned)q * 2u * nkb + c;
-                const int slot = pc % kNS;
-                if (!wait_or_fail(sh.full + slot, (pc / kNS) & 1, sh.fail)) return;
+                if (!wait_or_fail(sh.full + slot, phase, sh.fail)) return;
                 const unsigned char* tile = sh.ring + (size_t)slot * kChunkBytes + (j8 & 1) * 8;
                 float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f, q0 = 0.f, q1 = 0.f, q2 = 0.f, q3 = 0.f;
 #ifdef PSB_TC_EXPERIMENT_NO_STATS_LDS          // timing experiment only (wrong statistics)
-                if (pc == 0xffffffffu)
+                if (slot < 0)
 #endif
 #pragma unroll 8
                 for (int i = 0; i < kSlabRows / 2; ++i) {
@@ -213,10 +235,13 @@ struct TcEval {
                 }
                 __syncwarp();
                 if (lane == 0) tc::mbar_arrive(sh.sdone + slot);
+                slot += 2;
+                if (slot >= kNS) slot -= kNS, phase ^= 1u;
             }
             for (int c = wi; c < nkb; c += 2) {                 // B chunks of my slots: follow the phases only
-                const unsigned int pc = base + (unsigned)q * 2u * nkb + nkb + c;
-                if (!wait_or_fail(sh.full + pc % kNS, (pc / kNS) & 1, sh.fail)) return;
+                if (!wait_or_fail(sh.full + slot, phase, sh.fail)) return;
+                slot += 2;
+                if (slot >= kNS) slot -= kNS, phase ^= 1u;
             }
         }
         __syncwarp();
@@ -246,17 +271,19 @@ struct TcEval {
         const int nkb = F / kBlockK, S = __shfl_sync(0xffffffffu, num_active_slabs(), 0);
         constexpr uint32_t idesc1 = tc::idesc_f16(128, 16, 0, 0);    // GEMM1: A K-major, B K-major
         constexpr uint32_t idesc2 = tc::idesc_f16(128, 16, 1, 1);    // GEMM2: A MN-major, B MN-major
-        unsigned int pc = __shfl_sync(0xffffffffu, *sh.chunk_base, 0);
+        // ring position as running (slot, phase) counters — no per-chunk integer divisions on the issue path
+        const unsigned int pc0 = __shfl_sync(0xffffffffu, *sh.chunk_base, 0);
+        int slot = (int)(pc0 % (unsigned)kNS);
+        uint32_t phase = (pc0 / (unsigned)kNS) & 1u;
         const uint32_t tmem_u = __shfl_sync(0xffffffffu, tmem, 0);
         const uint32_t sB0 = tc::smem_u32(sh.sB), sR0 = tc::smem_u32(sh.sR), ring0 = tc::smem_u32(sh.ring);
 
         auto gemm1 = [&](int q) -> bool {                       // Z_{q&1} = A(q) x Wsp
-            for (int c = 0; c < nkb; ++c, ++pc) {
-                const int slot = pc % kNS;
+            for (int c = 0; c < nkb; ++c) {
 #ifdef PSB_TC_PROFILE
                 const long long tw = clock64();
 #endif
-                if (!wait_or_fail(sh.full + slot, (pc / kNS) & 1, sh.fail)) return false;
+                if (!wait_or_fail(sh.full + slot, phase, sh.fail)) return false;
 #ifdef PSB_TC_PROFILE
                 prof[0] += clock64() - tw;
 #endif
@@ -264,13 +291,16 @@ struct TcEval {
                 const uint64_t ad = tc::desc_k_sw128(ring0 + slot * kChunkBytes, 1024);
                 const uint64_t bd = tc::desc_k_sw128(sB0 + c * kBChunkBytes, 1024);
                 if (tc::elect_one()) {
+#ifndef PSB_TC_EXPERIMENT_NO_MMA               // timing experiment only: commits without MMAs
 #pragma unroll
                     for (int k = 0; k < kBlockK / 16; ++k)
                         tc::umma_f16(tmem_u + kColZ + 16 * (q & 1), ad + 2 * k, bd + 2 * k, idesc1, (c | k) ? 1u : 0u);
+#endif
                     tc::umma_commit(sh.empty + slot);
                     if (c == nkb - 1) tc::umma_commit(sh.z_full + (q & 1));
                 }
                 __syncwarp();
+                if (++slot == kNS) slot = 0, phase ^= 1u;
             }
             return true;
         };
@@ -281,15 +311,15 @@ struct TcEval {
             if (!wait_or_fail(sh.r_full, ruse[0] & 1, sh.fail)) return false;
             ++ruse[0];
 #ifdef PSB_TC_PROFILE
+            prof[1] += clock64() - tr;
 #endif
             tc::tc_fence_after();
-            for (int j = 0; j < nkb / 2; ++j, pc += 2) {
-                const int slot = pc % kNS;                      // chunks 2j, 2j+1 sit in adjacent slots
+            for (int j = 0; j < nkb / 2; ++j) {                 // chunks 2j, 2j+1 sit in adjacent slots (kNS even)
 #ifdef PSB_TC_PROFILE
                 const long long tb = clock64();
 #endif
-                if (!wait_or_fail(sh.full + slot, (pc / kNS) & 1, sh.fail)) return false;
-                if (!wait_or_fail(sh.full + slot + 1, ((pc + 1) / kNS) & 1, sh.fail)) return false;
+                if (!wait_or_fail(sh.full + slot, phase, sh.fail)) return false;
+                if (!wait_or_fail(sh.full + slot + 1, phase, sh.fail)) return false;
 #ifdef PSB_TC_PROFILE
                 prof[2] += clock64() - tb;
 #endif
@@ -297,25 +327,23 @@ struct TcEval {
                 const uint64_t ad0 = tc::desc_mn_sw128(ring0 + slot * kChunkBytes, kChunkBytes, 1024);
                 const uint64_t bd0 = tc::desc_mn_none(sR0, 256, 128);   // one Rsp buffer: epilogue(q+1) starts after GEMM2(q)
                 if (tc::elect_one()) {
+#ifndef PSB_TC_EXPERIMENT_NO_MMA
 #pragma unroll
                     for (int ks = 0; ks < kSlabRows / 16; ++ks)      // +2048 B of A, +512 B of B per 16 rows
                         tc::umma_f16(tmem_u + kColG + 16 * j, ad0 + (uint64_t)(ks * 128), bd0 + (uint64_t)(ks * 32),
                                      idesc2, (q | ks) ? 1u : 0u);
+#endif
                     tc::umma_commit(sh.empty + slot);
                     tc::umma_commit(sh.empty + slot + 1);
                 }
                 __syncwarp();
+                slot += 2;
+                if (slot == kNS) slot = 0, phase ^= 1u;
             }
             return true;
         };
         for (int q = 0; q < S; ++q) {
-#ifdef PSB_TC_PROFILE
-            const long long tg = clock64();
-#endif
             if (cfg.a && !gemm1(q)) return;
-#ifdef PSB_TC_PROFILE
-            prof[1] += clock64() - tg;
-#endif
             if (cfg.b && !gemm2(q)) return;
             if (cfg.b && !cfg.a) {           // gradient-only pass: tell the residual warps that Rsp(q) has been consumed
                 if (tc::elect_one()) tc::umma_commit(sh.z_full + (q & 1));
@@ -450,14 +478,20 @@ struct TcEval {
         __syncthreads();
         const float invn = 1.f / (float)count;
         if (warp == 0) {
+#if PSB_TC_PROFILE == 2
+            const long long tp0 = clock64();
+#endif
             if (lane == 0) produce(cfg);
+#if PSB_TC_PROFILE == 2
+            prof[3] += clock64() - tp0;
+#endif
             __syncwarp();
         } else if (warp == 1) {
-#ifdef PSB_TC_PROFILE
+#if PSB_TC_PROFILE == 1
             const long long tm0 = clock64();
 #endif
             mma_loop(cfg);
-#ifdef PSB_TC_PROFILE
+#if PSB_TC_PROFILE == 1
             prof[3] += clock64() - tm0;
 #endif
             __syncwarp();
@@ -690,7 +724,7 @@ psb_worker_tc_kernel(const __grid_constant__ CUtensorMap tmX, PsbSolver sv, Comm
         if (tid == 0) info_out[8 * w + 6] = (int)((clock64() - t_solve) >> 6), info_out[8 * w + 7] = (int)((clock64() - t_begin) >> 6);
 #ifdef PSB_TC_PROFILE
         __syncthreads();
-        if (tid == 32) for (int k = 0; k < 4; ++k) info_out[8 * w + 4 + k] = (int)(ev.prof[k] >> 6);
+        if (tid == (PSB_TC_PROFILE == 2 ? 0 : 32)) for (int k = 0; k < 4; ++k) info_out[8 * w + 4 + k] = (int)(ev.prof[k] >> 6);
 #endif
     }
     tc::tc_fence_before();

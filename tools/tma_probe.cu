@@ -13,21 +13,22 @@ int psb_make_tmap_2d_f16(CUtensorMap* out, const void* base, uint64_t rows, uint
 }
 constexpr int CH = 16384;
 template <int MODE>
-__global__ void __launch_bounds__(128, 1) probe(const __grid_constant__ CUtensorMap tm, const unsigned char* base, int rows_per_cta, int F, int NS, long long* cycles) {
+__global__ void __launch_bounds__(128, 1) probe(const __grid_constant__ CUtensorMap tm, const unsigned char* base, int rows_per_cta, int F, int NS, long long* cycles, int passes = 1, int cta_rows_mod = 1 << 30) {
     extern __shared__ __align__(1024) unsigned char smem_raw[];
     unsigned char* smem = (unsigned char*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
     uint64_t* full = (uint64_t*)(smem + (size_t)NS * CH); uint64_t* empty = full + NS;
     if (threadIdx.x == 0) { for (int s = 0; s < NS; ++s) tc::mbar_init(full + s, 1), tc::mbar_init(empty + s, 1); tc::mbar_fence_init(); }
     __syncthreads();
-    const int nkb = F / 64, nslab = rows_per_cta / 128, total = nkb * nslab;
+    const int nkb = F / 64, nslab = rows_per_cta / 128, per_pass = nkb * nslab, total = per_pass * passes;
+    const int row0 = (blockIdx.x % cta_rows_mod) * rows_per_cta;
     const long long t0 = clock64();
     if (threadIdx.x == 0) {
         for (int i = 0; i < total; ++i) {
             const int slot = i % NS; const unsigned use = i / NS;
             if (use > 0) while (!tc::mbar_try_wait(empty + slot, (use - 1) & 1)) {}
             tc::mbar_arrive_expect_tx(full + slot, CH);
-            const int sl = i / nkb, c = i % nkb;
-            if (MODE == 0) tc::tma_load_2d(smem + (size_t)slot * CH, &tm, c * 64, blockIdx.x * rows_per_cta + sl * 128, full + slot);
+            const int sl = (i % per_pass) / nkb, c = i % nkb;
+            if (MODE == 0) tc::tma_load_2d(smem + (size_t)slot * CH, &tm, c * 64, row0 + sl * 128, full + slot);
             else {
                 const unsigned char* src = base + ((size_t)blockIdx.x * total + i) * CH;
                 asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(tc::smem_u32(smem + (size_t)slot * CH)), "l"(src), "r"(CH), "r"(tc::smem_u32(full + slot)) : "memory");
@@ -62,6 +63,21 @@ int main() {
         cudaError_t err = cudaGetLastError();
         double gb = (double)ctas * rows * F * 2 / 1e9;
         printf("mode=%s NS=%d ctas=%d: %.1f us, %.1f GB/s total, %.1f GB/s per SM (%s)\n", mode ? "bulk1d" : "tensor2d", NS, ctas, ms * 1e3, gb / (ms * 1e-3), gb / (ms * 1e-3) / ctas, cudaGetErrorString(err));
+    }
+    // Long runs: `passes` sweeps over each CTA's own region.  region = 2 MB per CTA (296 MB, DRAM-bound) versus
+    // 256 KB per CTA (38-76 MB, L2-resident after the first sweep): the second is the L2 -> SM streaming ceiling.
+    cudaFuncSetAttribute(probe<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 1024 + 4 * CH + 64 + 64);
+    for (int ctas : {148, 296}) for (int rows_cta : {1024, 128}) {
+        const int passes = rows_cta == 1024 ? 40 : 320;
+        const int NS = 4; size_t smem = 1024 + (size_t)NS * CH + 2 * NS * 8 + 64;
+        cudaEvent_t e0, e1; cudaEventCreate(&e0); cudaEventCreate(&e1);
+        probe<0><<<ctas, 128, smem>>>(tm, d, rows_cta, F, NS, dc, 2, 148);
+        cudaEventRecord(e0);
+        probe<0><<<ctas, 128, smem>>>(tm, d, rows_cta, F, NS, dc, passes, 148);
+        cudaEventRecord(e1); cudaEventSynchronize(e1);
+        float ms; cudaEventElapsedTime(&ms, e0, e1);
+        double gb = (double)ctas * rows_cta * F * 2 * passes / 1e9;
+        printf("long ctas=%d region=%d KB/CTA (footprint %.0f MB) passes=%d: %.1f us, %.2f TB/s total, %.1f GB/s per SM (%s)\n", ctas, rows_cta * 2, 148.0 * rows_cta * F * 2 / 1e6, passes, ms * 1e3, gb / ms, gb / (ms * 1e-3) / 148, cudaGetErrorString(cudaGetLastError()));
     }
     return 0;
 }
