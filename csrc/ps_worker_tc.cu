@@ -129,8 +129,8 @@ struct TcEval {
     }
 
     // ---- TMA producer (one thread).  with_b: stream every slab twice, A(s) then B(s).
-    // fused: the statistics warps also read every A chunk, so a slot whose previous occupant was an A chunk
-    // of this pass is refilled only after their sdone arrival as well.
+    // fused: the statistics warps also read every chunk once (on its A or its B use), so a slot whose previous
+    // occupant was such a use is refilled only after their sdone arrival as well.
     __device__ void produce(const PassCfg& cfg) {
         const bool with_a = cfg.a, with_b = cfg.b, fused = cfg.fused;
         const int nkb = F / kBlockK, S = num_active_slabs();
@@ -152,8 +152,9 @@ struct TcEval {
             const long long ts = clock64();
             prof[0] += ts - te;
 #endif
-            if (fused && idx >= kNS) {        // previous occupant of the slot: chunk idx - kNS of this pass
-                if (lag_a) {
+            if (fused && idx >= kNS) {        // previous occupant of the slot: chunk idx - kNS of this pass;
+                                              // the statistics warps read it on its A use when c % 4 < 2, else on its B use
+                if ((((lag_c >> 1) & 1) == 0) == lag_a) {
                     if (!wait_or_fail(sh.sdone + slot, (sd_par >> slot) & 1u, sh.fail)) return false;
                     sd_par ^= 1u << slot;
                 }
@@ -173,6 +174,8 @@ struct TcEval {
             if (++slot == kNS) slot = 0, ++use;
             return true;
         };
+        // (Prefetching slab q+1 into L2 with cp.async.bulk.prefetch while slab q streams was measured: 0.585 ->
+        //  0.796 ms per clock at 296 workers — the extra TMA traffic costs more than the latency it hides.)
         for (int q = 0; q < S; ++q) {
             const int b = active_slab(q);
             if (with_a)
@@ -184,12 +187,13 @@ struct TcEval {
         }
     }
 
-    // ---- statistics fused into the first evaluation: 2 warps (wi = 0, 1) read the A chunks with c % 2 == wi
-    //      while the MMA warp consumes them.  Each half-warp takes every other row, a lane reads 8 bytes
-    //      (4 features) per row; per-chunk register sums are folded into shared per-feature accumulators
-    //      (sum in the spare half of the Rsp region, sum of squares in inv[], converted in place at the end).
-    //      The warp also waits on the B chunks of its slots, doing nothing: every use of a ring slot has the
-    //      same chunk parity, so a warp that follows all of them is never more than one mbarrier phase ahead.
+    // ---- statistics fused into the first evaluation: 2 warps (wi = 0, 1) read the chunks with c % 2 == wi
+    //      while the MMA warp consumes them — half of them during the A stream, the other half during the B
+    //      stream.  Each half-warp takes every other row, a lane reads 8 bytes (4 features) per row; per-chunk
+    //      register sums are folded into shared per-feature accumulators (sum in the spare half of the Rsp
+    //      region, sum of squares in inv[], converted in place at the end).  The warp waits on EVERY use of its
+    //      slots, reading or not: every use of a ring slot has the same chunk parity, so a warp that follows
+    //      all of them is never more than one mbarrier phase ahead.
     __device__ void stats_fused(int wi, int lane) const {
         const int nkb = F / kBlockK, S = num_active_slabs();
         // this warp's chunks are base + wi, base + wi + 2, ... through every A(q) B(q): one stride-2 walk of the ring
@@ -203,45 +207,46 @@ struct TcEval {
             const int b = active_slab(q);
             const bool full_slab = row_valid(b * kSlabRows) && row_valid(b * kSlabRows + kSlabRows - 1) &&
                                    slab_rows_contiguous(b);
-            for (int c = wi; c < nkb; c += 2) {
-                if (!wait_or_fail(sh.full + slot, phase, sh.fail)) return;
-                const unsigned char* tile = sh.ring + (size_t)slot * kChunkBytes + (j8 & 1) * 8;
-                float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f, q0 = 0.f, q1 = 0.f, q2 = 0.f, q3 = 0.f;
+            // half of this warp's chunks are read on their A use (c % 4 < 2), the other half on their B use — the
+            // bytes are the same, and the reads no longer pace the A stream
+            for (int pass = 0; pass < 2; ++pass) {
+                for (int c = wi; c < nkb; c += 2) {
+                    if (!wait_or_fail(sh.full + slot, phase, sh.fail)) return;
+                    if (((c >> 1) & 1) == pass) {
+                        const unsigned char* tile = sh.ring + (size_t)slot * kChunkBytes + (j8 & 1) * 8;
+                        float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f, q0 = 0.f, q1 = 0.f, q2 = 0.f, q3 = 0.f;
 #ifdef PSB_TC_EXPERIMENT_NO_STATS_LDS          // timing experiment only (wrong statistics)
-                if (slot < 0)
+                        if (slot < 0)
 #endif
 #pragma unroll 8
-                for (int i = 0; i < kSlabRows / 2; ++i) {
-                    const int r = 2 * i + h;
-                    const uint2 raw = *(const uint2*)(tile + tc::sw128_off(r, j8 >> 1));
-                    float2 x = __half22float2(*(const __half2*)&raw.x), y = __half22float2(*(const __half2*)&raw.y);
-                    if (!full_slab) {
-                        const float m = row_valid(b * kSlabRows + r) ? 1.f : 0.f;
-                        x.x *= m, x.y *= m, y.x *= m, y.y *= m;
+                        for (int i = 0; i < kSlabRows / 2; ++i) {
+                            const int r = 2 * i + h;
+                            const uint2 raw = *(const uint2*)(tile + tc::sw128_off(r, j8 >> 1));
+                            float2 x = __half22float2(*(const __half2*)&raw.x), y = __half22float2(*(const __half2*)&raw.y);
+                            if (!full_slab) {
+                                const float m = row_valid(b * kSlabRows + r) ? 1.f : 0.f;
+                                x.x *= m, x.y *= m, y.x *= m, y.y *= m;
+                            }
+                            a0 += x.x, a1 += x.y, a2 += y.x, a3 += y.y;
+                            q0 = fmaf(x.x, x.x, q0), q1 = fmaf(x.y, x.y, q1), q2 = fmaf(y.x, y.x, q2), q3 = fmaf(y.y, y.y, q3);
+                        }
+                        a0 += __shfl_xor_sync(0xffffffffu, a0, 16), a1 += __shfl_xor_sync(0xffffffffu, a1, 16);
+                        a2 += __shfl_xor_sync(0xffffffffu, a2, 16), a3 += __shfl_xor_sync(0xffffffffu, a3, 16);
+                        q0 += __shfl_xor_sync(0xffffffffu, q0, 16), q1 += __shfl_xor_sync(0xffffffffu, q1, 16);
+                        q2 += __shfl_xor_sync(0xffffffffu, q2, 16), q3 += __shfl_xor_sync(0xffffffffu, q3, 16);
+                        if (h == 0) {
+                            float4* ps = (float4*)(ssum + c * kBlockK + 4 * j8);
+                            float4* pq = (float4*)(ssq + c * kBlockK + 4 * j8);
+                            float4 u = *ps, v = *pq;
+                            *ps = make_float4(u.x + a0, u.y + a1, u.z + a2, u.w + a3);
+                            *pq = make_float4(v.x + q0, v.y + q1, v.z + q2, v.w + q3);
+                        }
+                        __syncwarp();
+                        if (lane == 0) tc::mbar_arrive(sh.sdone + slot);
                     }
-                    a0 += x.x, a1 += x.y, a2 += y.x, a3 += y.y;
-                    q0 = fmaf(x.x, x.x, q0), q1 = fmaf(x.y, x.y, q1), q2 = fmaf(y.x, y.x, q2), q3 = fmaf(y.y, y.y, q3);
+                    slot += 2;
+                    if (slot >= kNS) slot -= kNS, phase ^= 1u;
                 }
-                a0 += __shfl_xor_sync(0xffffffffu, a0, 16), a1 += __shfl_xor_sync(0xffffffffu, a1, 16);
-                a2 += __shfl_xor_sync(0xffffffffu, a2, 16), a3 += __shfl_xor_sync(0xffffffffu, a3, 16);
-                q0 += __shfl_xor_sync(0xffffffffu, q0, 16), q1 += __shfl_xor_sync(0xffffffffu, q1, 16);
-                q2 += __shfl_xor_sync(0xffffffffu, q2, 16), q3 += __shfl_xor_sync(0xffffffffu, q3, 16);
-                if (h == 0) {
-                    float4* ps = (float4*)(ssum + c * kBlockK + 4 * j8);
-                    float4* pq = (float4*)(ssq + c * kBlockK + 4 * j8);
-                    float4 u = *ps, v = *pq;
-                    *ps = make_float4(u.x + a0, u.y + a1, u.z + a2, u.w + a3);
-                    *pq = make_float4(v.x + q0, v.y + q1, v.z + q2, v.w + q3);
-                }
-                __syncwarp();
-                if (lane == 0) tc::mbar_arrive(sh.sdone + slot);
-                slot += 2;
-                if (slot >= kNS) slot -= kNS, phase ^= 1u;
-            }
-            for (int c = wi; c < nkb; c += 2) {                 // B chunks of my slots: follow the phases only
-                if (!wait_or_fail(sh.full + slot, phase, sh.fail)) return;
-                slot += 2;
-                if (slot >= kNS) slot -= kNS, phase ^= 1u;
             }
         }
         __syncwarp();
@@ -453,6 +458,9 @@ struct TcEval {
     // In the fused pass x holds the UNSCALED start weights w0 (1/std is being computed during the pass).
     __device__ double run_pass(const float* x, float* g, const PassCfg& cfg) {
         const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+#if PSB_TC_PROFILE == 3                        // thread 0: [0] weight staging [1] role section [2] pass tail
+        const long long tq0 = clock64();
+#endif
         if (cfg.a) {
             // Wsp = (x * inv) split into fp16 hi | lo, K-major SWIZZLE_128B, 16 rows per 64-feature chunk
             for (int f = tid; f < F; f += blockDim.x) {
@@ -477,6 +485,10 @@ struct TcEval {
         tc::fence_proxy_async_smem();
         __syncthreads();
         const float invn = 1.f / (float)count;
+#if PSB_TC_PROFILE == 3
+        const long long tq1 = clock64();
+        prof[0] += tq1 - tq0;
+#endif
         if (warp == 0) {
 #if PSB_TC_PROFILE == 2
             const long long tp0 = clock64();
@@ -501,11 +513,19 @@ struct TcEval {
             stats_fused(warp - 6, lane);
         }
         __syncthreads();
+#if PSB_TC_PROFILE == 3
+        const long long tq2 = clock64();
+        prof[1] += tq2 - tq1;
+#endif
         if (tid == 0)
             *sh.chunk_base += (unsigned)((cfg.a ? 1 : 0) + (cfg.b ? 1 : 0)) * (unsigned)num_active_slabs() * (F / kBlockK);
         if (cfg.b && tid < 8) g[F * 8 + tid] = sh.sred[1 + tid] * invn;
         const double loss = (double)sh.sred[0] * (double)invn;
         __syncthreads();
+#if PSB_TC_PROFILE == 3
+        prof[2] += clock64() - tq2;
+        prof[3] += 1;
+#endif
         return loss;
     }
 
@@ -724,7 +744,7 @@ psb_worker_tc_kernel(const __grid_constant__ CUtensorMap tmX, PsbSolver sv, Comm
         if (tid == 0) info_out[8 * w + 6] = (int)((clock64() - t_solve) >> 6), info_out[8 * w + 7] = (int)((clock64() - t_begin) >> 6);
 #ifdef PSB_TC_PROFILE
         __syncthreads();
-        if (tid == (PSB_TC_PROFILE == 2 ? 0 : 32)) for (int k = 0; k < 4; ++k) info_out[8 * w + 4 + k] = (int)(ev.prof[k] >> 6);
+        if (tid == (PSB_TC_PROFILE >= 2 ? 0 : 32)) for (int k = 0; k < 4; ++k) info_out[8 * w + 4 + k] = (int)(ev.prof[k] >> 6);
 #endif
     }
     tc::tc_fence_before();
