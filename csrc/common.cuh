@@ -147,6 +147,21 @@ __device__ __forceinline__ bool wait_ge_sys(const unsigned int* p, unsigned int 
     return true;
 }
 
+// ------------------------------------------------------------------ debug timeline (block 0, -DPSB_TC_TRACE only)
+#ifdef PSB_TC_TRACE
+__shared__ long long psb_trace_t[48];
+__shared__ int psb_trace_id[48];
+__shared__ int psb_trace_n;
+#define PSB_TRACE(id)                                                                   \
+    do {                                                                                \
+        if (threadIdx.x == 0 && blockIdx.x == 0 && psb_trace_n < 48) {                  \
+            psb_trace_t[psb_trace_n] = clock64(), psb_trace_id[psb_trace_n] = (id), ++psb_trace_n; \
+        }                                                                               \
+    } while (0)
+#else
+#define PSB_TRACE(id) do { } while (0)
+#endif
+
 // ------------------------------------------------------------------ block reductions
 // All threads get the same double.  `red` is shared scratch of >= 33 doubles.
 __device__ __forceinline__ double block_sum(double v, double* red) {

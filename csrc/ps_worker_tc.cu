@@ -203,6 +203,10 @@ struct TcEval {
         float* ssum = (float*)(sh.sR + kRBytes);
         float* ssq = sh.inv;
         const int h = lane >> 4, j8 = lane & 15;
+#ifdef PSB_TC_TRACE
+        long long st_wait = 0, st_read = 0;
+        int st_chunks = 0;
+#endif
         for (int q = 0; q < S; ++q) {
             const int b = active_slab(q);
             const bool full_slab = row_valid(b * kSlabRows) && row_valid(b * kSlabRows + kSlabRows - 1) &&
@@ -211,38 +215,60 @@ struct TcEval {
             // bytes are the same, and the reads no longer pace the A stream
             for (int pass = 0; pass < 2; ++pass) {
                 for (int c = wi; c < nkb; c += 2) {
+#ifdef PSB_TC_TRACE
+                    const long long tw0 = clock64();
+#endif
                     if (!wait_or_fail(sh.full + slot, phase, sh.fail)) return;
+#ifdef PSB_TC_TRACE
+                    const long long tw1 = clock64();
+                    st_wait += tw1 - tw0;
+#endif
                     if (((c >> 1) & 1) == pass) {
-                        const unsigned char* tile = sh.ring + (size_t)slot * kChunkBytes + (j8 & 1) * 8;
+                        const uint32_t tile = tc::smem_u32(sh.ring) + (uint32_t)slot * kChunkBytes + (j8 & 1) * 8;
                         float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f, q0 = 0.f, q1 = 0.f, q2 = 0.f, q3 = 0.f;
 #ifdef PSB_TC_EXPERIMENT_NO_STATS_LDS          // timing experiment only (wrong statistics)
                         if (slot < 0)
 #endif
-#pragma unroll 8
-                        for (int i = 0; i < kSlabRows / 2; ++i) {
-                            const int r = 2 * i + h;
-                            const uint2 raw = *(const uint2*)(tile + tc::sw128_off(r, j8 >> 1));
+                        // branch-free unrolled body (the row mask of a partial slab is a separate loop), so that the
+                        // eight loads of a group are in flight together and their arithmetic interleaves
+                        auto row = [&](const uint2 raw, const float m) {
                             float2 x = __half22float2(*(const __half2*)&raw.x), y = __half22float2(*(const __half2*)&raw.y);
-                            if (!full_slab) {
-                                const float m = row_valid(b * kSlabRows + r) ? 1.f : 0.f;
-                                x.x *= m, x.y *= m, y.x *= m, y.y *= m;
-                            }
+                            x.x *= m, x.y *= m, y.x *= m, y.y *= m;
                             a0 += x.x, a1 += x.y, a2 += y.x, a3 += y.y;
                             q0 = fmaf(x.x, x.x, q0), q1 = fmaf(x.y, x.y, q1), q2 = fmaf(y.x, y.x, q2), q3 = fmaf(y.y, y.y, q3);
+                        };
+                        if (full_slab) {
+#pragma unroll 1
+                            for (int i0 = 0; i0 < kSlabRows / 2; i0 += 8) {
+                                uint2 raw[8];
+#pragma unroll
+                                for (int u = 0; u < 8; ++u) raw[u] = tc::lds_v2(tile + tc::sw128_off(2 * (i0 + u) + h, j8 >> 1));
+#pragma unroll
+                                for (int u = 0; u < 8; ++u) row(raw[u], 1.f);
+                            }
+                        } else {
+#pragma unroll 4
+                            for (int i = 0; i < kSlabRows / 2; ++i) {
+                                const int r = 2 * i + h;
+                                row(tc::lds_v2(tile + tc::sw128_off(r, j8 >> 1)), row_valid(b * kSlabRows + r) ? 1.f : 0.f);
+                            }
                         }
                         a0 += __shfl_xor_sync(0xffffffffu, a0, 16), a1 += __shfl_xor_sync(0xffffffffu, a1, 16);
                         a2 += __shfl_xor_sync(0xffffffffu, a2, 16), a3 += __shfl_xor_sync(0xffffffffu, a3, 16);
                         q0 += __shfl_xor_sync(0xffffffffu, q0, 16), q1 += __shfl_xor_sync(0xffffffffu, q1, 16);
                         q2 += __shfl_xor_sync(0xffffffffu, q2, 16), q3 += __shfl_xor_sync(0xffffffffu, q3, 16);
                         if (h == 0) {
-                            float4* ps = (float4*)(ssum + c * kBlockK + 4 * j8);
-                            float4* pq = (float4*)(ssq + c * kBlockK + 4 * j8);
-                            float4 u = *ps, v = *pq;
-                            *ps = make_float4(u.x + a0, u.y + a1, u.z + a2, u.w + a3);
-                            *pq = make_float4(v.x + q0, v.y + q1, v.z + q2, v.w + q3);
+                            const uint32_t ps = tc::smem_u32(ssum + c * kBlockK + 4 * j8);
+                            const uint32_t pq = tc::smem_u32(ssq + c * kBlockK + 4 * j8);
+                            const float4 u = tc::lds_f4(ps), v = tc::lds_f4(pq);
+                            tc::sts_f4(ps, make_float4(u.x + a0, u.y + a1, u.z + a2, u.w + a3));
+                            tc::sts_f4(pq, make_float4(v.x + q0, v.y + q1, v.z + q2, v.w + q3));
                         }
                         __syncwarp();
                         if (lane == 0) tc::mbar_arrive(sh.sdone + slot);
+#ifdef PSB_TC_TRACE
+                        st_read += clock64() - tw1, ++st_chunks;
+#endif
                     }
                     slot += 2;
                     if (slot >= kNS) slot -= kNS, phase ^= 1u;
@@ -250,6 +276,11 @@ struct TcEval {
             }
         }
         __syncwarp();
+#ifdef PSB_TC_TRACE
+        if (blockIdx.x == 0 && lane == 0)
+            printf("stats warp %d: %d chunks read, %lld cycles reading (%lld per chunk), %lld cycles waiting\n", wi, st_chunks,
+                   st_read, st_read / (st_chunks ? st_chunks : 1), st_wait);
+#endif
         const float n = (float)count;
         bool redo = false;
         for (int c = wi; c < nkb; c += 2) {
@@ -408,9 +439,9 @@ struct TcEval {
             __align__(16) __half hi[8], lo[8];
 #pragma unroll
             for (int c = 0; c < 8; ++c) tc::split_half(rr[c], hi[c], lo[c]);
-            unsigned char* dst = sh.sR + (r >> 3) * 256 + (r & 7) * 16;
-            *(uint4*)dst = *(const uint4*)hi;
-            *(uint4*)(dst + 128) = *(const uint4*)lo;
+            const uint32_t dst = tc::smem_u32(sh.sR) + (r >> 3) * 256 + (r & 7) * 16;
+            tc::sts_v4(dst, *(const uint4*)hi);
+            tc::sts_v4(dst + 128, *(const uint4*)lo);
             tc::fence_proxy_async_smem();
             tc::tc_fence_before();
             __syncwarp();
@@ -461,6 +492,7 @@ struct TcEval {
 #if PSB_TC_PROFILE == 3                        // thread 0: [0] weight staging [1] role section [2] pass tail
         const long long tq0 = clock64();
 #endif
+        PSB_TRACE(20);
         if (cfg.a) {
             // Wsp = (x * inv) split into fp16 hi | lo, K-major SWIZZLE_128B, 16 rows per 64-feature chunk
             for (int f = tid; f < F; f += blockDim.x) {
@@ -468,13 +500,13 @@ struct TcEval {
                 const float sc = cfg.fused ? 1.f : sh.inv[f];
                 const float w[8] = {a.x * sc, a.y * sc, a.z * sc, a.w * sc, b.x * sc, b.y * sc, b.z * sc, b.w * sc};
                 const int kb = f >> 6, k = f & 63, j = k >> 3, e = k & 7;
-                unsigned char* chunk = sh.sB + (size_t)kb * kBChunkBytes;
+                const uint32_t chunk = tc::smem_u32(sh.sB) + (uint32_t)kb * kBChunkBytes + e * 2;
 #pragma unroll
                 for (int c = 0; c < 8; ++c) {
                     __half hi, lo;
                     tc::split_half(w[c], hi, lo);
-                    *(__half*)(chunk + tc::sw128_off(c, j) + e * 2) = hi;
-                    *(__half*)(chunk + 1024 + tc::sw128_off(c, j) + e * 2) = lo;
+                    tc::sts_u16(chunk + tc::sw128_off(c, j), __half_as_ushort(hi));
+                    tc::sts_u16(chunk + 1024 + tc::sw128_off(c, j), __half_as_ushort(lo));
                 }
             }
         }
@@ -485,6 +517,7 @@ struct TcEval {
         tc::fence_proxy_async_smem();
         __syncthreads();
         const float invn = 1.f / (float)count;
+        PSB_TRACE(21);
 #if PSB_TC_PROFILE == 3
         const long long tq1 = clock64();
         prof[0] += tq1 - tq0;
@@ -513,6 +546,7 @@ struct TcEval {
             stats_fused(warp - 6, lane);
         }
         __syncthreads();
+        PSB_TRACE(22);
 #if PSB_TC_PROFILE == 3
         const long long tq2 = clock64();
         prof[1] += tq2 - tq1;
@@ -641,6 +675,11 @@ psb_worker_tc_kernel(const __grid_constant__ CUtensorMap tmX, PsbSolver sv, Comm
     sh.chunk_base = &s_chunk_base;
     sh.need_redo = &s_need_redo;
 
+#ifdef PSB_TC_TRACE
+    if (tid == 0) psb_trace_n = 0;
+    __syncthreads();
+    PSB_TRACE(0);
+#endif
     if (tid == 0) {
         s_fail = 0, s_chunk_base = 0, s_need_redo = 0;
         tc::tma_prefetch_desc(&tmX);
@@ -664,6 +703,7 @@ psb_worker_tc_kernel(const __grid_constant__ CUtensorMap tmX, PsbSolver sv, Comm
     const int* lw = labels + (size_t)w * cap;
 
     // ---- pull
+    PSB_TRACE(1);
     const long long t_begin = clock64();
     float* w0 = ws.w0;
     bool alive = true;
@@ -707,6 +747,7 @@ psb_worker_tc_kernel(const __grid_constant__ CUtensorMap tmX, PsbSolver sv, Comm
         // instead of two): at the start point the effective weights are w0 itself.
         bool have_f0 = false;
         double f0 = 0.0;
+        PSB_TRACE(2);
         if (sv.standardize) {
             f0 = ev.eval_first_fused(w0, v.g);
             have_f0 = !s_need_redo;
@@ -714,8 +755,10 @@ psb_worker_tc_kernel(const __grid_constant__ CUtensorMap tmX, PsbSolver sv, Comm
             ev.unit_scale();
         }
         const long long t_stats = clock64();
+        PSB_TRACE(3);
         to_scaled_space(v.x, w0, sh.inv, F);
         __syncthreads();
+        PSB_TRACE(4);
 
         SolveResult res;
         if (cached) {
@@ -725,10 +768,12 @@ psb_worker_tc_kernel(const __grid_constant__ CUtensorMap tmX, PsbSolver sv, Comm
             res = local_solve(ev, v, sv.solver, sv.max_iter, sv.sgd_lr, sh.red, have_f0, f0);
         }
         const long long t_solve = clock64();
+        PSB_TRACE(5);
 
         float* delta = v.tmp;
         finish_delta(delta, v.x, w0, sh.inv, F, R, sv.center && sv.solver == PSB_SOLVER_LBFGS);
         __syncthreads();
+        PSB_TRACE(6);
         if (tid == 0) {
             loss_out[w] = s_fail ? nanf("") : (float)res.loss;
             info_out[8 * w + 0] = res.evals, info_out[8 * w + 1] = res.iterations;
@@ -742,6 +787,12 @@ psb_worker_tc_kernel(const __grid_constant__ CUtensorMap tmX, PsbSolver sv, Comm
             comm_push(cx, (const float4*)delta);
         }
         if (tid == 0) info_out[8 * w + 6] = (int)((clock64() - t_solve) >> 6), info_out[8 * w + 7] = (int)((clock64() - t_begin) >> 6);
+        PSB_TRACE(7);
+#ifdef PSB_TC_TRACE
+        if (tid == 0 && blockIdx.x == 0)
+            for (int i = 1; i < psb_trace_n; ++i)
+                printf("trace %2d -> %2d : %7lld cycles\n", psb_trace_id[i - 1], psb_trace_id[i], psb_trace_t[i] - psb_trace_t[i - 1]);
+#endif
 #ifdef PSB_TC_PROFILE
         __syncthreads();
         if (tid == (PSB_TC_PROFILE >= 2 ? 0 : 32)) for (int k = 0; k < 4; ++k) info_out[8 * w + 4 + k] = (int)(ev.prof[k] >> 6);

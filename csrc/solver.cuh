@@ -40,15 +40,6 @@ __device__ __forceinline__ void vec_axpy_to(float* out, const float* x, double a
         o4[i] = make_float4(fmaf(fa, dv.x, xv.x), fmaf(fa, dv.y, xv.y), fmaf(fa, dv.z, xv.z), fmaf(fa, dv.w, xv.w));
     }
 }
-__device__ __forceinline__ void vec_sub_to(float* out, const float* a, const float* b, int n4) {
-    const float4* a4 = (const float4*)a;
-    const float4* b4 = (const float4*)b;
-    float4* o4 = (float4*)out;
-    for (int i = threadIdx.x; i < n4; i += blockDim.x) {
-        float4 u = a4[i], v = b4[i];
-        o4[i] = make_float4(u.x - v.x, u.y - v.y, u.z - v.z, u.w - v.w);
-    }
-}
 __device__ __forceinline__ void vec_scale_copy(float* out, const float* a, double s, int n4) {
     const float fs = (float)s;
     const float4* a4 = (const float4*)a;
@@ -174,6 +165,107 @@ __device__ inline bool lbfgs_direction(SolveVecs& v, int hist, double* red) {
     return true;
 }
 
+// Several block-wide sums at once (all threads get all N results; deterministic order).  `red`: >= 33 doubles.
+template <int N>
+__device__ __forceinline__ void block_sum_multi(double (&v)[N], double* red) {
+    const int w = threadIdx.x >> 5, l = threadIdx.x & 31, nw = (blockDim.x + 31) >> 5;
+#pragma unroll
+    for (int k = 0; k < N; ++k)
+        for (int o = 16; o; o >>= 1) v[k] += __shfl_xor_sync(0xffffffffu, v[k], o);
+#pragma unroll
+    for (int k = 0; k < N; ++k) {
+        __syncthreads();
+        if (l == 0) red[w] = v[k];
+        __syncthreads();
+        double t = 0.0;
+        for (int i = 0; i < nw; ++i) t += red[i];
+        v[k] = t;
+    }
+}
+
+// Steepest-descent start and the one-pair two-loop recursion written as fused sweeps: the solver's vectors live in
+// global memory, so what a CTA pays for is the number of passes and block-wide reductions, not the flops.
+//   hist == 0: one pass      — d = -g, gg = g.g                               (dd0 = -gg, |d| = sqrt(gg))
+//   hist == 1: two passes    — (s.y, y.y, s.g, y.g, g.g), then d = -(diag (g - a y) + (a - beta) s) with
+//                              a = s.g / s.y, diag = s.y / y.y, beta = diag (y.g - a y.y) / s.y, and g.d, d.d
+// Same algebra as lbfgs_direction.  Returns false on a bad pair (s.y < 0 or NaN); gg is valid either way.
+__device__ inline bool lbfgs_direction_fused(SolveVecs& v, int hist, double* red, double& gg, double& dd0, double& dn) {
+    const float4* g4 = (const float4*)v.g;
+    float4* d4 = (float4*)v.d;
+    if (hist == 0) {
+        double acc[1] = {0.0};
+        float s = 0.f;
+        for (int i = threadIdx.x; i < v.n4; i += blockDim.x) {
+            const float4 g = g4[i];
+            d4[i] = make_float4(-g.x, -g.y, -g.z, -g.w);
+            s += g.x * g.x + g.y * g.y + g.z * g.z + g.w * g.w;
+        }
+        acc[0] = (double)s;
+        block_sum_multi(acc, red);
+        gg = acc[0], dd0 = -gg, dn = sqrt(gg);
+        return true;
+    }
+    const float4* s4 = (const float4*)v.s[0];
+    const float4* y4 = (const float4*)v.y[0];
+    float sy = 0.f, yy = 0.f, sg = 0.f, yg = 0.f, g2 = 0.f;
+    for (int i = threadIdx.x; i < v.n4; i += blockDim.x) {
+        const float4 g = g4[i], s = s4[i], y = y4[i];
+        sy += s.x * y.x + s.y * y.y + s.z * y.z + s.w * y.w;
+        yy += y.x * y.x + y.y * y.y + y.z * y.z + y.w * y.w;
+        sg += s.x * g.x + s.y * g.y + s.z * g.z + s.w * g.w;
+        yg += y.x * g.x + y.y * g.y + y.z * g.z + y.w * g.w;
+        g2 += g.x * g.x + g.y * g.y + g.z * g.z + g.w * g.w;
+    }
+    double acc[5] = {(double)sy, (double)yy, (double)sg, (double)yg, (double)g2};
+    block_sum_multi(acc, red);
+    gg = acc[4];
+    if (acc[0] < 0.0 || isnan(acc[0])) return false;
+    const double a = acc[2] / acc[0], diag = acc[0] / acc[1];
+    const double beta = diag * (acc[3] - a * acc[1]) / acc[0];
+    const float fa = (float)a, fdiag = (float)diag, fc = (float)(a - beta);
+    float gd = 0.f, d2 = 0.f;
+    for (int i = threadIdx.x; i < v.n4; i += blockDim.x) {
+        const float4 g = g4[i], s = s4[i], y = y4[i];
+        float4 d;
+        d.x = -fmaf(fc, s.x, fdiag * fmaf(-fa, y.x, g.x));
+        d.y = -fmaf(fc, s.y, fdiag * fmaf(-fa, y.y, g.y));
+        d.z = -fmaf(fc, s.z, fdiag * fmaf(-fa, y.z, g.z));
+        d.w = -fmaf(fc, s.w, fdiag * fmaf(-fa, y.w, g.w));
+        d4[i] = d;
+        gd += g.x * d.x + g.y * d.y + g.z * d.z + g.w * d.w;
+        d2 += d.x * d.x + d.y * d.y + d.z * d.z + d.w * d.w;
+    }
+    double acc2[2] = {(double)gd, (double)d2};
+    block_sum_multi(acc2, red);
+    dd0 = acc2[0], dn = sqrt(acc2[1]);
+    return true;
+}
+
+// s = xt - x and y = gt - g in one sweep (the new curvature pair)
+__device__ __forceinline__ void vec_pair_update(float* s, float* y, const float* xt, const float* x, const float* gt,
+                                                const float* g, int n4) {
+    for (int i = threadIdx.x; i < n4; i += blockDim.x) {
+        const float4 a = ((const float4*)xt)[i], b = ((const float4*)x)[i];
+        const float4 c = ((const float4*)gt)[i], e = ((const float4*)g)[i];
+        ((float4*)s)[i] = make_float4(a.x - b.x, a.y - b.y, a.z - b.z, a.w - b.w);
+        ((float4*)y)[i] = make_float4(c.x - e.x, c.y - e.y, c.z - e.z, c.w - e.w);
+    }
+}
+
+// direction + the three scalars the line search needs; fused sweeps for hist <= 1, the general recursion otherwise
+__device__ inline bool lbfgs_step_setup(SolveVecs& v, int hist, double* red, double& gg, double& dd0, double& dn) {
+    if (hist <= 1) {
+        const bool ok = lbfgs_direction_fused(v, hist, red, gg, dd0, dn);
+        __syncthreads();
+        return ok;
+    }
+    gg = block_dot(v.g, v.g, v.n4, red);
+    if (!lbfgs_direction(v, hist, red)) return false;
+    dd0 = block_dot(v.g, v.d, v.n4, red);
+    dn = sqrt(block_dot(v.d, v.d, v.n4, red));
+    return true;
+}
+
 // L-BFGS for evaluators that cache the logits.  The logits are linear in the parameters,
 // z(x + t d) = z(x) + t z(d), which makes every line-search trial after the first one free:
 //   * the first trial of an iteration is a full evaluation at x + t1 d (loss, gradient, and its logits Zt);
@@ -192,18 +284,19 @@ __device__ SolveResult local_solve_cached(Eval& ev, SolveVecs& v, int max_iter, 
     int hist = 0;
     const double tol = 1e-6;
     for (int it = 0; it < max_iter; ++it) {
-        const double gnorm = sqrt(block_dot(v.g, v.g, v.n4, red));
+        double gg = 0.0, dd0 = 0.0, dn = 0.0;
+        PSB_TRACE(10);
+        bool ok = lbfgs_step_setup(v, hist, red, gg, dd0, dn);
+        PSB_TRACE(11);
+        const double gnorm = sqrt(gg);
         if (gnorm <= fmax(tol * fabs(f), 1e-8)) {
             r.status = 1;
             break;
         }
-        bool ok = lbfgs_direction(v, hist, red);
         double alpha = 0.0, f_new = f, t_first = 0.0;
         bool derived = false;
         int calls = 0;
         if (ok) {
-            const double dd0 = block_dot(v.g, v.d, v.n4, red);
-            const double dn = sqrt(block_dot(v.d, v.d, v.n4, red));
             auto phi = [&](double t) {
                 ++r.evals;
                 Bracket b;
@@ -211,8 +304,11 @@ __device__ SolveResult local_solve_cached(Eval& ev, SolveVecs& v, int max_iter, 
                 if (calls++ == 0) {                                       // full evaluation, logits parked in Zd
                     vec_axpy_to(v.xt, v.x, t, v.d, v.n4);
                     __syncthreads();
+                    PSB_TRACE(12);
                     b.f = ev.eval_store(v.xt, v.gt, ev.Zd);
+                    PSB_TRACE(13);
                     b.dd = block_dot(v.gt, v.d, v.n4, red);
+                    PSB_TRACE(14);
                     t_first = t;
                     if (isinf(b.f) || isnan(b.f)) calls = 0;              // unusable logits: evaluate fully again
                 } else {
@@ -247,9 +343,9 @@ __device__ SolveResult local_solve_cached(Eval& ev, SolveVecs& v, int max_iter, 
                 float* py = v.y[i];
                 v.s[i] = v.s[i - 1], v.y[i] = v.y[i - 1], v.s[i - 1] = ps, v.y[i - 1] = py;
             }
-            vec_sub_to(v.s[0], v.xt, v.x, v.n4);
-            vec_sub_to(v.y[0], v.gt, v.g, v.n4);
+            vec_pair_update(v.s[0], v.y[0], v.xt, v.x, v.gt, v.g, v.n4);
             __syncthreads();
+            PSB_TRACE(15);
             if (hist < PSB_HIST - 1) ++hist;
             float* p = v.g;
             v.g = v.gt, v.gt = p;
@@ -281,18 +377,15 @@ __device__ SolveResult local_solve(Eval& ev, SolveVecs& v, int solver, int max_i
     int hist = 0;            // pairs stored; newest at index 0
     const double tol = 1e-6;
     for (int it = 0; it < max_iter; ++it) {
-        const double gg = block_dot(v.g, v.g, v.n4, red);
+        double gg = 0.0, dd0 = 0.0, dn = 0.0;
+        bool ok = lbfgs_step_setup(v, hist, red, gg, dd0, dn);
         const double gnorm = sqrt(gg);
         if (gnorm <= fmax(tol * fabs(f), 1e-8)) {
             r.status = 1;
             break;
         }
-        const bool bad = !lbfgs_direction(v, hist, red);
         double alpha = 0.0, f_new = f;
-        bool ok = !bad;
         if (ok) {
-            const double dd0 = block_dot(v.g, v.d, v.n4, red);
-            const double dn = sqrt(block_dot(v.d, v.d, v.n4, red));
             ok = strong_wolfe(ev, v, f, dd0, it == 0 ? 1.0 / dn : 1.0, red, r.evals, alpha, f_new);
             if (ok && alpha * gnorm < 1e-10) ok = false;
         }
@@ -305,8 +398,7 @@ __device__ SolveResult local_solve(Eval& ev, SolveVecs& v, int solver, int max_i
         float* y_last = v.y[PSB_HIST - 1];
         for (int i = PSB_HIST - 1; i > 0; --i) v.s[i] = v.s[i - 1], v.y[i] = v.y[i - 1];
         v.s[0] = s_last, v.y[0] = y_last;
-        vec_sub_to(v.s[0], v.xt, v.x, v.n4);
-        vec_sub_to(v.y[0], v.gt, v.g, v.n4);
+        vec_pair_update(v.s[0], v.y[0], v.xt, v.x, v.gt, v.g, v.n4);
         __syncthreads();
         if (hist < PSB_HIST) ++hist;
         float* p;
