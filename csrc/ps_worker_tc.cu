@@ -676,6 +676,8 @@ psb_worker_tc_kernel(const __grid_constant__ CUtensorMap tmX, PsbSolver sv, Comm
     sh.need_redo = &s_need_redo;
 
 #ifdef PSB_TC_TRACE
+    unsigned long long gt_start = 0;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(gt_start));
     if (tid == 0) psb_trace_n = 0;
     __syncthreads();
     PSB_TRACE(0);
@@ -801,6 +803,13 @@ psb_worker_tc_kernel(const __grid_constant__ CUtensorMap tmX, PsbSolver sv, Comm
     tc::tc_fence_before();
     __syncthreads();
     if (warp == 0) tc::tmem_dealloc(tmem, kTmemCols);
+#ifdef PSB_TC_TRACE                            // wall-clock (ns, low 31 bits) of this CTA's first and last instruction
+    if (tid == 0) {
+        unsigned long long gt_end;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(gt_end));
+        info_out[8 * w + 4] = (int)(gt_start & 0x7fffffffull), info_out[8 * w + 5] = (int)(gt_end & 0x7fffffffull);
+    }
+#endif
 }
 
 int psb_launch_worker_tc(const PsbSolver* s, const CommCtx& cx, int num_workers, const void* d_X, const int* d_labels,

@@ -29,6 +29,8 @@ for std in ((True,) if os.environ.get('ONLY_STD') else (True, False)):
         eng.step()
     e1.record()
     torch.cuda.synchronize()
+    tot = eng.info.cpu().float()[:, 7]
+    print(f"  per-CTA total cycles/64: min {tot.min():.0f} mean {tot.mean():.0f} max {tot.max():.0f}")
     info = eng.info.cpu().float().mean(0).tolist()
     print(f"standardize={std} W={W} ms/clock={e0.elapsed_time(e1) / steps:.4f} evals={info[0]:.2f} "
           f"cycles64 first={info[4]:.0f} solve={info[5]:.0f} push={info[6]:.0f} total={info[7]:.0f} status={eng.status()}")
