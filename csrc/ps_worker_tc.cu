@@ -90,6 +90,7 @@ struct TcEval {
     uint32_t tmem;
     TcShared sh;
     unsigned int zuse[2], ruse[2], guse;   // per-thread running barrier use counts (persist across evaluations)
+    int pass_no;                           // passes run so far (every thread counts them): parity = slab direction
     float* Zx;                             // cached logits of the current point / of the direction, [cap][8] each
     float* Zd;                             // (null: no caching, every trial is a full evaluation)
 #ifdef PSB_TC_PROFILE
@@ -121,8 +122,10 @@ struct TcEval {
         for (int b = 0; b < cap / kSlabRows; ++b) n += slab_active(b) ? 1 : 0;
         return n;
     }
-    // b-th slab index of the q-th active slab
+    // slab index of the q-th slab this pass visits.  Passes alternate direction: the slabs a pass ends on are the
+    // ones the next pass starts with, still in L2 (126 MB / 296 co-resident workers ~ 1.6 slabs each).
     __device__ int active_slab(int q) const {
+        if (pass_no & 1) q = num_active_slabs() - 1 - q;
         for (int b = 0; b < cap / kSlabRows; ++b)
             if (slab_active(b) && q-- == 0) return b;
         return 0;
@@ -183,7 +186,7 @@ struct TcEval {
                     if (!load(b, c, with_b ? tc::kL2EvictLast : tc::kL2EvictFirst)) return;
             if (with_b)
                 for (int c = 0; c < nkb; ++c)
-                    if (!load(b, c, tc::kL2EvictFirst)) return;
+                    if (!load(b, c, q + 2 >= S ? tc::kL2EvictLast : tc::kL2EvictFirst)) return;   // tail slabs: next pass starts here
         }
     }
 
@@ -395,12 +398,26 @@ struct TcEval {
         const bool fused = cfg.fused;
         const int nkb = F / kBlockK, S = num_active_slabs();
         float lsum = 0.f, rs[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-        const float* bias = sh.sred + 16;            // intercepts staged behind the reduction words
+        float bias[8];                               // intercepts staged behind the reduction words
+#pragma unroll
+        for (int c = 0; c < 8; ++c) bias[c] = sh.sred[16 + c];
+        const int r = wi * 32 + lane;
+        // the label of the NEXT slab's row is requested before waiting for this slab's logits, so that its latency
+        // is not part of the z_full -> r_full path the MMA warp sits on
+        int lab_next = 0;
+        if (S > 0) {
+            const int s0 = active_slab(0) * kSlabRows + r;
+            lab_next = row_valid(s0) ? labels[s0] : 0;
+        }
         for (int q = 0; q < S; ++q) {
             const int b = active_slab(q), zb = q & 1;
-            const int r = wi * 32 + lane;
             const int slot = b * kSlabRows + r;
             const bool valid = row_valid(slot);
+            const int lab = lab_next;
+            if (q + 1 < S) {
+                const int s1 = active_slab(q + 1) * kSlabRows + r;
+                lab_next = row_valid(s1) ? labels[s1] : 0;
+            }
             float z[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
             if (cfg.a) {
                 if (!wait_or_fail(sh.z_full + zb, zuse[zb] & 1, sh.fail)) return;
@@ -430,7 +447,7 @@ struct TcEval {
             }
             float rr[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
             if (valid) {
-                lsum += softmax_residual(z, bias, labels[slot], R, rr);
+                lsum += softmax_residual(z, bias, lab, R, rr);
 #pragma unroll
                 for (int c = 0; c < 8; ++c) rs[c] += rr[c];
             }
@@ -555,6 +572,7 @@ struct TcEval {
             *sh.chunk_base += (unsigned)((cfg.a ? 1 : 0) + (cfg.b ? 1 : 0)) * (unsigned)num_active_slabs() * (F / kBlockK);
         if (cfg.b && tid < 8) g[F * 8 + tid] = sh.sred[1 + tid] * invn;
         const double loss = (double)sh.sred[0] * (double)invn;
+        ++pass_no;
         __syncthreads();
 #if PSB_TC_PROFILE == 3
         prof[2] += clock64() - tq2;
@@ -733,6 +751,7 @@ psb_worker_tc_kernel(const __grid_constant__ CUtensorMap tmX, PsbSolver sv, Comm
         ev.start = start, ev.count = count, ev.cap = cap, ev.F = F, ev.R = R, ev.kNS = kNS;
         ev.tmem = tmem, ev.sh = sh;
         ev.zuse[0] = ev.zuse[1] = ev.ruse[0] = ev.ruse[1] = ev.guse = 0;
+        ev.pass_no = 0;
         // logit cache in two spare solver vectors (the L-BFGS pairs of index PSB_HIST-1 are never reached when
         // max_iter <= PSB_HIST-1): [cap][8] floats each must fit one parameter vector
         const bool cached = sv.solver == PSB_SOLVER_LBFGS && cap * 8 <= nv && sv.max_iter <= PSB_HIST - 1;
