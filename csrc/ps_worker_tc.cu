@@ -39,25 +39,35 @@ constexpr int kColG = 32;                              // G tile j at 32 + 16*j
 // (Rotating consecutive MMAs over independent accumulators was measured: no gain — an SS-mode
 //  128x16x16 MMA costs ~80 cycles of operand fetch regardless of accumulator dependencies.)
 
+// Dynamic shared memory of the kernel.  The carve-up is kept as 32-bit offsets from this symbol and turned into
+// pointers by the accessors below: pointers derived from a __shared__ symbol stay in the shared window for the
+// compiler (LDS / STS / ATOMS with 32-bit addresses), where pointers parked in a struct degrade to generic
+// 64-bit ones — and seventeen of those cost thirty-four registers of a kernel that runs at the 128-register cap.
+extern __shared__ __align__(1024) unsigned char psb_tc_smem[];
+
 struct TcShared {
-    unsigned char* ring;      // kNS x 16 KB, 1024-aligned
-    unsigned char* sB;        // nkb x 2 KB
-    unsigned char* sR;        // 4 KB Rsp + 4 KB per-feature sums of the fused statistics
-    float* inv;               // [F]
-    float* sred;              // [32]
-    double* red;              // [34]
-    uint64_t* full;           // [kNS]
-    uint64_t* empty;          // [kNS]
-    uint64_t* z_full;         // [2]
-    uint64_t* r_full;         // [2]
-    uint64_t* g_full;
-    uint64_t* sdone;          // [kNS] statistics warps finished reading the slot (fused first evaluation)
-    uint64_t* inv_ready;      // 1/std written (fused first evaluation)
-    uint32_t* tmem_slot;
-    volatile int* fail;
-    volatile unsigned int* chunk_base;   // ring position (chunks streamed so far), shared by all roles
-    volatile int* need_redo;             // a constant non-zero column was found: redo the first evaluation
+    uint32_t o_ring, o_sB, o_sR, o_inv, o_sred, o_red, o_bar;   // offsets from psb_tc_smem
+    int kNS;
+    __device__ __forceinline__ unsigned char* ring() const { return psb_tc_smem + o_ring; }      // kNS x 16 KB, 1024-aligned
+    __device__ __forceinline__ unsigned char* sB() const { return psb_tc_smem + o_sB; }          // nkb x 2 KB
+    __device__ __forceinline__ unsigned char* sR() const { return psb_tc_smem + o_sR; }          // 4 KB Rsp + 4 KB statistics sums
+    __device__ __forceinline__ float* inv() const { return (float*)(psb_tc_smem + o_inv); }      // [F]
+    __device__ __forceinline__ float* sred() const { return (float*)(psb_tc_smem + o_sred); }    // [32]
+    __device__ __forceinline__ double* red() const { return (double*)(psb_tc_smem + o_red); }    // [34]
+    __device__ __forceinline__ uint64_t* bars() const { return (uint64_t*)(psb_tc_smem + o_bar); }
+    __device__ __forceinline__ uint64_t* full() const { return bars(); }                          // [kNS]
+    __device__ __forceinline__ uint64_t* empty() const { return bars() + kNS; }                   // [kNS]
+    __device__ __forceinline__ uint64_t* z_full() const { return bars() + 2 * kNS; }              // [2]
+    __device__ __forceinline__ uint64_t* r_full() const { return bars() + 2 * kNS + 2; }          // [2]
+    __device__ __forceinline__ uint64_t* g_full() const { return bars() + 2 * kNS + 4; }
+    __device__ __forceinline__ uint64_t* sdone() const { return bars() + 2 * kNS + 5; }           // [kNS] statistics warps done with the slot
+    __device__ __forceinline__ uint64_t* inv_ready() const { return bars() + 3 * kNS + 5; }       // 1/std written (fused first evaluation)
+    __device__ __forceinline__ uint32_t* tmem_slot() const { return (uint32_t*)(bars() + 3 * kNS + 6); }
 };
+// control words shared by all roles
+__shared__ int psb_tc_fail;                    // a bounded wait gave up
+__shared__ unsigned int psb_tc_chunk_base;     // ring position (chunks streamed so far)
+__shared__ int psb_tc_need_redo;               // a constant non-zero column was found: redo the first evaluation
 
 __device__ __forceinline__ bool wait_or_fail(uint64_t* bar, uint32_t parity, volatile int* fail) {
     if (tc::mbar_try_wait(bar, parity)) return true;            // common case: no clock read, no fail poll
@@ -139,7 +149,7 @@ struct TcEval {
         const int nkb = F / kBlockK, S = num_active_slabs();
         // ring position as running (slot, use) counters: this thread is alone on its warp, so the latency of a
         // runtime integer division per chunk (~100 cycles each) would pace the whole stream
-        const unsigned int pc0 = *sh.chunk_base;
+        const unsigned int pc0 = psb_tc_chunk_base;
         int slot = (int)(pc0 % (unsigned)kNS);
         unsigned int use = pc0 / (unsigned)kNS;
         int idx = 0;                          // chunks issued in this pass
@@ -150,7 +160,7 @@ struct TcEval {
 #if PSB_TC_PROFILE == 2
             const long long te = clock64();
 #endif
-            if (use > 0 && !wait_or_fail(sh.empty + slot, (use - 1) & 1, sh.fail)) return false;
+            if (use > 0 && !wait_or_fail(sh.empty() + slot, (use - 1) & 1, &psb_tc_fail)) return false;
 #if PSB_TC_PROFILE == 2
             const long long ts = clock64();
             prof[0] += ts - te;
@@ -158,7 +168,7 @@ struct TcEval {
             if (fused && idx >= kNS) {        // previous occupant of the slot: chunk idx - kNS of this pass;
                                               // the statistics warps read it on its A use when c % 4 < 2, else on its B use
                 if ((((lag_c >> 1) & 1) == 0) == lag_a) {
-                    if (!wait_or_fail(sh.sdone + slot, (sd_par >> slot) & 1u, sh.fail)) return false;
+                    if (!wait_or_fail(sh.sdone() + slot, (sd_par >> slot) & 1u, &psb_tc_fail)) return false;
                     sd_par ^= 1u << slot;
                 }
                 if (++lag_c == nkb) lag_c = 0, lag_a = !lag_a;
@@ -167,11 +177,11 @@ struct TcEval {
             prof[1] += clock64() - ts;
 #endif
 #ifdef PSB_TC_EXPERIMENT_NO_TMA                // timing experiment only: no data movement, barriers still cycle
-            tc::mbar_arrive(sh.full + slot);
+            tc::mbar_arrive(sh.full() + slot);
 #else
-            tc::mbar_arrive_expect_tx(sh.full + slot, kChunkBytes);
-            tc::tma_load_2d_hint(sh.ring + (size_t)slot * kChunkBytes, tmX, c * kBlockK, row_base + b * kSlabRows,
-                                 sh.full + slot, policy);
+            tc::mbar_arrive_expect_tx(sh.full() + slot, kChunkBytes);
+            tc::tma_load_2d_hint(sh.ring() + (size_t)slot * kChunkBytes, tmX, c * kBlockK, row_base + b * kSlabRows,
+                                 sh.full() + slot, policy);
 #endif
             ++idx;
             if (++slot == kNS) slot = 0, ++use;
@@ -200,11 +210,11 @@ struct TcEval {
     __device__ void stats_fused(int wi, int lane) const {
         const int nkb = F / kBlockK, S = num_active_slabs();
         // this warp's chunks are base + wi, base + wi + 2, ... through every A(q) B(q): one stride-2 walk of the ring
-        const unsigned int pc0 = *sh.chunk_base + (unsigned)wi;
+        const unsigned int pc0 = psb_tc_chunk_base + (unsigned)wi;
         int slot = (int)(pc0 % (unsigned)kNS);
         uint32_t phase = (pc0 / (unsigned)kNS) & 1u;
-        float* ssum = (float*)(sh.sR + kRBytes);
-        float* ssq = sh.inv;
+        float* ssum = (float*)(sh.sR() + kRBytes);
+        float* ssq = sh.inv();
         const int h = lane >> 4, j8 = lane & 15;
 #ifdef PSB_TC_TRACE
         long long st_wait = 0, st_read = 0;
@@ -221,13 +231,13 @@ struct TcEval {
 #ifdef PSB_TC_TRACE
                     const long long tw0 = clock64();
 #endif
-                    if (!wait_or_fail(sh.full + slot, phase, sh.fail)) return;
+                    if (!wait_or_fail(sh.full() + slot, phase, &psb_tc_fail)) return;
 #ifdef PSB_TC_TRACE
                     const long long tw1 = clock64();
                     st_wait += tw1 - tw0;
 #endif
                     if (((c >> 1) & 1) == pass) {
-                        const uint32_t tile = tc::smem_u32(sh.ring) + (uint32_t)slot * kChunkBytes + (j8 & 1) * 8;
+                        const uint32_t tile = tc::smem_u32(sh.ring()) + (uint32_t)slot * kChunkBytes + (j8 & 1) * 8;
                         float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f, q0 = 0.f, q1 = 0.f, q2 = 0.f, q3 = 0.f;
 #ifdef PSB_TC_EXPERIMENT_NO_STATS_LDS          // timing experiment only (wrong statistics)
                         if (slot < 0)
@@ -268,7 +278,7 @@ struct TcEval {
                             tc::sts_f4(pq, make_float4(v.x + q0, v.y + q1, v.z + q2, v.w + q3));
                         }
                         __syncwarp();
-                        if (lane == 0) tc::mbar_arrive(sh.sdone + slot);
+                        if (lane == 0) tc::mbar_arrive(sh.sdone() + slot);
 #ifdef PSB_TC_TRACE
                         st_read += clock64() - tw1, ++st_chunks;
 #endif
@@ -298,10 +308,10 @@ struct TcEval {
                 redo = redo || (iv == 0.f && s2 != 0.f);
             }
         }
-        if (redo) *sh.need_redo = 1;
+        if (redo) psb_tc_need_redo = 1;
         __threadfence_block();
         __syncwarp();
-        if (lane == 0) tc::mbar_arrive(sh.inv_ready);
+        if (lane == 0) tc::mbar_arrive(sh.inv_ready());
     }
 
     // ---- MMA issuer: the whole warp walks the ring in stream order (warp-uniform state), one elected
@@ -311,18 +321,18 @@ struct TcEval {
         constexpr uint32_t idesc1 = tc::idesc_f16(128, 16, 0, 0);    // GEMM1: A K-major, B K-major
         constexpr uint32_t idesc2 = tc::idesc_f16(128, 16, 1, 1);    // GEMM2: A MN-major, B MN-major
         // ring position as running (slot, phase) counters — no per-chunk integer divisions on the issue path
-        const unsigned int pc0 = __shfl_sync(0xffffffffu, *sh.chunk_base, 0);
+        const unsigned int pc0 = __shfl_sync(0xffffffffu, psb_tc_chunk_base, 0);
         int slot = (int)(pc0 % (unsigned)kNS);
         uint32_t phase = (pc0 / (unsigned)kNS) & 1u;
         const uint32_t tmem_u = __shfl_sync(0xffffffffu, tmem, 0);
-        const uint32_t sB0 = tc::smem_u32(sh.sB), sR0 = tc::smem_u32(sh.sR), ring0 = tc::smem_u32(sh.ring);
+        const uint32_t sB0 = tc::smem_u32(sh.sB()), sR0 = tc::smem_u32(sh.sR()), ring0 = tc::smem_u32(sh.ring());
 
         auto gemm1 = [&](int q) -> bool {                       // Z_{q&1} = A(q) x Wsp
             for (int c = 0; c < nkb; ++c) {
 #ifdef PSB_TC_PROFILE
                 const long long tw = clock64();
 #endif
-                if (!wait_or_fail(sh.full + slot, phase, sh.fail)) return false;
+                if (!wait_or_fail(sh.full() + slot, phase, &psb_tc_fail)) return false;
 #ifdef PSB_TC_PROFILE
                 prof[0] += clock64() - tw;
 #endif
@@ -335,8 +345,8 @@ struct TcEval {
                     for (int k = 0; k < kBlockK / 16; ++k)
                         tc::umma_f16(tmem_u + kColZ + 16 * (q & 1), ad + 2 * k, bd + 2 * k, idesc1, (c | k) ? 1u : 0u);
 #endif
-                    tc::umma_commit(sh.empty + slot);
-                    if (c == nkb - 1) tc::umma_commit(sh.z_full + (q & 1));
+                    tc::umma_commit(sh.empty() + slot);
+                    if (c == nkb - 1) tc::umma_commit(sh.z_full() + (q & 1));
                 }
                 __syncwarp();
                 if (++slot == kNS) slot = 0, phase ^= 1u;
@@ -347,7 +357,7 @@ struct TcEval {
 #ifdef PSB_TC_PROFILE
             const long long tr = clock64();
 #endif
-            if (!wait_or_fail(sh.r_full, ruse[0] & 1, sh.fail)) return false;
+            if (!wait_or_fail(sh.r_full(), ruse[0] & 1, &psb_tc_fail)) return false;
             ++ruse[0];
 #ifdef PSB_TC_PROFILE
             prof[1] += clock64() - tr;
@@ -357,8 +367,8 @@ struct TcEval {
 #ifdef PSB_TC_PROFILE
                 const long long tb = clock64();
 #endif
-                if (!wait_or_fail(sh.full + slot, phase, sh.fail)) return false;
-                if (!wait_or_fail(sh.full + slot + 1, phase, sh.fail)) return false;
+                if (!wait_or_fail(sh.full() + slot, phase, &psb_tc_fail)) return false;
+                if (!wait_or_fail(sh.full() + slot + 1, phase, &psb_tc_fail)) return false;
 #ifdef PSB_TC_PROFILE
                 prof[2] += clock64() - tb;
 #endif
@@ -372,8 +382,8 @@ struct TcEval {
                         tc::umma_f16(tmem_u + kColG + 16 * j, ad0 + (uint64_t)(ks * 128), bd0 + (uint64_t)(ks * 32),
                                      idesc2, (q | ks) ? 1u : 0u);
 #endif
-                    tc::umma_commit(sh.empty + slot);
-                    tc::umma_commit(sh.empty + slot + 1);
+                    tc::umma_commit(sh.empty() + slot);
+                    tc::umma_commit(sh.empty() + slot + 1);
                 }
                 __syncwarp();
                 slot += 2;
@@ -385,11 +395,11 @@ struct TcEval {
             if (cfg.a && !gemm1(q)) return;
             if (cfg.b && !gemm2(q)) return;
             if (cfg.b && !cfg.a) {           // gradient-only pass: tell the residual warps that Rsp(q) has been consumed
-                if (tc::elect_one()) tc::umma_commit(sh.z_full + (q & 1));
+                if (tc::elect_one()) tc::umma_commit(sh.z_full() + (q & 1));
                 __syncwarp();
             }
         }
-        if (cfg.b && tc::elect_one()) tc::umma_commit(sh.g_full);
+        if (cfg.b && tc::elect_one()) tc::umma_commit(sh.g_full());
         __syncwarp();
     }
 
@@ -400,7 +410,7 @@ struct TcEval {
         float lsum = 0.f, rs[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
         float bias[8];                               // intercepts staged behind the reduction words
 #pragma unroll
-        for (int c = 0; c < 8; ++c) bias[c] = sh.sred[16 + c];
+        for (int c = 0; c < 8; ++c) bias[c] = sh.sred()[16 + c];
         const int r = wi * 32 + lane;
         // the label of the NEXT slab's row is requested before waiting for this slab's logits, so that its latency
         // is not part of the z_full -> r_full path the MMA warp sits on
@@ -420,7 +430,7 @@ struct TcEval {
             }
             float z[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
             if (cfg.a) {
-                if (!wait_or_fail(sh.z_full + zb, zuse[zb] & 1, sh.fail)) return;
+                if (!wait_or_fail(sh.z_full() + zb, zuse[zb] & 1, &psb_tc_fail)) return;
                 ++zuse[zb];
                 tc::tc_fence_after();
                 float v[16];
@@ -436,7 +446,7 @@ struct TcEval {
                 // gradient-only pass: nothing paces these warps but the single Rsp buffer — wait until GEMM2(q-1)
                 // has consumed it (the MMA warp commits z_full[(q-1)&1] behind that GEMM)
                 if (q >= 1) {
-                    if (!wait_or_fail(sh.z_full + ((q - 1) & 1), zuse[(q - 1) & 1] & 1, sh.fail)) return;
+                    if (!wait_or_fail(sh.z_full() + ((q - 1) & 1), zuse[(q - 1) & 1] & 1, &psb_tc_fail)) return;
                     ++zuse[(q - 1) & 1];
                 }
             }
@@ -456,16 +466,16 @@ struct TcEval {
             __align__(16) __half hi[8], lo[8];
 #pragma unroll
             for (int c = 0; c < 8; ++c) tc::split_half(rr[c], hi[c], lo[c]);
-            const uint32_t dst = tc::smem_u32(sh.sR) + (r >> 3) * 256 + (r & 7) * 16;
+            const uint32_t dst = tc::smem_u32(sh.sR()) + (r >> 3) * 256 + (r & 7) * 16;
             tc::sts_v4(dst, *(const uint4*)hi);
             tc::sts_v4(dst + 128, *(const uint4*)lo);
             tc::fence_proxy_async_smem();
             tc::tc_fence_before();
             __syncwarp();
-            if (lane == 0) tc::mbar_arrive(sh.r_full);
+            if (lane == 0) tc::mbar_arrive(sh.r_full());
         }
         if (!cfg.a && S >= 1) {                  // consume the last "Rsp consumed" commit of a gradient-only pass
-            if (!wait_or_fail(sh.z_full + ((S - 1) & 1), zuse[(S - 1) & 1] & 1, sh.fail)) return;
+            if (!wait_or_fail(sh.z_full() + ((S - 1) & 1), zuse[(S - 1) & 1] & 1, &psb_tc_fail)) return;
             ++zuse[(S - 1) & 1];
         }
         for (int o = 16; o; o >>= 1) {
@@ -474,20 +484,20 @@ struct TcEval {
             for (int c = 0; c < 8; ++c) rs[c] += __shfl_xor_sync(0xffffffffu, rs[c], o);
         }
         if (lane == 0) {
-            atomicAdd(&sh.sred[0], lsum);
+            atomicAdd(&sh.sred()[0], lsum);
 #pragma unroll
-            for (int c = 0; c < 8; ++c) atomicAdd(&sh.sred[1 + c], rs[c]);
+            for (int c = 0; c < 8; ++c) atomicAdd(&sh.sred()[1 + c], rs[c]);
         }
         // drain the gradient accumulators: thread = feature row of each 128-feature tile
-        if (fused && !wait_or_fail(sh.inv_ready, 0, sh.fail)) return;
-        if (!wait_or_fail(sh.g_full, guse & 1, sh.fail)) return;
+        if (fused && !wait_or_fail(sh.inv_ready(), 0, &psb_tc_fail)) return;
+        if (!wait_or_fail(sh.g_full(), guse & 1, &psb_tc_fail)) return;
         ++guse;
         tc::tc_fence_after();
         for (int j = 0; j < nkb / 2; ++j) {
             float v[16];
             tc::tmem_ld_32x32b_x16(tmem + kColG + 16 * j + ((uint32_t)(wi * 32) << 16), v);
             const int f = j * 128 + wi * 32 + lane;
-            const float sc = sh.inv[f] * invn;
+            const float sc = sh.inv()[f] * invn;
             float4* g4 = (float4*)g + 2 * f;
             g4[0] = make_float4((v[0] + v[8]) * sc, (v[1] + v[9]) * sc, (v[2] + v[10]) * sc, (v[3] + v[11]) * sc);
             g4[1] = make_float4((v[4] + v[12]) * sc, (v[5] + v[13]) * sc, (v[6] + v[14]) * sc, (v[7] + v[15]) * sc);
@@ -497,7 +507,7 @@ struct TcEval {
 
     // ---- no standardisation: 1/std = 1 (all threads enter)
     __device__ void unit_scale() {
-        for (int f = threadIdx.x; f < F; f += blockDim.x) sh.inv[f] = 1.f;
+        for (int f = threadIdx.x; f < F; f += blockDim.x) sh.inv()[f] = 1.f;
         __syncthreads();
     }
 
@@ -514,10 +524,10 @@ struct TcEval {
             // Wsp = (x * inv) split into fp16 hi | lo, K-major SWIZZLE_128B, 16 rows per 64-feature chunk
             for (int f = tid; f < F; f += blockDim.x) {
                 const float4 a = ((const float4*)x)[2 * f], b = ((const float4*)x)[2 * f + 1];
-                const float sc = cfg.fused ? 1.f : sh.inv[f];
+                const float sc = cfg.fused ? 1.f : sh.inv()[f];
                 const float w[8] = {a.x * sc, a.y * sc, a.z * sc, a.w * sc, b.x * sc, b.y * sc, b.z * sc, b.w * sc};
                 const int kb = f >> 6, k = f & 63, j = k >> 3, e = k & 7;
-                const uint32_t chunk = tc::smem_u32(sh.sB) + (uint32_t)kb * kBChunkBytes + e * 2;
+                const uint32_t chunk = tc::smem_u32(sh.sB()) + (uint32_t)kb * kBChunkBytes + e * 2;
 #pragma unroll
                 for (int c = 0; c < 8; ++c) {
                     __half hi, lo;
@@ -527,10 +537,10 @@ struct TcEval {
                 }
             }
         }
-        if (tid < 16) sh.sred[tid] = 0.f;
-        if (tid < 8) sh.sred[16 + tid] = x[F * 8 + tid];          // intercepts (unscaled)
+        if (tid < 16) sh.sred()[tid] = 0.f;
+        if (tid < 8) sh.sred()[16 + tid] = x[F * 8 + tid];          // intercepts (unscaled)
         if (cfg.fused)
-            for (int f = tid; f < F; f += blockDim.x) sh.inv[f] = 0.f, ((float*)(sh.sR + kRBytes))[f] = 0.f;
+            for (int f = tid; f < F; f += blockDim.x) sh.inv()[f] = 0.f, ((float*)(sh.sR() + kRBytes))[f] = 0.f;
         tc::fence_proxy_async_smem();
         __syncthreads();
         const float invn = 1.f / (float)count;
@@ -569,9 +579,9 @@ struct TcEval {
         prof[1] += tq2 - tq1;
 #endif
         if (tid == 0)
-            *sh.chunk_base += (unsigned)((cfg.a ? 1 : 0) + (cfg.b ? 1 : 0)) * (unsigned)num_active_slabs() * (F / kBlockK);
-        if (cfg.b && tid < 8) g[F * 8 + tid] = sh.sred[1 + tid] * invn;
-        const double loss = (double)sh.sred[0] * (double)invn;
+            psb_tc_chunk_base += (unsigned)((cfg.a ? 1 : 0) + (cfg.b ? 1 : 0)) * (unsigned)num_active_slabs() * (F / kBlockK);
+        if (cfg.b && tid < 8) g[F * 8 + tid] = sh.sred()[1 + tid] * invn;
+        const double loss = (double)sh.sred()[0] * (double)invn;
         ++pass_no;
         __syncthreads();
 #if PSB_TC_PROFILE == 3
@@ -637,8 +647,8 @@ struct TcEval {
             for (int c = 0; c < 8; ++c) dsum = fmaf(rr[c], zd[c] + bd[c], dsum);
         }
         const double n = (double)count;
-        f = block_sum((double)lsum, sh.red) / n;
-        dd = block_sum((double)dsum, sh.red) / n;
+        f = block_sum((double)lsum, sh.red()) / n;
+        dd = block_sum((double)dsum, sh.red()) / n;
 #ifdef PSB_TC_DEBUG
         if (blockIdx.x == 0 && threadIdx.x == 0) printf("trial t=%g f=%g dd=%g\n", t, f, dd);
 #endif
@@ -665,33 +675,19 @@ psb_worker_tc_kernel(const __grid_constant__ CUtensorMap tmX, PsbSolver sv, Comm
                      const int* __restrict__ labels, const int* __restrict__ win, const float* __restrict__ w_in,
                      float* __restrict__ delta_out, float* __restrict__ loss_out, int* __restrict__ info_out,
                      float* __restrict__ scratch) {
-    extern __shared__ __align__(1024) unsigned char smem_raw[];
-    unsigned char* smem = (unsigned char*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
     const int F = sv.num_features, R = sv.num_class_rows, cap = sv.cap;
     const int nv = (F + 1) * 8, n4 = nv / 4, nkb = F / kBlockK;
     const int w = blockIdx.x, tid = threadIdx.x, warp = tid >> 5;
-    __shared__ int s_fail;
-    __shared__ unsigned int s_chunk_base;
-    __shared__ int s_need_redo;
 
     TcShared sh;
-    sh.ring = smem;
-    sh.sB = sh.ring + (size_t)kNS * kChunkBytes;
-    sh.sR = sh.sB + (size_t)nkb * kBChunkBytes;
-    sh.inv = (float*)(sh.sR + 2 * kRBytes);
-    sh.sred = sh.inv + F;
-    sh.red = (double*)(sh.sred + 32);
-    sh.full = (uint64_t*)(sh.red + 34);
-    sh.empty = sh.full + kNS;
-    sh.z_full = sh.empty + kNS;
-    sh.r_full = sh.z_full + 2;
-    sh.g_full = sh.r_full + 2;
-    sh.sdone = sh.g_full + 1;
-    sh.inv_ready = sh.sdone + kNS;
-    sh.tmem_slot = (uint32_t*)(sh.inv_ready + 1);
-    sh.fail = &s_fail;
-    sh.chunk_base = &s_chunk_base;
-    sh.need_redo = &s_need_redo;
+    sh.kNS = kNS;
+    sh.o_ring = (1024u - (tc::smem_u32(psb_tc_smem) & 1023u)) & 1023u;      // the ring wants 1024-byte alignment
+    sh.o_sB = sh.o_ring + (uint32_t)kNS * kChunkBytes;
+    sh.o_sR = sh.o_sB + (uint32_t)nkb * kBChunkBytes;
+    sh.o_inv = sh.o_sR + 2 * kRBytes;
+    sh.o_sred = sh.o_inv + (uint32_t)F * 4;
+    sh.o_red = sh.o_sred + 32 * 4;
+    sh.o_bar = sh.o_red + 34 * 8;
 
 #ifdef PSB_TC_TRACE
     unsigned long long gt_start = 0;
@@ -701,20 +697,20 @@ psb_worker_tc_kernel(const __grid_constant__ CUtensorMap tmX, PsbSolver sv, Comm
     PSB_TRACE(0);
 #endif
     if (tid == 0) {
-        s_fail = 0, s_chunk_base = 0, s_need_redo = 0;
+        psb_tc_fail = 0, psb_tc_chunk_base = 0, psb_tc_need_redo = 0;
         tc::tma_prefetch_desc(&tmX);
-        for (int s = 0; s < kNS; ++s) tc::mbar_init(sh.full + s, 1), tc::mbar_init(sh.empty + s, 1);
-        for (int i = 0; i < 2; ++i) tc::mbar_init(sh.z_full + i, 1), tc::mbar_init(sh.r_full + i, 4);
-        tc::mbar_init(sh.g_full, 1);
-        for (int s = 0; s < kNS; ++s) tc::mbar_init(sh.sdone + s, 1);
-        tc::mbar_init(sh.inv_ready, 2);
+        for (int s = 0; s < kNS; ++s) tc::mbar_init(sh.full() + s, 1), tc::mbar_init(sh.empty() + s, 1);
+        for (int i = 0; i < 2; ++i) tc::mbar_init(sh.z_full() + i, 1), tc::mbar_init(sh.r_full() + i, 4);
+        tc::mbar_init(sh.g_full(), 1);
+        for (int s = 0; s < kNS; ++s) tc::mbar_init(sh.sdone() + s, 1);
+        tc::mbar_init(sh.inv_ready(), 2);
         tc::mbar_fence_init();
     }
-    if (warp == 0) tc::tmem_alloc(sh.tmem_slot, kTmemCols);
+    if (warp == 0) tc::tmem_alloc(sh.tmem_slot(), kTmemCols);
     tc::tc_fence_before();
     __syncthreads();
     tc::tc_fence_after();
-    const uint32_t tmem = *sh.tmem_slot;
+    const uint32_t tmem = *sh.tmem_slot();
 
     WorkerScratch ws(scratch + (size_t)w * PSB_SCRATCH_VECS * nv, nv);
     const int head = win[2 * w], count = win[2 * w + 1];
@@ -771,34 +767,34 @@ psb_worker_tc_kernel(const __grid_constant__ CUtensorMap tmX, PsbSolver sv, Comm
         PSB_TRACE(2);
         if (sv.standardize) {
             f0 = ev.eval_first_fused(w0, v.g);
-            have_f0 = !s_need_redo;
+            have_f0 = !psb_tc_need_redo;
         } else {
             ev.unit_scale();
         }
         const long long t_stats = clock64();
         PSB_TRACE(3);
-        to_scaled_space(v.x, w0, sh.inv, F);
+        to_scaled_space(v.x, w0, sh.inv(), F);
         __syncthreads();
         PSB_TRACE(4);
 
         SolveResult res;
         if (cached) {
             if (!have_f0) f0 = ev.eval(v.x, v.g);                    // (also fills the logit cache)
-            res = local_solve_cached(ev, v, sv.max_iter, sh.red, f0);
+            res = local_solve_cached(ev, v, sv.max_iter, sh.red(), f0);
         } else {
-            res = local_solve(ev, v, sv.solver, sv.max_iter, sv.sgd_lr, sh.red, have_f0, f0);
+            res = local_solve(ev, v, sv.solver, sv.max_iter, sv.sgd_lr, sh.red(), have_f0, f0);
         }
         const long long t_solve = clock64();
         PSB_TRACE(5);
 
         float* delta = v.tmp;
-        finish_delta(delta, v.x, w0, sh.inv, F, R, sv.center && sv.solver == PSB_SOLVER_LBFGS);
+        finish_delta(delta, v.x, w0, sh.inv(), F, R, sv.center && sv.solver == PSB_SOLVER_LBFGS);
         __syncthreads();
         PSB_TRACE(6);
         if (tid == 0) {
-            loss_out[w] = s_fail ? nanf("") : (float)res.loss;
+            loss_out[w] = psb_tc_fail ? nanf("") : (float)res.loss;
             info_out[8 * w + 0] = res.evals, info_out[8 * w + 1] = res.iterations;
-            info_out[8 * w + 2] = s_fail ? -2 : res.status, info_out[8 * w + 3] = count;
+            info_out[8 * w + 2] = psb_tc_fail ? -2 : res.status, info_out[8 * w + 3] = count;
             info_out[8 * w + 4] = (int)((t_stats - t_begin) >> 6), info_out[8 * w + 5] = (int)((t_solve - t_stats) >> 6);
         }
         if (cx.c.mode == PSB_COMM_NONE) {
