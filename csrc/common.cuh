@@ -178,7 +178,18 @@ __device__ __forceinline__ double block_sum(double v, double* red) {
     __syncthreads();
     return red[32];
 }
+// Ask L1 for this thread's strides of a parameter-sized vector.  The solver's vectors live in global memory and a
+// pass over one is a chain of ~8 dependent load-use round trips per thread; the prefetches put those round trips
+// in flight together without holding registers (batching the loads in registers spills: the kernels that use
+// these helpers run at their register cap).
+__device__ __forceinline__ void vec_prefetch(const float* p, int n4) {
+    const float4* p4 = (const float4*)p;
+    for (int i = threadIdx.x; i < n4; i += blockDim.x) asm volatile("prefetch.global.L1 [%0];" ::"l"(p4 + i));
+}
+
 __device__ __forceinline__ double block_dot(const float* a, const float* b, int n4, double* red) {
+    vec_prefetch(a, n4);
+    if (b != a) vec_prefetch(b, n4);
     float s = 0.f;
     const float4* a4 = (const float4*)a;
     const float4* b4 = (const float4*)b;

@@ -522,6 +522,7 @@ struct TcEval {
         PSB_TRACE(20);
         if (cfg.a) {
             // Wsp = (x * inv) split into fp16 hi | lo, K-major SWIZZLE_128B, 16 rows per 64-feature chunk
+            vec_prefetch(x, F * 2);
             for (int f = tid; f < F; f += blockDim.x) {
                 const float4 a = ((const float4*)x)[2 * f], b = ((const float4*)x)[2 * f + 1];
                 const float sc = cfg.fused ? 1.f : sh.inv()[f];

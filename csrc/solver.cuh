@@ -31,6 +31,8 @@ struct SolveResult {
 };
 
 __device__ __forceinline__ void vec_axpy_to(float* out, const float* x, double a, const float* d, int n4) {
+    vec_prefetch(x, n4);
+    vec_prefetch(d, n4);
     const float fa = (float)a;
     const float4* x4 = (const float4*)x;
     const float4* d4 = (const float4*)d;
@@ -41,6 +43,7 @@ __device__ __forceinline__ void vec_axpy_to(float* out, const float* x, double a
     }
 }
 __device__ __forceinline__ void vec_scale_copy(float* out, const float* a, double s, int n4) {
+    vec_prefetch(a, n4);
     const float fs = (float)s;
     const float4* a4 = (const float4*)a;
     float4* o4 = (float4*)out;
@@ -192,6 +195,7 @@ __device__ __forceinline__ void block_sum_multi(double (&v)[N], double* red) {
 __device__ inline bool lbfgs_direction_fused(SolveVecs& v, int hist, double* red, double& gg, double& dd0, double& dn) {
     const float4* g4 = (const float4*)v.g;
     float4* d4 = (float4*)v.d;
+    vec_prefetch(v.g, v.n4);
     if (hist == 0) {
         double acc[1] = {0.0};
         float s = 0.f;
@@ -207,6 +211,8 @@ __device__ inline bool lbfgs_direction_fused(SolveVecs& v, int hist, double* red
     }
     const float4* s4 = (const float4*)v.s[0];
     const float4* y4 = (const float4*)v.y[0];
+    vec_prefetch(v.s[0], v.n4);
+    vec_prefetch(v.y[0], v.n4);
     float sy = 0.f, yy = 0.f, sg = 0.f, yg = 0.f, g2 = 0.f;
     for (int i = threadIdx.x; i < v.n4; i += blockDim.x) {
         const float4 g = g4[i], s = s4[i], y = y4[i];
@@ -244,6 +250,7 @@ __device__ inline bool lbfgs_direction_fused(SolveVecs& v, int hist, double* red
 // s = xt - x and y = gt - g in one sweep (the new curvature pair)
 __device__ __forceinline__ void vec_pair_update(float* s, float* y, const float* xt, const float* x, const float* gt,
                                                 const float* g, int n4) {
+    vec_prefetch(xt, n4), vec_prefetch(x, n4), vec_prefetch(gt, n4), vec_prefetch(g, n4);
     for (int i = threadIdx.x; i < n4; i += blockDim.x) {
         const float4 a = ((const float4*)xt)[i], b = ((const float4*)x)[i];
         const float4 c = ((const float4*)gt)[i], e = ((const float4*)g)[i];

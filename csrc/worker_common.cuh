@@ -69,6 +69,7 @@ __device__ __forceinline__ void feature_inv_std(const __half* X, int start, int 
 
 // x = w0 * std  (std = 1/inv, 0 when inv == 0); intercept row copied
 __device__ __forceinline__ void to_scaled_space(float* x, const float* w0, const float* inv, int F) {
+    vec_prefetch(w0, (F + 1) * 2);
     for (int i = threadIdx.x; i < (F + 1) * 2; i += blockDim.x) {
         const int f = i >> 1;
         float4 v = ((const float4*)w0)[i];
@@ -81,6 +82,7 @@ __device__ __forceinline__ void to_scaled_space(float* x, const float* w0, const
 // delta = (x * inv, centred across the R class rows when asked) - w0
 __device__ __forceinline__ void finish_delta(float* delta, const float* x, const float* w0, const float* inv, int F,
                                              int R, int center) {
+    vec_prefetch(x, (F + 1) * 2), vec_prefetch(w0, (F + 1) * 2);
     for (int f = threadIdx.x; f <= F; f += blockDim.x) {
         const float sc = f < F ? inv[f] : 1.f;
         float v[8];
