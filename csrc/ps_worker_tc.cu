@@ -187,8 +187,9 @@ struct TcEval {
             if (++slot == kNS) slot = 0, ++use;
             return true;
         };
-        // (Prefetching slab q+1 into L2 with cp.async.bulk.prefetch while slab q streams was measured: 0.585 ->
-        //  0.796 ms per clock at 296 workers — the extra TMA traffic costs more than the latency it hides.)
+        // (L2 prefetch of the coming A chunks with cp.async.bulk.prefetch was measured twice: the whole next slab
+        //  issued from this thread, 0.585 -> 0.796 ms per clock at 296 workers; eight chunks ahead of the MMA warp
+        //  from an idle thread, 0.492 -> 0.492 — the A stream is not waiting on DRAM latency.)
         for (int q = 0; q < S; ++q) {
             const int b = active_slab(q);
             if (with_a)
