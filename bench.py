@@ -41,8 +41,9 @@ def parse():
     p.add_argument("--solver", default="lbfgs2", choices=["lbfgs2", "sgd"])
     p.add_argument("--consistency_model", type=int, default=0)
     p.add_argument("--ingest_rows", type=int, default=128, help="new rows per worker per step in the e2e run")
-    p.add_argument("--ingest_format", choices=["bitmap", "dense"], default="bitmap",
-                   help="e2e wire format of the fresh rows: presence bitmap + fp16 non-zeros (lossless) or dense fp16")
+    p.add_argument("--ingest_format", choices=["palette", "bitmap", "dense"], default="palette",
+                   help="e2e wire format of the fresh rows (all lossless w.r.t. the fp16 rings): presence bitmap + per-row "
+                        "palette and 4-bit codes, presence bitmap + fp16 non-zeros, or dense fp16")
     p.add_argument("--no_e2e", action="store_true")
     p.add_argument("--events_per_min", type=float, default=0.0,
                    help="e2e run: per-worker arrival rate used for the dynamic buffer size bc x events/min (0: unthrottled -> max)")
@@ -204,12 +205,15 @@ def main():
         n_new = W * a.ingest_rows
         g = torch.Generator().manual_seed(7 + rank)
         pool = 4                                              # rotating pinned batches of fresh rows
-        host_rows = [(torch.randn((n_new, F), generator=g) * (torch.rand((n_new, F), generator=g) < a.density))
-                     for _ in range(pool)]
+        # the same row model as the resident buffers (synth_buffers): signed hashed counts 1..3, L2-normalised
+        host_rows = [(torch.rand((n_new, F), generator=g) < a.density).float()
+                     * torch.randint(1, 4, (n_new, F), generator=g).float()
+                     * (torch.randint(0, 2, (n_new, F), generator=g).float() * 2 - 1) for _ in range(pool)]
         host_rows = [(r / r.norm(dim=1, keepdim=True).clamp_min(1e-6)).half().pin_memory() for r in host_rows]
         host_lab = [torch.randint(1, 6, (n_new,), generator=g, dtype=torch.int32).pin_memory() for _ in range(pool)]
-        if a.ingest_format == "bitmap":           # what the producer hands over: bitmap-packed rows in pinned memory
-            host_rows = [native.PackedRows(n_new, F).pack_dense(r, l) for r, l in zip(host_rows, host_lab)]
+        if a.ingest_format != "dense":            # what the producer hands over: packed rows in pinned memory
+            host_rows = [native.PackedRows(n_new, F, palette=a.ingest_format == "palette").pack_dense(r, l)
+                         for r, l in zip(host_rows, host_lab)]
         workers = np.repeat(np.arange(W, dtype=np.int32), a.ingest_rows)
         # arrival timestamps drive the dynamic buffer size: target = clamp(bc * events_per_minute, min, max)
         gap_ms = 60000.0 / a.events_per_min if a.events_per_min > 0 else 0.0

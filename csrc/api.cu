@@ -23,6 +23,8 @@ int psb_launch_ring_scatter(const uint32_t*, int, int, void*, int*, int, int, cu
 int psb_launch_ring_store_dense(const void*, int, const int*, const int*, int, void*, int*, int, int, cudaStream_t);
 int psb_launch_ring_store_bitmap(const uint32_t*, const int*, const void*, const int*, const int*, int, void*, int*, int, int,
                                  cudaStream_t);
+int psb_launch_ring_store_palette(const uint32_t*, const int*, const void*, const int*, const int*, int, void*, int*, int, int,
+                                  cudaStream_t);
 int psb_launch_apply_delta(float*, const float*, float, int, int, cudaStream_t);
 
 extern "C" {
@@ -160,6 +162,16 @@ int psb_ring_store_bitmap(const uint32_t* d_bitmap, const int* d_row_off, const 
     PSB_REQUIRE(num_features % 32 == 0, "psb_ring_store_bitmap: num_features must be a multiple of 32");
     return psb_launch_ring_store_bitmap(d_bitmap, d_row_off, d_values, d_labels_in, d_worker_slot, n, d_X, d_labels, cap,
                                         num_features, (cudaStream_t)stream);
+}
+
+int psb_ring_store_palette(const uint32_t* d_bitmap, const int* d_row_off, const void* d_payload, const int* d_labels_in,
+                           const int* d_worker_slot, int n, void* d_X, int* d_labels, int cap, int num_features,
+                           void* stream) {
+    PSB_REQUIRE(d_bitmap && d_row_off && d_payload && d_labels_in && d_worker_slot && d_X && d_labels,
+                "psb_ring_store_palette: null pointer");
+    PSB_REQUIRE(num_features % 32 == 0, "psb_ring_store_palette: num_features must be a multiple of 32");
+    return psb_launch_ring_store_palette(d_bitmap, d_row_off, d_payload, d_labels_in, d_worker_slot, n, d_X, d_labels,
+                                         cap, num_features, (cudaStream_t)stream);
 }
 
 // Random 32-byte row traffic (sharded sparse path): ask L2 to fetch 32-byte sectors instead of promoting every

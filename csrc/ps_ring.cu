@@ -101,6 +101,68 @@ __global__ void __launch_bounds__(256) psb_ring_store_bitmap_kernel(const uint32
     }
 }
 
+// Bitmap + per-row palette rows (psb_pack_palette_dense): one warp per row.  Lanes 0..15 hold the palette; lane l
+// expands presence word l of every 32-word group: the warp scan of the popcounts gives it its first code index,
+// every set bit fetches its nibble and the value comes from the palette lane by shuffle.  Raw rows (npal == 0)
+// read their fp16 values directly.
+__global__ void __launch_bounds__(256) psb_ring_store_palette_kernel(const uint32_t* __restrict__ bitmap,
+                                                                    const int* __restrict__ row_off,
+                                                                    const unsigned char* __restrict__ payload,
+                                                                    const int* __restrict__ labels_in,
+                                                                    const int* __restrict__ worker_slot, int n,
+                                                                    __half* __restrict__ X, int* __restrict__ labels,
+                                                                    int cap, int F) {
+    const int lane = threadIdx.x & 31, wpb = blockDim.x >> 5;
+    const int words = F >> 5;
+    for (int r = blockIdx.x * wpb + (threadIdx.x >> 5); r < n; r += gridDim.x * wpb) {
+        const int worker = worker_slot[2 * r], slot = worker_slot[2 * r + 1];
+        __half* dst = X + ((size_t)worker * cap + slot) * F;
+        const unsigned char* p = payload + row_off[r];
+        const int npal = *(const unsigned short*)p;
+        const unsigned short* vals = (const unsigned short*)(p + 2);           // palette, or the raw values
+        const unsigned char* codes = p + 2 + 2 * npal;
+        const unsigned int pal = lane < npal ? vals[lane] : 0u;
+        int base = 0;
+        for (int w0 = 0; w0 < words; w0 += 32) {
+            const int w = w0 + lane;
+            const uint32_t bits = w < words ? bitmap[(size_t)r * words + w] : 0u;
+            const int cnt = __popc(bits);
+            int incl = cnt;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const int t = __shfl_up_sync(0xffffffffu, incl, o);
+                if (lane >= o) incl += t;
+            }
+            int k = base + incl - cnt;
+            __align__(16) unsigned short out[32];
+            if (npal > 0) {                                                    // warp-uniform branch
+#pragma unroll
+                for (int b = 0; b < 32; ++b) {
+                    const bool on = (bits >> b) & 1u;
+                    const unsigned int code = on ? (codes[k >> 1] >> ((k & 1) * 4)) & 15u : 0u;
+                    const unsigned int v = __shfl_sync(0xffffffffu, pal, (int)code);
+                    out[b] = on ? (unsigned short)v : (unsigned short)0;
+                    k += on;
+                }
+            } else {
+#pragma unroll
+                for (int b = 0; b < 32; ++b) {
+                    const bool on = (bits >> b) & 1u;
+                    out[b] = on ? vals[k] : (unsigned short)0;
+                    k += on;
+                }
+            }
+            if (w < words) {
+                uint4* d16 = (uint4*)(dst + (size_t)w * 32);
+#pragma unroll
+                for (int q = 0; q < 4; ++q) d16[q] = ((const uint4*)out)[q];
+            }
+            base += __shfl_sync(0xffffffffu, incl, 31);
+        }
+        if (lane == 0) labels[(size_t)worker * cap + slot] = labels_in[r];
+    }
+}
+
 __global__ void psb_apply_delta_kernel(float* __restrict__ w, const float* __restrict__ delta, float lr, int n4,
                                        int skip_index) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -140,6 +202,16 @@ int psb_launch_ring_store_bitmap(const uint32_t* d_bitmap, const int* d_row_off,
     const int blocks = (n + 7) / 8;
     psb_ring_store_bitmap_kernel<<<blocks < 2368 ? blocks : 2368, 256, 0, stream>>>(
         d_bitmap, d_row_off, (const __half*)d_values, d_labels_in, d_ws, n, (__half*)d_X, d_labels, cap, F);
+    PSB_CHECK_CUDA(cudaGetLastError());
+    return 0;
+}
+int psb_launch_ring_store_palette(const uint32_t* d_bitmap, const int* d_row_off, const void* d_payload,
+                                  const int* d_labels_in, const int* d_ws, int n, void* d_X, int* d_labels, int cap, int F,
+                                  cudaStream_t stream) {
+    if (n <= 0) return 0;
+    const int blocks = (n + 7) / 8;
+    psb_ring_store_palette_kernel<<<blocks < 2368 ? blocks : 2368, 256, 0, stream>>>(
+        d_bitmap, d_row_off, (const unsigned char*)d_payload, d_labels_in, d_ws, n, (__half*)d_X, d_labels, cap, F);
     PSB_CHECK_CUDA(cudaGetLastError());
     return 0;
 }

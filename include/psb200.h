@@ -191,7 +191,18 @@ int psb_ring_store_bitmap(const uint32_t* d_bitmap, const int* d_row_off, const 
                           const int* d_labels_in, const int* d_worker_slot, int n, void* d_X, int* d_labels,
                           int cap, int num_features, void* stream);
 
+/* Bitmap + per-row palette rows -> ring slots (see psb_pack_palette_dense for the payload format):
+ * d_row_off [n] = byte offset of the row's payload in d_payload. */
+int psb_ring_store_palette(const uint32_t* d_bitmap, const int* d_row_off, const void* d_payload,
+                           const int* d_labels_in, const int* d_worker_slot, int n, void* d_X, int* d_labels,
+                           int cap, int num_features, void* stream);
+
 /* ---------------------------------------------------------------- host runtime (C++) */
+/* Dense fp16 rows -> presence bitmap + per-row palette (the <= 16 distinct fp16 values of the row) + one 4-bit
+ * code per non-zero; rows with more distinct values keep raw fp16 values.  Bit-exact.  out_row_off [n+1] are byte
+ * offsets into out_payload (capacity in bytes; n * (2 F + 2) always suffices).  Returns the payload bytes, -1 on error. */
+long long psb_pack_palette_dense(const uint16_t* rows, long long n_rows, int num_features, uint32_t* out_bitmap,
+                                 int* out_row_off, uint8_t* out_payload, long long payload_capacity);
 /* CSR (sorted or unsorted column indices, fp32 values) -> bitmap-packed rows with fp16 values (host side of
  * psb_ring_store_bitmap).  out_bitmap [n][F/32], out_row_off [n+1], out_values: uint16 fp16 bits, capacity
  * indptr[n].  Explicit zeros and out-of-range columns are dropped.  Returns the number of values written. */

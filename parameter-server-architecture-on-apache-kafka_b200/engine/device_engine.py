@@ -228,7 +228,12 @@ class DeviceEngine:
                                                          device=self.device) for _ in range(self.stage_sets)]
                     self.stage_off_dev = [torch.zeros(self.stage_rows + 1, dtype=torch.int32, device=self.device)
                                           for _ in range(self.stage_sets)]
-                self.stage_dev[j].view(-1)[:pk.nnz].copy_(pk.values[:pk.nnz], non_blocking=True)
+                if pk.palette:
+                    assert pk.payload_bytes <= self.stage_rows * self.F * 2, "palette payload larger than a staging set"
+                    self.stage_dev[j].view(torch.uint8).view(-1)[:pk.payload_bytes].copy_(
+                        pk.payload[:pk.payload_bytes], non_blocking=True)
+                else:
+                    self.stage_dev[j].view(-1)[:pk.nnz].copy_(pk.values[:pk.nnz], non_blocking=True)
                 self.stage_bitmap_dev[j][:n].copy_(pk.bitmap[:n], non_blocking=True)
                 self.stage_off_dev[j][:n + 1].copy_(pk.row_off[:n + 1], non_blocking=True)
                 self.stage_lab_dev[j][:n].copy_(pk.labels[:n], non_blocking=True)
@@ -240,7 +245,8 @@ class DeviceEngine:
             self.stage_ws_dev[j][:n].copy_(self.stage_ws_host[j][:n], non_blocking=True)
             self.stage_win_dev[j].copy_(self.stage_win_host[j], non_blocking=True)
             self.h2d_done[j].record(s)
-        self._end_set(j, n, "bitmap" if packed else "dense", nbytes + n * 8 + self.W * 8)
+        self._end_set(j, n, ("palette" if rows_f16.palette else "bitmap") if packed else "dense",
+                      nbytes + n * 8 + self.W * 8)
 
     def ingest_commit(self, wait: bool = True) -> None:
         """Second half: store the oldest begun batch into the rings (after the running step, before the next)."""
@@ -254,7 +260,11 @@ class DeviceEngine:
         s.wait_event(self.h2d_done[j])
         with torch.cuda.stream(s):
             self.win.copy_(self.stage_win_dev[j], non_blocking=True)
-            if self.stage_kind[j] == "bitmap":
+            if self.stage_kind[j] == "palette":
+                native.ring_store_palette(self.stage_bitmap_dev[j], self.stage_off_dev[j], self.stage_dev[j],
+                                          self.stage_lab_dev[j], self.stage_ws_dev[j], n, self.X, self.labels, self.cap,
+                                          self.F, stream=s)
+            elif self.stage_kind[j] == "bitmap":
                 native.ring_store_bitmap(self.stage_bitmap_dev[j], self.stage_off_dev[j], self.stage_dev[j],
                                          self.stage_lab_dev[j], self.stage_ws_dev[j], n, self.X, self.labels, self.cap,
                                          self.F, stream=s)

@@ -103,6 +103,9 @@ def lib() -> C.CDLL:
     L.psb_pack_bitmap_csr.argtypes = [vp, vp, vp, C.c_longlong, C.c_int, vp, vp, vp]
     L.psb_pack_bitmap_dense.restype = C.c_longlong
     L.psb_pack_bitmap_dense.argtypes = [vp, C.c_longlong, C.c_int, vp, vp, vp]
+    L.psb_pack_palette_dense.restype = C.c_longlong
+    L.psb_pack_palette_dense.argtypes = [vp, C.c_longlong, C.c_int, vp, vp, vp, C.c_longlong]
+    L.psb_ring_store_palette.argtypes = [vp, ip, vp, ip, ip, C.c_int, vp, ip, C.c_int, C.c_int, vp]
     L.psb_csv_parse.argtypes = [C.c_char_p, C.c_int, vp, vp, vp, vp, C.c_longlong, C.c_longlong]
     L.psb_tracker_create.restype = C.c_void_p
     L.psb_tracker_create.argtypes = [C.c_int, C.c_int]
@@ -171,25 +174,39 @@ def csv_to_csr(path: str, has_header: bool = True):
 
 
 class PackedRows:
-    """Bitmap-packed rows in pinned host memory: the sparse wire format of ingestion (presence bitmap +
-    fp16 values in feature order; LabeledData.java:14-28 without the keys).  Lossless w.r.t. the fp16 rings."""
+    """Packed rows in pinned host memory: the sparse wire format of ingestion (LabeledData.java:14-28 without the
+    keys).  Lossless w.r.t. the fp16 rings.  Two encodings of the non-zeros, both behind a presence bitmap:
+      * ``palette=False``: the fp16 values in feature order (128 B + 2 B per non-zero at F = 1024);
+      * ``palette=True`` : per row the <= 16 distinct fp16 values it uses + a 4-bit code per non-zero (hashed
+        bag-of-words rows hold a handful of distinct values: count / norm, signed); rows with more distinct
+        values fall back to raw fp16 values.  128 B + ~0.5 B per non-zero."""
 
-    def __init__(self, max_rows: int, num_features: int, pin: bool = True):
+    def __init__(self, max_rows: int, num_features: int, pin: bool = True, palette: bool = False):
         import torch
         assert num_features % 32 == 0, "bitmap packing needs num_features % 32 == 0"
-        self.max_rows, self.F, self.n, self.nnz = max_rows, num_features, 0, 0
+        self.max_rows, self.F, self.n, self.nnz, self.palette = max_rows, num_features, 0, 0, bool(palette)
         mk = (lambda *a, **k: torch.zeros(*a, **k).pin_memory()) if pin and torch.cuda.is_available() else torch.zeros
         self.bitmap = mk((max_rows, num_features // 32), dtype=torch.int32)
         self.row_off = mk(max_rows + 1, dtype=torch.int32)
-        self.values = mk(max_rows * num_features, dtype=torch.float16)
+        if self.palette:
+            self.payload = mk(max_rows * (2 * num_features + 2), dtype=torch.uint8)
+            self.payload_bytes = 0
+        else:
+            self.values = mk(max_rows * num_features, dtype=torch.float16)
         self.labels = mk(max_rows, dtype=torch.int32)
 
     def pack_dense(self, rows_f16, labels) -> "PackedRows":
         """rows_f16: torch/numpy fp16 [n, F] on the host."""
         n = int(rows_f16.shape[0])
         assert n <= self.max_rows and int(rows_f16.shape[1]) == self.F
-        self.nnz = int(check(lib().psb_pack_bitmap_dense(_ptr(rows_f16), n, self.F, _ptr(self.bitmap),
-                                                         _ptr(self.row_off), _ptr(self.values)), "pack_bitmap_dense"))
+        if self.palette:
+            self.payload_bytes = int(check(lib().psb_pack_palette_dense(
+                _ptr(rows_f16), n, self.F, _ptr(self.bitmap), _ptr(self.row_off), _ptr(self.payload),
+                self.payload.numel()), "pack_palette_dense"))
+            self.nnz = -1
+        else:
+            self.nnz = int(check(lib().psb_pack_bitmap_dense(_ptr(rows_f16), n, self.F, _ptr(self.bitmap),
+                                                             _ptr(self.row_off), _ptr(self.values)), "pack_bitmap_dense"))
         self.n = n
         self.labels[:n] = _as_int32_tensor(labels)[:n]
         return self
@@ -197,6 +214,10 @@ class PackedRows:
     def pack_csr(self, batch) -> "PackedRows":
         n = len(batch)
         assert n <= self.max_rows and batch.num_features <= self.F
+        if self.palette:
+            dense = np.zeros((n, self.F), dtype=np.float16)
+            dense[:, :batch.num_features] = batch.to_dense(np.float16)
+            return self.pack_dense(dense, batch.labels)
         indptr = np.ascontiguousarray(batch.indptr, dtype=np.int64)
         indices = np.ascontiguousarray(batch.indices, dtype=np.int32)
         values = np.ascontiguousarray(batch.values, dtype=np.float32)
@@ -209,14 +230,29 @@ class PackedRows:
 
     @property
     def nbytes(self) -> int:
-        """Bytes that cross PCIe for this batch (bitmap + offsets + values + labels)."""
-        return self.n * (self.F // 8) + (self.n + 1) * 4 + self.nnz * 2 + self.n * 4
+        """Bytes that cross PCIe for this batch (bitmap + offsets + values or payload + labels)."""
+        body = self.payload_bytes if self.palette else self.nnz * 2
+        return self.n * (self.F // 8) + (self.n + 1) * 4 + body + self.n * 4
 
     def to_dense(self) -> np.ndarray:
         """Reference expansion on the host (tests)."""
         out = np.zeros((self.n, self.F), dtype=np.float16)
         bits = np.unpackbits(self.bitmap[: self.n].numpy().view(np.uint8), axis=1, bitorder="little").astype(bool)
-        out[bits] = self.values[: self.nnz].numpy()
+        if not self.palette:
+            out[bits] = self.values[: self.nnz].numpy()
+            return out
+        pay, off = self.payload.numpy(), self.row_off.numpy()
+        for r in range(self.n):
+            p = pay[off[r]: off[r + 1]]
+            npal, nnz = int(p[:2].view(np.uint16)[0]), int(bits[r].sum())
+            if npal == 0:
+                vals = p[2: 2 + 2 * nnz].view(np.float16)
+            else:
+                pal = p[2: 2 + 2 * npal].view(np.float16)
+                c = p[2 + 2 * npal: 2 + 2 * npal + (nnz + 1) // 2]
+                codes = np.stack([c & 15, c >> 4], axis=1).reshape(-1)[:nnz]
+                vals = pal[codes]
+            out[r, bits[r]] = vals
         return out
 
 
@@ -232,6 +268,13 @@ def ring_store_bitmap(bitmap, row_off, values, labels_in, worker_slot, n: int, X
     check(lib().psb_ring_store_bitmap(_ptr(bitmap), _ptr(row_off), _ptr(values), _ptr(labels_in), _ptr(worker_slot), n,
                                       _ptr(X), _ptr(labels), cap, num_features, _stream(stream)),
           "psb_ring_store_bitmap")
+
+
+def ring_store_palette(bitmap, row_off, payload, labels_in, worker_slot, n: int, X, labels, cap: int,
+                       num_features: int, stream=None) -> None:
+    check(lib().psb_ring_store_palette(_ptr(bitmap), _ptr(row_off), _ptr(payload), _ptr(labels_in), _ptr(worker_slot), n,
+                                       _ptr(X), _ptr(labels), cap, num_features, _stream(stream)),
+          "psb_ring_store_palette")
 
 
 class NativeTracker:
@@ -336,7 +379,7 @@ class StreamProducer:
         """The bitmap-packed form of ready batch `batch` (views of the producer's pinned buffers, no copy)."""
         assert self.is_packed, "StreamProducer(packed=True) required"
         pk = PackedRows.__new__(PackedRows)
-        pk.max_rows, pk.F, pk.n = self.batch_rows, self.F, n
+        pk.max_rows, pk.F, pk.n, pk.palette = self.batch_rows, self.F, n, False
         pk.bitmap, pk.row_off, pk.values, pk.labels = (self.bitmap[batch], self.row_off[batch], self.values[batch],
                                                        self.labels[batch])
         pk.nnz = int(self.row_off[batch, n])

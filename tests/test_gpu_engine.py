@@ -134,7 +134,7 @@ def test_packed_ingest_equals_dense_ingest():
         lab = torch.from_numpy(rng.integers(1, 6, n).astype(np.int32)).pin_memory()
         workers = rng.integers(0, 3, n).astype(np.int32)
         engines[0].ingest(rows, lab, workers)
-        engines[1].ingest(native.PackedRows(96, 256).pack_dense(rows, lab), None, workers)
+        engines[1].ingest(native.PackedRows(96, 256, palette=bool(it & 1)).pack_dense(rows, lab), None, workers)
     torch.cuda.synchronize()
     a, b = engines
     assert torch.equal(a.X.view(torch.int16) * (a.X != 0), b.X.view(torch.int16) * (b.X != 0))

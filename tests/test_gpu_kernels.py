@@ -198,6 +198,35 @@ def test_ring_store_bitmap_matches_dense_store(F, density):
     assert torch.equal(lab, lab2)
 
 
+@pytest.mark.parametrize("F,density,raw_rows", [(1024, 0.45, 0), (1024, 0.05, 3), (256, 1.0, 1), (2048, 0.3, 2), (96, 0.5, 5)])
+def test_ring_store_palette_matches_dense_store(F, density, raw_rows):
+    """Palette-packed rows (palette and raw-fallback rows mixed) expand to exactly the dense store's ring contents."""
+    native = _native()
+    dev = torch.device("cuda")
+    cap, W, n = 64, 5, 150
+    rng = np.random.default_rng(F + raw_rows)
+    cnt = rng.integers(1, 6, (n, F)) * (rng.integers(0, 2, (n, F)) * 2 - 1) * (rng.random((n, F)) < density)
+    rows = (cnt / np.maximum(np.linalg.norm(cnt, axis=1, keepdims=True), 1e-6)).astype(np.float16)
+    rows[11] = 0
+    for r in range(raw_rows):
+        rows[20 + r] = (rng.standard_normal(F) * (rng.random(F) < max(density, 0.3))).astype(np.float16)
+    labels_in = rng.integers(1, 6, n).astype(np.int32)
+    slots = rng.permutation(W * cap)[:n]
+    ws = np.stack([slots // cap, slots % cap], axis=1).astype(np.int32)
+    pk = native.PackedRows(n + 3, F, palette=True).pack_dense(rows, labels_in)
+    X = torch.full((W, cap, F), 7.0, dtype=torch.float16, device=dev)
+    lab = torch.zeros((W, cap), dtype=torch.int32, device=dev)
+    native.ring_store_palette(pk.bitmap.to(dev), pk.row_off.to(dev), pk.payload[:pk.payload_bytes + 2].to(dev), pk.labels.to(dev),
+                              torch.from_numpy(ws).to(dev), n, X, lab, cap, F)
+    X2 = torch.full_like(X, 7.0)
+    lab2 = torch.zeros_like(lab)
+    native.ring_store_dense(torch.from_numpy(rows).to(dev), torch.from_numpy(labels_in).to(dev),
+                            torch.from_numpy(ws).to(dev), n, X2, lab2, cap, F)
+    torch.cuda.synchronize()
+    assert torch.equal(X.view(torch.int16), X2.view(torch.int16).where(X2 != 0, torch.zeros_like(X2).view(torch.int16)))
+    assert torch.equal(lab, lab2)
+
+
 def test_apply_delta_and_q1_compat():
     native = _native()
     dev = torch.device("cuda")

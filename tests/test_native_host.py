@@ -89,3 +89,26 @@ def test_bitmap_packers_roundtrip_dense_and_csr():
     b.indices[:] = perm
     pk2 = native.PackedRows(32, F, pin=False).pack_csr(b)
     assert np.array_equal(pk2.to_dense(), b.to_dense(np.float16))
+
+
+def test_palette_packer_roundtrip_with_raw_fallback():
+    """psb_pack_palette_dense: per-row palette + 4-bit codes reproduce hashed-count rows bit for bit; a row with
+    more than 16 distinct values, an empty row and an odd number of non-zeros take the fallback / padding paths."""
+    rng = np.random.default_rng(11)
+    F, n = 256, 45
+    cnt = rng.integers(1, 4, (n, F)) * (rng.integers(0, 2, (n, F)) * 2 - 1) * (rng.random((n, F)) < 0.4)
+    rows = (cnt / np.maximum(np.linalg.norm(cnt, axis=1, keepdims=True), 1e-6)).astype(np.float16)
+    rows[5] = 0
+    rows[7] = (rng.standard_normal(F) * (rng.random(F) < 0.5)).astype(np.float16)        # > 16 distinct values: raw
+    rows[9] = 0
+    rows[9, [3, 77, 200]] = np.float16(0.5)                                               # 3 non-zeros, 1 palette entry
+    labels = rng.integers(1, 6, n).astype(np.int32)
+    pk = native.PackedRows(64, F, pin=False, palette=True).pack_dense(rows, labels)
+    ref = np.where(rows == 0, np.float16(0), rows)
+    assert np.array_equal(pk.to_dense().view(np.uint16), ref.view(np.uint16))
+    off = pk.row_off[:n + 1].numpy()
+    assert (off % 2 == 0).all() and off[n] == pk.payload_bytes
+    assert int(pk.payload[off[7]:off[7] + 2].numpy().view(np.uint16)[0]) == 0            # raw row
+    assert int(pk.payload[off[9]:off[9] + 2].numpy().view(np.uint16)[0]) == 1
+    plain = native.PackedRows(64, F, pin=False).pack_dense(rows, labels)
+    assert pk.nbytes < 0.6 * plain.nbytes
