@@ -228,16 +228,30 @@ def main():
         # (ingest_begin, copy stream, three staging sets) are in flight while step i trains; ingest_commit stores
         # batch i into the rings between two steps.  Every step still pays its own H2D (pinned host -> device)
         # and its own D2H read of the losses.
+        # The result read is pipelined the same way: step i's losses are copied device -> host behind step i and
+        # consumed on the host after step i+1 has been queued (read_loss_begin / read_loss_end).
+        pending = [None]
+        seen = [0.0]
+
         def one(i):
             eng.ingest_commit()                                                            # batch i -> rings
             eng.step()                                                                     # enqueue clock i
+            ticket = eng.read_loss_begin()                                                 # D2H of clock i's result
             eng.ingest_begin(host_rows[(i + 2) % pool], host_lab[(i + 2) % pool], workers, stamps())   # H2D of i+2
-            return eng.read_loss()                                                        # D2H of the result
+            if pending[0] is not None:
+                seen[0] = float(eng.read_loss_end(pending[0])[0])                          # clock i-1's result, on the host
+            pending[0] = ticket
+
+        def drain():
+            if pending[0] is not None:
+                seen[0] = float(eng.read_loss_end(pending[0])[0])
+                pending[0] = None
 
         eng.ingest_begin(host_rows[0], host_lab[0], workers, stamps())
         eng.ingest_begin(host_rows[1], host_lab[1], workers, stamps())
         for i in range(a.warmup):
             one(i)
+        drain()
         barrier()
         h0 = eng.h2d_bytes
         t0 = torch.cuda.Event(enable_timing=True)
@@ -246,11 +260,13 @@ def main():
         wall0 = time.perf_counter()
         for i in range(a.steps):
             one(i)
+        drain()                                                          # the last clock's result is read inside the timed region
         t1.record()
         torch.cuda.synchronize()
         wall = (time.perf_counter() - wall0) * 1000.0
         barrier()
         ems = max_over_ranks(max(t0.elapsed_time(t1), wall))
+        eng.ingest_commit(), eng.ingest_commit()                       # drain the two batches still in the pipeline
         rows_eff = float(eng.win_host[:, 1].float().mean())            # dynamic buffer size actually trained on
         e2e = {"value": W * world * rows_eff * a.steps / (ems / 1000.0), "unit": "samples/sec",
                "buffer_rows_effective": rows_eff, "events_per_min_per_worker": a.events_per_min,

@@ -84,9 +84,10 @@ class DeviceEngine:
         self.stage_dev = [torch.zeros((self.stage_rows, F), dtype=torch.float16, device=dev) for _ in range(S)]
         self.stage_lab_dev = [torch.zeros(self.stage_rows, dtype=torch.int32, device=dev) for _ in range(S)]
         self.stage_ws_dev = [torch.zeros((self.stage_rows, 2), dtype=torch.int32, device=dev) for _ in range(S)]
-        self.stage_win_dev = [torch.zeros((self.W, 2), dtype=torch.int32, device=dev) for _ in range(S)]
         self.stage_bitmap_dev = self.stage_off_dev = None            # allocated on the first packed batch
         self.stage_csr_dev = [None] * S                              # (device rows, stride) of an ingest_sparse batch
+        self.stage_future = [None] * S                               # slot assignment of the set (helper thread)
+        self._slot_thread = None
         self.stage_kind = ["dense"] * S
         self.stage_n = [0] * S
         self.stage_head = self.stage_tail = self.stage_pending = 0
@@ -144,6 +145,7 @@ class DeviceEngine:
     def fill(self, rows: torch.Tensor, labels: torch.Tensor) -> None:
         """Bulk-load every ring: rows fp16 [W, n, F] (device or host), labels int32 [W, n]; n <= cap."""
         n = rows.shape[1]
+        self._wait_slot_thread()
         self.X[:, :n].copy_(rows)
         self.labels[:, :n].copy_(labels)
         self.buffers = [native.NativeBuffer(self.cfg.min_buffer_size, self.cap, self.cfg.buffer_size_coefficient)
@@ -171,34 +173,50 @@ class DeviceEngine:
         device (fewer PCIe bytes than dense fp16 below ~25 % density; see PackedRows for the denser case)."""
         from ..data.csr import pack_stage_rows
         n = len(batch)
-        j = self._begin_set(n, workers, now_ms)
+        j = self._begin_set(n, workers, now_ms, sync=True)
         stage = torch.from_numpy(pack_stage_rows(batch, self.stage_ws_host[j].numpy()[:n]).view(np.int32)).pin_memory()
         with torch.cuda.stream(self.copy_stream):
             stage_dev = stage.to(self.device, non_blocking=True)
-            self.stage_win_dev[j].copy_(self.stage_win_host[j], non_blocking=True)
             self.h2d_done[j].record(self.copy_stream)
         stage_dev.record_stream(self.ingest_stream)
         self.stage_csr_dev[j] = (stage_dev, stage.shape[1], stage)     # pinned source must outlive the async copy
         self._end_set(j, n, "csr", stage.numel() * 4 + self.W * 8)
         self.ingest_commit()
 
-    def _begin_set(self, n: int, workers: np.ndarray, now_ms: Optional[np.ndarray]) -> int:
-        """Claim staging set `head`: assign ring slots to the n rows (dynamic-buffer policy) and snapshot the
-        windows they produce into the set's pinned tables."""
+    def _begin_set(self, n: int, workers: np.ndarray, now_ms: Optional[np.ndarray], sync: bool = False) -> int:
+        """Claim staging set `head` and hand its slot assignment (dynamic-buffer policy: ring slot per row, the
+        windows they produce) to the engine's helper thread, which fills the set's pinned tables.  The tables are
+        needed only at commit time, so the ~0.4 ms of host work per 38k rows overlaps the caller's enqueueing and
+        the running step; batches are assigned strictly in begin order (one helper thread)."""
         assert n <= self.stage_rows, "ingest batch larger than a staging set"
         if self.stage_pending == self.stage_sets:
             raise native.NativeError("ingest_begin: every staging set holds an uncommitted batch; call ingest_commit")
         j = self.stage_head
-        self.h2d_done[j].synchronize()                      # the set's pinned tables are free again
-        if now_ms is None:
-            now_ms = np.zeros(n, dtype=np.float64)
+        self.store_done[j].synchronize()                    # the set's pinned tables and device buffers are free again
         if self._buf_handles is None:
             self._buf_handles = native.buffer_handles(self.buffers)
-        native.buffers_on_batch(self.buffers, workers[:n], now_ms[:n], self.stage_ws_host[j].numpy(),
-                                self.win_host.numpy(), handles=self._buf_handles)
-        self.stage_win_host[j].copy_(self.win_host)
-        self.copy_stream.wait_event(self.store_done[j])     # the set's device buffers have been drained
+        workers = np.ascontiguousarray(workers[:n], dtype=np.int32)
+        now_ms = np.zeros(n, dtype=np.float64) if now_ms is None else np.ascontiguousarray(now_ms[:n], dtype=np.float64)
+        handles, buffers = self._buf_handles, self.buffers
+
+        def assign():
+            native.buffers_on_batch(buffers, workers, now_ms, self.stage_ws_host[j].numpy(), self.win_host.numpy(),
+                                    handles=handles)
+            self.stage_win_host[j].copy_(self.win_host)
+
+        if self._slot_thread is None:
+            from concurrent.futures import ThreadPoolExecutor
+            self._slot_thread = ThreadPoolExecutor(max_workers=1, thread_name_prefix="psb-slots")
+        self.stage_future[j] = self._slot_thread.submit(assign)
+        if sync:
+            self.stage_future[j].result()
         return j
+
+    def _wait_slot_thread(self) -> None:
+        """Block until the helper thread has finished every slot assignment handed to it."""
+        for f in self.stage_future:
+            if f is not None:
+                f.result()
 
     def _end_set(self, j: int, n: int, kind: str, nbytes: int) -> None:
         self.stage_n[j], self.stage_kind[j] = n, kind
@@ -242,8 +260,6 @@ class DeviceEngine:
                 self.stage_dev[j][:n].copy_(rows_f16[:n], non_blocking=True)
                 self.stage_lab_dev[j][:n].copy_(labels[:n], non_blocking=True)
                 nbytes = n * self.F * 2 + n * 4
-            self.stage_ws_dev[j][:n].copy_(self.stage_ws_host[j][:n], non_blocking=True)
-            self.stage_win_dev[j].copy_(self.stage_win_host[j], non_blocking=True)
             self.h2d_done[j].record(s)
         self._end_set(j, n, ("palette" if rows_f16.palette else "bitmap") if packed else "dense",
                       nbytes + n * 8 + self.W * 8)
@@ -256,10 +272,13 @@ class DeviceEngine:
         n = self.stage_n[j]
         s = self.ingest_stream
         torch.cuda.nvtx.range_push("psb.ingest_commit")
+        self.stage_future[j].result()                       # slot tables of this batch are written (helper thread)
         s.wait_stream(torch.cuda.current_stream())          # the previous step must be done with the rings
         s.wait_event(self.h2d_done[j])
         with torch.cuda.stream(s):
-            self.win.copy_(self.stage_win_dev[j], non_blocking=True)
+            if self.stage_kind[j] != "csr":
+                self.stage_ws_dev[j][:n].copy_(self.stage_ws_host[j][:n], non_blocking=True)
+            self.win.copy_(self.stage_win_host[j], non_blocking=True)
             if self.stage_kind[j] == "palette":
                 native.ring_store_palette(self.stage_bitmap_dev[j], self.stage_off_dev[j], self.stage_dev[j],
                                           self.stage_lab_dev[j], self.stage_ws_dev[j], n, self.X, self.labels, self.cap,
@@ -307,6 +326,23 @@ class DeviceEngine:
         self.loss_host.copy_(self.loss, non_blocking=True)
         torch.cuda.current_stream().synchronize()
         return self.loss_host
+
+    def read_loss_begin(self) -> int:
+        """Enqueue the device -> pinned host copy of the losses of the step just enqueued; returns a ticket for
+        ``read_loss_end``.  Lets the host read step k's result while step k+1 is already queued (two tickets may be
+        outstanding)."""
+        k = self._loss_ticket = (getattr(self, "_loss_ticket", -1) + 1) % 2
+        if not hasattr(self, "_loss_ring"):
+            self._loss_ring = [torch.zeros(self.W, dtype=torch.float32).pin_memory() for _ in range(2)]
+            self._loss_ev = [torch.cuda.Event() for _ in range(2)]
+        self._loss_ring[k].copy_(self.loss, non_blocking=True)
+        self._loss_ev[k].record()
+        return k
+
+    def read_loss_end(self, ticket: int) -> torch.Tensor:
+        """Wait for the copy behind ``ticket`` and return the pinned per-worker losses."""
+        self._loss_ev[ticket].synchronize()
+        return self._loss_ring[ticket]
 
     def weights(self) -> torch.Tensor:
         """Current global weights as seen by this rank ([(F+1), 8] view of device memory)."""
@@ -357,6 +393,10 @@ class DeviceEngine:
         return float(self.metrics_host[0]), float(self.metrics_host[1])
 
     def close(self) -> None:
+        if self._slot_thread is not None:
+            self._wait_slot_thread()
+            self._slot_thread.shutdown(wait=True)
+            self._slot_thread = None
         if self.block:
             torch.cuda.synchronize(self.device)
             for q, p in enumerate(self.peers):
