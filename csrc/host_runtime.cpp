@@ -298,6 +298,10 @@ extern "C" int psb_buffers_on_batch(void** buffers, int num_buffers, const int* 
 
 #include <cuda_fp16.h>
 
+extern "C" long long psb_pack_palette_dense(const uint16_t* rows, long long n_rows, int F, uint32_t* out_bitmap,
+                                            int* out_row_off, uint8_t* out_payload, long long payload_capacity);
+extern "C" long long psb_pack_bitmap_dense(const uint16_t* rows, long long n_rows, int F, uint32_t* out_bitmap,
+                                           int* out_row_off, uint16_t* out_values);
 namespace {
 struct Producer {
     std::string path;
@@ -309,6 +313,8 @@ struct Producer {
     uint32_t* pk_bitmap = nullptr;            // optional: every published batch is also bitmap-packed
     int* pk_row_off = nullptr;                //   [num_batches][batch_rows + 1]
     uint16_t* pk_values = nullptr;            //   [num_batches][batch_rows * F]
+    uint8_t* pk_payload = nullptr;            // palette mode instead of pk_values: [num_batches][pk_stride] bytes
+    long long pk_stride = 0;
     std::vector<std::atomic<int>> ready;      // -1 free, >=0 rows published
     std::atomic<long long> rows_sent{0};      // global rows "sent" (all partitions)
     std::atomic<int> eof{0}, stop{0};
@@ -335,7 +341,12 @@ void producer_main(Producer* P) {
     double batch_t0 = 0.0;
     auto publish = [&] {
         if (fill == 0) return;
-        if (P->pk_bitmap)
+        if (P->pk_bitmap && P->pk_payload)
+            psb_pack_palette_dense(P->rows + (size_t)batch * P->batch_rows * P->F, fill, P->F,
+                                   P->pk_bitmap + (size_t)batch * P->batch_rows * (P->F / 32),
+                                   P->pk_row_off + (size_t)batch * (P->batch_rows + 1),
+                                   P->pk_payload + (size_t)batch * P->pk_stride, P->pk_stride);
+        else if (P->pk_bitmap)
             psb_pack_bitmap_dense(P->rows + (size_t)batch * P->batch_rows * P->F, fill, P->F,
                                   P->pk_bitmap + (size_t)batch * P->batch_rows * (P->F / 32),
                                   P->pk_row_off + (size_t)batch * (P->batch_rows + 1),
@@ -411,11 +422,38 @@ extern "C" void* psb_producer_start(const char* path, int has_header, int num_wo
                                      batch_rows, num_batches, h_rows_f16, h_labels, h_workers, h_times, flush_ms, nullptr,
                                      nullptr, nullptr);
 }
+static void* producer_start_impl(const char* path, int has_header, int num_workers_total, int worker_begin,
+                                 int worker_count, int num_features, int p_ms, int batch_rows, int num_batches,
+                                 void* h_rows_f16, int* h_labels, int* h_workers, double* h_times, int flush_ms,
+                                 uint32_t* h_bitmap, int* h_row_off, void* h_values_f16, uint8_t* h_payload,
+                                 long long payload_stride);
 extern "C" void* psb_producer_start_packed(const char* path, int has_header, int num_workers_total, int worker_begin,
                                            int worker_count, int num_features, int p_ms, int batch_rows,
                                            int num_batches, void* h_rows_f16, int* h_labels, int* h_workers,
                                            double* h_times, int flush_ms, uint32_t* h_bitmap, int* h_row_off,
                                            void* h_values_f16) {
+    return producer_start_impl(path, has_header, num_workers_total, worker_begin, worker_count, num_features, p_ms,
+                               batch_rows, num_batches, h_rows_f16, h_labels, h_workers, h_times, flush_ms, h_bitmap,
+                               h_row_off, h_values_f16, nullptr, 0);
+}
+extern "C" void* psb_producer_start_palette(const char* path, int has_header, int num_workers_total, int worker_begin,
+                                            int worker_count, int num_features, int p_ms, int batch_rows,
+                                            int num_batches, void* h_rows_f16, int* h_labels, int* h_workers,
+                                            double* h_times, int flush_ms, uint32_t* h_bitmap, int* h_row_off,
+                                            uint8_t* h_payload, long long payload_stride) {
+    if (!h_bitmap || !h_row_off || !h_payload || payload_stride < (long long)batch_rows * (2 * num_features + 2)) {
+        psb_set_error("psb_producer_start_palette: needs bitmap, offsets and a payload of >= batch_rows * (2 F + 2) bytes per batch");
+        return nullptr;
+    }
+    return producer_start_impl(path, has_header, num_workers_total, worker_begin, worker_count, num_features, p_ms,
+                               batch_rows, num_batches, h_rows_f16, h_labels, h_workers, h_times, flush_ms, h_bitmap,
+                               h_row_off, h_payload, h_payload, payload_stride);
+}
+static void* producer_start_impl(const char* path, int has_header, int num_workers_total, int worker_begin,
+                                 int worker_count, int num_features, int p_ms, int batch_rows, int num_batches,
+                                 void* h_rows_f16, int* h_labels, int* h_workers, double* h_times, int flush_ms,
+                                 uint32_t* h_bitmap, int* h_row_off, void* h_values_f16, uint8_t* h_payload,
+                                 long long payload_stride) {
     if ((h_bitmap || h_row_off || h_values_f16) && !(h_bitmap && h_row_off && h_values_f16 && num_features % 32 == 0)) {
         psb_set_error("psb_producer_start_packed: packing needs all three buffers and num_features %% 32 == 0");
         return nullptr;
@@ -430,6 +468,7 @@ extern "C" void* psb_producer_start_packed(const char* path, int has_header, int
     P->num_batches = num_batches, P->flush_ms = flush_ms > 0 ? flush_ms : 50;
     P->rows = (uint16_t*)h_rows_f16, P->labels = h_labels, P->workers = h_workers, P->times = h_times;
     P->pk_bitmap = h_bitmap, P->pk_row_off = h_row_off, P->pk_values = (uint16_t*)h_values_f16;
+    P->pk_payload = h_payload, P->pk_stride = payload_stride;
     P->th = std::thread(producer_main, P);
     return P;
 }

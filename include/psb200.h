@@ -247,6 +247,12 @@ void* psb_producer_start_packed(const char* path, int has_header, int num_worker
                                 int worker_count, int num_features, int p_ms, int batch_rows, int num_batches,
                                 void* h_rows_f16, int* h_labels, int* h_workers, double* h_times, int flush_ms,
                                 uint32_t* h_bitmap, int* h_row_off, void* h_values_f16);
+/* the same with palette packing (psb_pack_palette_dense): h_payload [num_batches][payload_stride] bytes,
+ * payload_stride >= batch_rows * (2 F + 2); h_row_off [num_batches][batch_rows + 1] are byte offsets. */
+void* psb_producer_start_palette(const char* path, int has_header, int num_workers_total, int worker_begin,
+                                 int worker_count, int num_features, int p_ms, int batch_rows, int num_batches,
+                                 void* h_rows_f16, int* h_labels, int* h_workers, double* h_times, int flush_ms,
+                                 uint32_t* h_bitmap, int* h_row_off, uint8_t* h_payload, long long payload_stride);
 int psb_producer_poll(void* h, int* batch, int* n, int* eof);
 void psb_producer_release(void* h, int batch);
 long long psb_producer_rows_sent(void* h);

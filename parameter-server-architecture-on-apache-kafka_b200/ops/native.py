@@ -124,6 +124,8 @@ def lib() -> C.CDLL:
                                      vp, vp, vp, vp, C.c_int]
     L.psb_producer_start_packed.restype = C.c_void_p
     L.psb_producer_start_packed.argtypes = L.psb_producer_start.argtypes + [vp, vp, vp]
+    L.psb_producer_start_palette.restype = C.c_void_p
+    L.psb_producer_start_palette.argtypes = L.psb_producer_start.argtypes + [vp, vp, vp, C.c_longlong]
     L.psb_producer_poll.argtypes = [vp, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int)]
     L.psb_producer_release.argtypes = [vp, C.c_int]
     L.psb_producer_rows_sent.restype = C.c_longlong
@@ -344,7 +346,9 @@ class StreamProducer:
 
     def __init__(self, path: str, num_workers_total: int, worker_begin: int, worker_count: int, num_features: int,
                  p_ms: int, batch_rows: int = 1024, num_batches: int = 4, has_header: bool = True, flush_ms: int = 50,
-                 packed: bool = False):
+                 packed=False):
+        """packed: False (dense fp16 batches only), True (also bitmap + fp16 values) or "palette" (also bitmap +
+        per-row palette + 4-bit codes)."""
         import torch
         pin = torch.cuda.is_available()
         mk = (lambda *s, dtype: torch.zeros(*s, dtype=dtype).pin_memory()) if pin else \
@@ -354,17 +358,25 @@ class StreamProducer:
         self.workers = mk(num_batches, batch_rows, dtype=torch.int32)
         self.times = mk(num_batches, batch_rows, dtype=torch.float64)
         self.is_packed = bool(packed) and num_features % 32 == 0
+        self.is_palette = self.is_packed and packed == "palette"
         self.F, self.batch_rows = num_features, batch_rows
+        common = (path.encode(), int(has_header), num_workers_total, worker_begin, worker_count, num_features, int(p_ms),
+                  batch_rows, num_batches, self.rows.data_ptr(), self.labels.data_ptr(), self.workers.data_ptr(),
+                  self.times.data_ptr(), flush_ms)
         if self.is_packed:
             self.bitmap = mk(num_batches, batch_rows, num_features // 32, dtype=torch.int32)
             self.row_off = mk(num_batches, batch_rows + 1, dtype=torch.int32)
+        if self.is_palette:
+            stride = batch_rows * (2 * num_features + 2)
+            self.payload = mk(num_batches, stride, dtype=torch.uint8)
+            self.h = lib().psb_producer_start_palette(*common, self.bitmap.data_ptr(), self.row_off.data_ptr(),
+                                                      self.payload.data_ptr(), stride)
+        elif self.is_packed:
             self.values = mk(num_batches, batch_rows * num_features, dtype=torch.float16)
-        pk = (self.bitmap.data_ptr(), self.row_off.data_ptr(), self.values.data_ptr()) if self.is_packed \
-            else (None, None, None)
-        self.h = lib().psb_producer_start_packed(
-            path.encode(), int(has_header), num_workers_total, worker_begin, worker_count, num_features, int(p_ms),
-            batch_rows, num_batches, self.rows.data_ptr(), self.labels.data_ptr(), self.workers.data_ptr(),
-            self.times.data_ptr(), flush_ms, *pk)
+            self.h = lib().psb_producer_start_packed(*common, self.bitmap.data_ptr(), self.row_off.data_ptr(),
+                                                     self.values.data_ptr())
+        else:
+            self.h = lib().psb_producer_start_packed(*common, None, None, None)
         if not self.h:
             raise NativeError("psb_producer_start: " + lib().psb_last_error().decode())
 
@@ -379,10 +391,12 @@ class StreamProducer:
         """The bitmap-packed form of ready batch `batch` (views of the producer's pinned buffers, no copy)."""
         assert self.is_packed, "StreamProducer(packed=True) required"
         pk = PackedRows.__new__(PackedRows)
-        pk.max_rows, pk.F, pk.n, pk.palette = self.batch_rows, self.F, n, False
-        pk.bitmap, pk.row_off, pk.values, pk.labels = (self.bitmap[batch], self.row_off[batch], self.values[batch],
-                                                       self.labels[batch])
-        pk.nnz = int(self.row_off[batch, n])
+        pk.max_rows, pk.F, pk.n, pk.palette = self.batch_rows, self.F, n, self.is_palette
+        pk.bitmap, pk.row_off, pk.labels = self.bitmap[batch], self.row_off[batch], self.labels[batch]
+        if self.is_palette:
+            pk.payload, pk.payload_bytes, pk.nnz = self.payload[batch], int(self.row_off[batch, n]), -1
+        else:
+            pk.values, pk.nnz = self.values[batch], int(self.row_off[batch, n])
         return pk
 
     def release(self, batch: int) -> None:

@@ -61,14 +61,18 @@ def test_missing_file_reports_error(tmp_path):
     assert eof == 2
 
 
-def test_packed_batches_expand_to_the_dense_rows(tmp_path):
-    """StreamProducer(packed=True): every published batch also carries its bitmap-packed form, bit-identical
+import pytest
+
+
+@pytest.mark.parametrize("mode", [True, "palette"])
+def test_packed_batches_expand_to_the_dense_rows(tmp_path, mode):
+    """StreamProducer(packed=True | "palette"): every published batch also carries its packed form, bit-identical
     to the dense fp16 rows of the same batch."""
     b = ReviewGenerator(num_features=64, vocab=500, mean_len=12).train_split(300)
     path = os.path.join(tmp_path, "t.csv")
     write_csv(path, b)
-    prod = native.StreamProducer(path, 2, 0, 2, 64, 0, batch_rows=50, num_batches=3, packed=True)
-    assert prod.is_packed
+    prod = native.StreamProducer(path, 2, 0, 2, 64, 0, batch_rows=50, num_batches=3, packed=mode)
+    assert prod.is_packed and prod.is_palette == (mode == "palette")
     seen, t0 = 0, time.time()
     while time.time() - t0 < 20:
         bi, n, eof = prod.poll()
@@ -79,7 +83,7 @@ def test_packed_batches_expand_to_the_dense_rows(tmp_path):
             continue
         pk = prod.packed(bi, n)
         dense = prod.rows[bi, :n].numpy()
-        assert pk.n == n and pk.nnz == int((dense != 0).sum())
+        assert pk.n == n and (pk.palette or pk.nnz == int((dense != 0).sum()))
         assert np.array_equal(pk.to_dense().view(np.uint16), dense.view(np.uint16))
         assert pk.labels[:n].tolist() == prod.labels[bi, :n].tolist()
         seen += n
