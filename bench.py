@@ -10,6 +10,13 @@ deltas are reduced and applied (w += delta/numWorkers, ServerProcessor.java:148-
 new weights are published.  samples/sec = numWorkers x buffer rows x clocks / second — the same
 accounting BASELINE.md uses for the reference (worker iterations/s x buffer size = ~130).
 
+Two timed regions.  `value`: K clocks on resident buffers, CUDA events around the launches (device time).
+`e2e`: the same K clocks through the public engine API with, every clock, 128 fresh rows per worker copied from
+pinned host memory (packed: presence bitmap + per-row palette, bit-exact) and stored into the rings, and the
+clock's per-worker losses copied back and read on the host.  The e2e loop is software-pipelined (copies of
+batches i+1 and i+2 and the read of clock i-1's result overlap clock i) but nothing is skipped: bytes are
+counted from the tensors copied, and its time is max(CUDA events, host wall clock).
+
 Prints ONE JSON line on rank 0.  `--impl reference` reports that the Java/Kafka/Spark reference
 cannot be installed here.
 """

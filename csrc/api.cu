@@ -174,6 +174,18 @@ int psb_ring_store_palette(const uint32_t* d_bitmap, const int* d_row_off, const
                                          cap, num_features, (cudaStream_t)stream);
 }
 
+// Several host -> device copies with one call (the ingestion path issues 2-4 small copies per batch; from Python
+// each costs more in interpreter time than on the wire).  Sources should be pinned for the copies to be asynchronous.
+int psb_h2d_copies(int n, void* const* d_dst, const void* const* h_src, const size_t* bytes, void* stream) {
+    PSB_REQUIRE(n >= 0 && (n == 0 || (d_dst && h_src && bytes)), "psb_h2d_copies: null table");
+    for (int i = 0; i < n; ++i) {
+        if (bytes[i] == 0) continue;
+        PSB_REQUIRE(d_dst[i] && h_src[i], "psb_h2d_copies: null pointer in entry %d", i);
+        PSB_CHECK_CUDA(cudaMemcpyAsync(d_dst[i], h_src[i], bytes[i], cudaMemcpyHostToDevice, (cudaStream_t)stream));
+    }
+    return 0;
+}
+
 // Random 32-byte row traffic (sharded sparse path): ask L2 to fetch 32-byte sectors instead of promoting every
 // miss to 64/128 bytes.  A hint; returns the granularity the device reports afterwards.
 int psb_set_l2_fetch_granularity(int bytes) {

@@ -197,6 +197,9 @@ int psb_ring_store_palette(const uint32_t* d_bitmap, const int* d_row_off, const
                            const int* d_labels_in, const int* d_worker_slot, int n, void* d_X, int* d_labels,
                            int cap, int num_features, void* stream);
 
+/* n host -> device copies on `stream` with one call (pinned sources for asynchronous copies) */
+int psb_h2d_copies(int n, void* const* d_dst, const void* const* h_src, const size_t* bytes, void* stream);
+
 /* ---------------------------------------------------------------- host runtime (C++) */
 /* Dense fp16 rows -> presence bitmap + per-row palette (the <= 16 distinct fp16 values of the row) + one 4-bit
  * code per non-zero; rows with more distinct values keep raw fp16 values.  Bit-exact.  out_row_off [n+1] are byte

@@ -237,30 +237,27 @@ class DeviceEngine:
         n = rows_f16.n if packed else rows_f16.shape[0]
         j = self._begin_set(n, workers, now_ms)
         s = self.copy_stream
-        with torch.cuda.stream(s):
-            if packed:
-                pk = rows_f16
-                assert pk.F == self.F
-                if self.stage_bitmap_dev is None:
-                    self.stage_bitmap_dev = [torch.zeros((self.stage_rows, self.F // 32), dtype=torch.int32,
-                                                         device=self.device) for _ in range(self.stage_sets)]
-                    self.stage_off_dev = [torch.zeros(self.stage_rows + 1, dtype=torch.int32, device=self.device)
-                                          for _ in range(self.stage_sets)]
-                if pk.palette:
-                    assert pk.payload_bytes <= self.stage_rows * self.F * 2, "palette payload larger than a staging set"
-                    self.stage_dev[j].view(torch.uint8).view(-1)[:pk.payload_bytes].copy_(
-                        pk.payload[:pk.payload_bytes], non_blocking=True)
-                else:
-                    self.stage_dev[j].view(-1)[:pk.nnz].copy_(pk.values[:pk.nnz], non_blocking=True)
-                self.stage_bitmap_dev[j][:n].copy_(pk.bitmap[:n], non_blocking=True)
-                self.stage_off_dev[j][:n + 1].copy_(pk.row_off[:n + 1], non_blocking=True)
-                self.stage_lab_dev[j][:n].copy_(pk.labels[:n], non_blocking=True)
-                nbytes = pk.nbytes
+        if packed:
+            pk = rows_f16
+            assert pk.F == self.F
+            if self.stage_bitmap_dev is None:
+                self.stage_bitmap_dev = [torch.zeros((self.stage_rows, self.F // 32), dtype=torch.int32,
+                                                     device=self.device) for _ in range(self.stage_sets)]
+                self.stage_off_dev = [torch.zeros(self.stage_rows + 1, dtype=torch.int32, device=self.device)
+                                      for _ in range(self.stage_sets)]
+            if pk.palette:
+                assert pk.payload_bytes <= self.stage_rows * self.F * 2, "palette payload larger than a staging set"
+                body = (self.stage_dev[j], pk.payload, pk.payload_bytes)
             else:
-                self.stage_dev[j][:n].copy_(rows_f16[:n], non_blocking=True)
-                self.stage_lab_dev[j][:n].copy_(labels[:n], non_blocking=True)
-                nbytes = n * self.F * 2 + n * 4
-            self.h2d_done[j].record(s)
+                body = (self.stage_dev[j], pk.values, pk.nnz * 2)
+            copies = [body, (self.stage_bitmap_dev[j], pk.bitmap, n * (self.F // 32) * 4),
+                      (self.stage_off_dev[j], pk.row_off, (n + 1) * 4), (self.stage_lab_dev[j], pk.labels, n * 4)]
+            nbytes = pk.nbytes
+        else:
+            copies = [(self.stage_dev[j], rows_f16, n * self.F * 2), (self.stage_lab_dev[j], labels, n * 4)]
+            nbytes = n * self.F * 2 + n * 4
+        native.h2d_copies(copies, stream=s)                 # one native call: rows / payload, bitmap, offsets, labels
+        self.h2d_done[j].record(s)
         self._end_set(j, n, ("palette" if rows_f16.palette else "bitmap") if packed else "dense",
                       nbytes + n * 8 + self.W * 8)
 
@@ -275,26 +272,26 @@ class DeviceEngine:
         self.stage_future[j].result()                       # slot tables of this batch are written (helper thread)
         s.wait_stream(torch.cuda.current_stream())          # the previous step must be done with the rings
         s.wait_event(self.h2d_done[j])
-        with torch.cuda.stream(s):
-            if self.stage_kind[j] != "csr":
-                self.stage_ws_dev[j][:n].copy_(self.stage_ws_host[j][:n], non_blocking=True)
-            self.win.copy_(self.stage_win_host[j], non_blocking=True)
-            if self.stage_kind[j] == "palette":
-                native.ring_store_palette(self.stage_bitmap_dev[j], self.stage_off_dev[j], self.stage_dev[j],
-                                          self.stage_lab_dev[j], self.stage_ws_dev[j], n, self.X, self.labels, self.cap,
-                                          self.F, stream=s)
-            elif self.stage_kind[j] == "bitmap":
-                native.ring_store_bitmap(self.stage_bitmap_dev[j], self.stage_off_dev[j], self.stage_dev[j],
-                                         self.stage_lab_dev[j], self.stage_ws_dev[j], n, self.X, self.labels, self.cap,
-                                         self.F, stream=s)
-            elif self.stage_kind[j] == "csr":
-                stage_dev, stride, _ = self.stage_csr_dev[j]
-                native.ring_scatter(stage_dev, n, stride, self.X, self.labels, self.cap, self.F, stream=s)
-            else:
-                native.ring_store_dense(self.stage_dev[j], self.stage_lab_dev[j], self.stage_ws_dev[j], n, self.X,
-                                        self.labels, self.cap, self.F, stream=s)
-            self.store_done[j].record(s)
-            self.ingest_done.record(s)
+        tables = [(self.win, self.stage_win_host[j], self.W * 8)]
+        if self.stage_kind[j] != "csr":
+            tables.append((self.stage_ws_dev[j], self.stage_ws_host[j], n * 8))
+        native.h2d_copies(tables, stream=s)
+        if self.stage_kind[j] == "palette":
+            native.ring_store_palette(self.stage_bitmap_dev[j], self.stage_off_dev[j], self.stage_dev[j],
+                                      self.stage_lab_dev[j], self.stage_ws_dev[j], n, self.X, self.labels, self.cap,
+                                      self.F, stream=s)
+        elif self.stage_kind[j] == "bitmap":
+            native.ring_store_bitmap(self.stage_bitmap_dev[j], self.stage_off_dev[j], self.stage_dev[j],
+                                     self.stage_lab_dev[j], self.stage_ws_dev[j], n, self.X, self.labels, self.cap,
+                                     self.F, stream=s)
+        elif self.stage_kind[j] == "csr":
+            stage_dev, stride, _ = self.stage_csr_dev[j]
+            native.ring_scatter(stage_dev, n, stride, self.X, self.labels, self.cap, self.F, stream=s)
+        else:
+            native.ring_store_dense(self.stage_dev[j], self.stage_lab_dev[j], self.stage_ws_dev[j], n, self.X,
+                                    self.labels, self.cap, self.F, stream=s)
+        self.store_done[j].record(s)
+        self.ingest_done.record(s)
         self.kernel_launches += 1
         self.stage_tail = (j + 1) % self.stage_sets
         self.stage_pending -= 1

@@ -103,6 +103,7 @@ def lib() -> C.CDLL:
     L.psb_pack_bitmap_csr.argtypes = [vp, vp, vp, C.c_longlong, C.c_int, vp, vp, vp]
     L.psb_pack_bitmap_dense.restype = C.c_longlong
     L.psb_pack_bitmap_dense.argtypes = [vp, C.c_longlong, C.c_int, vp, vp, vp]
+    L.psb_h2d_copies.argtypes = [C.c_int, vp, vp, vp, vp]
     L.psb_pack_palette_dense.restype = C.c_longlong
     L.psb_pack_palette_dense.argtypes = [vp, C.c_longlong, C.c_int, vp, vp, vp, C.c_longlong]
     L.psb_ring_store_palette.argtypes = [vp, ip, vp, ip, ip, C.c_int, vp, ip, C.c_int, C.c_int, vp]
@@ -270,6 +271,16 @@ def ring_store_bitmap(bitmap, row_off, values, labels_in, worker_slot, n: int, X
     check(lib().psb_ring_store_bitmap(_ptr(bitmap), _ptr(row_off), _ptr(values), _ptr(labels_in), _ptr(worker_slot), n,
                                       _ptr(X), _ptr(labels), cap, num_features, _stream(stream)),
           "psb_ring_store_bitmap")
+
+
+def h2d_copies(copies, stream=None) -> None:
+    """copies: iterable of (device tensor, pinned host tensor, nbytes); one native call, asynchronous on `stream`."""
+    copies = [c for c in copies if c[2] > 0]
+    n = len(copies)
+    dst = (C.c_void_p * n)(*[c[0].data_ptr() for c in copies])
+    src = (C.c_void_p * n)(*[c[1].data_ptr() for c in copies])
+    nb = (C.c_size_t * n)(*[int(c[2]) for c in copies])
+    check(lib().psb_h2d_copies(n, dst, src, nb, _stream(stream)), "psb_h2d_copies")
 
 
 def ring_store_palette(bitmap, row_off, payload, labels_in, worker_slot, n: int, X, labels, cap: int,
