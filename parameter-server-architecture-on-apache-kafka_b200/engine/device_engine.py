@@ -254,6 +254,8 @@ class DeviceEngine:
                       (self.stage_off_dev[j], pk.row_off, (n + 1) * 4), (self.stage_lab_dev[j], pk.labels, n * 4)]
             nbytes = pk.nbytes
         else:
+            if rows_f16.dtype != torch.float16 or labels.dtype != torch.int32 or not rows_f16.is_contiguous():
+                raise native.NativeError("ingest: rows must be contiguous fp16 [n, F] and labels int32 (pinned host tensors)")
             copies = [(self.stage_dev[j], rows_f16, n * self.F * 2), (self.stage_lab_dev[j], labels, n * 4)]
             nbytes = n * self.F * 2 + n * 4
         native.h2d_copies(copies, stream=s)                 # one native call: rows / payload, bitmap, offsets, labels
