@@ -1,12 +1,13 @@
 // K2, tensor flavour: the worker's local solve with every pass over the input buffer running on
-// tcgen05 tensor cores fed by TMA, accumulators in TMEM.  One CTA per worker, one CTA per SM.
+// tcgen05 tensor cores fed by TMA, accumulators in TMEM.  One CTA per worker; two CTAs share an SM when there
+// are more workers than SMs (4-slot rings), otherwise one CTA per SM with a 10-slot ring.
 //
 // One loss/gradient evaluation is one continuous TMA stream through a shared-memory ring of
 // [128 rows x 64 features] fp16 chunks (16 KB, SWIZZLE_128B); a "slab" is 128 rows = F/64 chunks:
 //   A(s)    : slab s, consumed K-major by GEMM1   Z_s[128 x 16] = slab x Wsp[F x 16]
 //             (Wsp = fp16 hi | lo halves of the 8 weight columns, resident in shared memory)
 //   epilogue: TMEM -> registers, + intercept, softmax over the R class rows, loss, residual r = p - y,
-//             r -> fp16 hi | lo -> shared memory as a 16 x 128 MN-major B operand (double buffered)
+//             r -> fp16 hi | lo -> shared memory as a 16 x 128 MN-major B operand
 //   B(s)    : slab s AGAIN (an L2 hit: A(s) is fetched with an evict-last policy, B(s) right behind it with
 //             evict-first), the same bytes consumed MN-major by GEMM2
 //             G[F x 16] += slab^T x Rsp_s   (M = 128 features per tile, K = 128 rows)
@@ -15,7 +16,11 @@
 // and DRAM sees each row once per evaluation.  X^T R needs no atomics.  After the last slab the G accumulators
 // (F/128 tiles x 16 TMEM columns) are drained, scaled by 1/(n std_f) and written to the solver's
 // gradient vector.  The per-feature standard deviation (Spark standardisation) is computed by two
-// otherwise idle warps straight from the shared-memory chunks of the FIRST evaluation's A stream.
+// otherwise idle warps straight from the shared-memory chunks of the FIRST evaluation (half of the chunks on
+// their A use, half on their B use).  Consecutive passes visit the slabs in opposite directions (L2 reuse).
+// Build-time instrumentation (off by default): -DPSB_TC_PROFILE=1|2|3 (cycles per role into info[4..7]),
+// -DPSB_TC_TRACE (block-0 timeline, printf), -DPSB_TC_EXPERIMENT_NO_TMA / _NO_MMA / _NO_STATS_LDS (timing-only
+// builds with wrong numerics); drivers in tools/ (mma_role_profile.py, trace_step.py, cta_span.py, phase_times.py).
 //
 // The solver driving these evaluations (L-BFGS + strong-Wolfe, or SGD) is solver.cuh; pull / push /
 // apply over peer memory is comm.cuh.  Replaces LogisticRegressionTaskSpark.calculateGradients
