@@ -24,8 +24,9 @@ for W, impl in ((296, native.IMPL_TC), (148, native.IMPL_SIMT)):
     rows = X[0, :128].repeat(W, 1).cpu().pin_memory()
     labs = y[0, :128].repeat(W).cpu().pin_memory()
     workers = np.repeat(np.arange(W, dtype=np.int32), 128)
-    for _ in range(3):
-        eng.ingest(rows, labs, workers, np.zeros(W * 128))
+    packs = [native.PackedRows(W * 128, F, palette=pal).pack_dense(rows, labs) for pal in (True, False)]
+    for it in range(3):
+        eng.ingest(rows if it == 0 else packs[it - 1], labs, workers, np.zeros(W * 128))   # dense, palette, bitmap
         eng.step()
         eng.evaluate()
     print("dense impl", impl, "W", W, "loss", float(eng.read_loss().mean()), "status", eng.status())
