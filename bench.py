@@ -128,6 +128,8 @@ def synth_buffers(torch, W, cap, F, density, seed, device):
 def main():
     a = parse()
     if a.impl == "reference":
+        if int(os.environ.get("RANK", "0")) != 0:          # under torchrun: one line, from rank 0
+            return 0
         print(json.dumps({"impl": "reference",
                           "unavailable": "reference is Java 8 + Gradle + Kafka + Spark (no setup.py/pyproject; pip "
                                          "install of /root/reference fails), and no JVM/Gradle/Kafka/Spark exists "
