@@ -105,7 +105,7 @@ __global__ void __launch_bounds__(256) psb_ring_store_bitmap_kernel(const uint32
 // expands presence word l of every 32-word group: the warp scan of the popcounts gives it its first code index,
 // every set bit fetches its nibble and the value comes from the palette lane by shuffle.  Raw rows (npal == 0)
 // read their fp16 values directly.
-__global__ void __launch_bounds__(256) psb_ring_store_palette_kernel(const uint32_t* __restrict__ bitmap,
+__global__ void __launch_bounds__(256, 4) psb_ring_store_palette_kernel(const uint32_t* __restrict__ bitmap,
                                                                     const int* __restrict__ row_off,
                                                                     const unsigned char* __restrict__ payload,
                                                                     const int* __restrict__ labels_in,
