@@ -180,3 +180,26 @@ def test_pipelined_ingest_three_sets_in_order():
     assert torch.equal(piped.X.view(torch.int16) * (piped.X != 0), plain.X.view(torch.int16) * (plain.X != 0))
     assert torch.equal(piped.labels, plain.labels) and torch.equal(piped.win, plain.win)
     piped.close(), plain.close()
+
+
+def test_pipelined_loss_read_returns_the_step_it_was_issued_behind():
+    """read_loss_begin / read_loss_end: the copy is ordered behind the step it follows, so its ticket still holds
+    that step's losses after the next step has been queued."""
+    from psb200.engine.device_engine import DeviceEngine
+    cfg = PSConfig(num_workers=2, num_features=256, max_buffer_size=128, min_buffer_size=16)
+    rng = np.random.default_rng(4)
+    eng = DeviceEngine(cfg, 2, impl=0)
+    rows = torch.from_numpy((rng.standard_normal((2, 128, 256)) * (rng.random((2, 128, 256)) < 0.3)).astype(np.float16)).cuda()
+    labs = torch.from_numpy(rng.integers(1, 6, (2, 128)).astype(np.int32)).cuda()
+    eng.fill(rows, labs)
+    eng.step()
+    t1 = eng.read_loss_begin()
+    first = eng.read_loss().clone()               # synchronous read of the same step
+    eng.step()
+    t2 = eng.read_loss_begin()
+    assert t1 != t2
+    assert torch.equal(eng.read_loss_end(t1), first)
+    second = eng.read_loss().clone()
+    assert torch.equal(eng.read_loss_end(t2), second)
+    assert not torch.equal(first, second)         # the two clocks really differ
+    eng.close()
