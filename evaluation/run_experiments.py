@@ -12,7 +12,6 @@ import sys
 import time
 
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
-import numpy as np
 
 from psb200.config import PSConfig, SERVER_LOG_HEADER, WORKER_LOG_HEADER
 from psb200.data import ReviewGenerator

@@ -10,8 +10,6 @@ from __future__ import annotations
 
 import os
 import signal
-import sys
-from typing import Optional
 
 from ..config import PSConfig
 from ..data import CSRBatch, ReviewGenerator, read_csv

@@ -21,7 +21,6 @@ never makes one launch wait on another.
 """
 from __future__ import annotations
 
-import ctypes as C
 from typing import List, Optional
 
 import numpy as np

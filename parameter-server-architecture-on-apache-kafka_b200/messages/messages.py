@@ -12,7 +12,7 @@ Values are dense ``float32`` vectors over the key range instead of boxed maps.
 """
 from __future__ import annotations
 
-from dataclasses import dataclass, field
+from dataclasses import dataclass
 from typing import Dict, Optional
 
 import numpy as np

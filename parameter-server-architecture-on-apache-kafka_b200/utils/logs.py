@@ -10,12 +10,10 @@ everything printed afterwards lands in the file, including the producer's EOF li
 """
 from __future__ import annotations
 
-import io
 import sys
 import threading
 from typing import List, Optional, TextIO
 
-from ..config import SERVER_LOG_HEADER, WORKER_LOG_HEADER
 
 
 def _num(x) -> str:

@@ -5,7 +5,7 @@ import pytest
 torch = pytest.importorskip("torch")
 
 from psb200.config import PSConfig
-from psb200.data import CSRBatch, ReviewGenerator
+from psb200.data import ReviewGenerator
 
 pytestmark = pytest.mark.gpu
 

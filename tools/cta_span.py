@@ -16,7 +16,6 @@ dev = torch.device("cuda", 0)
 X, y = synth_buffers(torch, W, 1024, 1024, 0.45, 1, dev)
 eng = DeviceEngine(PSConfig(num_workers=W, max_buffer_size=1024), W, impl=native.IMPL_TC, stage_rows=W)
 eng.fill(X, y)
-import contextlib, io
 for _ in range(3):
     eng.step()
 torch.cuda.synchronize()
