@@ -283,6 +283,20 @@ extern "C" int psb_buffers_on_batch(void** buffers, int num_buffers, const int* 
         worker_slot[2 * i] = w, worker_slot[2 * i + 1] = slot;
         win[2 * w] = head, win[2 * w + 1] = count;
     }
+    // A batch that carries more rows for one worker than its ring holds writes some slots twice.  The store
+    // kernels handle the rows of a batch in parallel, so only the LAST row of each (worker, slot) may be
+    // written: earlier ones get slot -1 and are skipped on the device (the ring then holds the last
+    // max_size rows, as a row-by-row replay would leave it).
+    int min_cap = 1 << 30;
+    for (int w = 0; w < num_buffers; ++w) min_cap = std::min(min_cap, ((Buffer*)buffers[w])->max_size);
+    if (n > min_cap) {
+        std::vector<int> kept((size_t)num_buffers, 0);
+        for (int i = n - 1; i >= 0; --i) {
+            const int w = worker_slot[2 * i];
+            if (kept[w] >= ((Buffer*)buffers[w])->max_size) worker_slot[2 * i + 1] = -1;
+            else ++kept[w];
+        }
+    }
     return 0;
 }
 

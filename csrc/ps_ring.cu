@@ -11,6 +11,7 @@ __global__ void __launch_bounds__(256) psb_ring_scatter_kernel(const uint32_t* _
     for (int r = blockIdx.x; r < n; r += gridDim.x) {
         const uint32_t* row = stage + (size_t)r * stride_words;
         const int nnz = (int)row[0], worker = (int)row[2], slot = (int)row[3];
+        if (slot < 0) continue;                   // superseded by a later row of the same batch (block-uniform)
         __half* dst = X + ((size_t)worker * cap + slot) * F;
         // zero-fill then scatter: two phases, rows are short
         uint4* d16 = (uint4*)dst;
@@ -33,6 +34,7 @@ __global__ void __launch_bounds__(256) psb_ring_store_half_kernel(const __half* 
                                                                  int cap, int F) {
     for (int r = blockIdx.x; r < n; r += gridDim.x) {
         const int worker = worker_slot[2 * r], slot = worker_slot[2 * r + 1];
+        if (slot < 0) continue;
         const uint4* src = (const uint4*)(rows + (size_t)r * F);
         uint4* dst = (uint4*)(X + ((size_t)worker * cap + slot) * F);
         for (int i = threadIdx.x; i < F / 8; i += blockDim.x) dst[i] = src[i];
@@ -47,6 +49,7 @@ __global__ void __launch_bounds__(256) psb_ring_store_dense_kernel(const float* 
                                                                   int cap, int F) {
     for (int r = blockIdx.x; r < n; r += gridDim.x) {
         const int worker = worker_slot[2 * r], slot = worker_slot[2 * r + 1];
+        if (slot < 0) continue;
         const float2* src = (const float2*)(rows + (size_t)r * F);
         __half2* dst = (__half2*)(X + ((size_t)worker * cap + slot) * F);
         for (int i = threadIdx.x; i < F / 2; i += blockDim.x) dst[i] = __float22half2_rn(src[i]);
@@ -69,6 +72,7 @@ __global__ void __launch_bounds__(256) psb_ring_store_bitmap_kernel(const uint32
     const int words = F >> 5;
     for (int r = blockIdx.x * wpb + (threadIdx.x >> 5); r < n; r += gridDim.x * wpb) {
         const int worker = worker_slot[2 * r], slot = worker_slot[2 * r + 1];
+        if (slot < 0) continue;                   // warp-uniform: one row per warp
         __half* dst = X + ((size_t)worker * cap + slot) * F;
         int base = row_off[r];
         for (int w0 = 0; w0 < words; w0 += 32) {
@@ -116,6 +120,7 @@ __global__ void __launch_bounds__(256, 4) psb_ring_store_palette_kernel(const ui
     const int words = F >> 5;
     for (int r = blockIdx.x * wpb + (threadIdx.x >> 5); r < n; r += gridDim.x * wpb) {
         const int worker = worker_slot[2 * r], slot = worker_slot[2 * r + 1];
+        if (slot < 0) continue;
         __half* dst = X + ((size_t)worker * cap + slot) * F;
         const unsigned char* p = payload + row_off[r];
         const int npal = *(const unsigned short*)p;

@@ -32,10 +32,29 @@ def test_native_buffer_batch_form():
     ws = np.zeros((len(workers), 2), dtype=np.int32)
     win = np.zeros((3, 2), dtype=np.int32)
     native.buffers_on_batch(bufs, workers, now, ws, win)
-    for i, w in enumerate(workers):
-        assert ws[i, 0] == w and ws[i, 1] == ref[w].on_event(now[i])
+    later = {w: 0 for w in range(3)}                     # rows of the same worker that follow in the batch
+    expect = [ref[w].on_event(now[i]) for i, w in enumerate(workers)]
+    for i in range(len(workers) - 1, -1, -1):
+        w = workers[i]
+        assert ws[i, 0] == w and ws[i, 1] == (expect[i] if later[w] < 32 else -1)   # superseded rows are dropped
+        later[w] += 1
     for w in range(3):
         assert (win[w, 0], win[w, 1]) == (ref[w].ring.head, ref[w].ring.count)
+
+
+def test_batch_with_more_rows_than_the_ring_keeps_only_the_last_row_of_every_slot():
+    """The store kernels write the rows of one batch in parallel, so a (worker, slot) pair may appear once."""
+    cap = 8
+    bufs = [native.NativeBuffer(4, cap, 0.3) for _ in range(2)]
+    workers = np.array([0] * 21 + [1] * 5, dtype=np.int32)
+    ws = np.zeros((len(workers), 2), dtype=np.int32)
+    win = np.zeros((2, 2), dtype=np.int32)
+    native.buffers_on_batch(bufs, workers, np.zeros(len(workers)), ws, win)
+    live = ws[ws[:, 1] >= 0]
+    assert len({(int(w), int(s)) for w, s in live}) == len(live)            # no slot written twice
+    assert (ws[:21 - cap, 1] == -1).all() and (ws[21 - cap:, 1] >= 0).all()  # worker 0: only its last `cap` rows survive
+    assert sorted(ws[21 - cap:21, 1].tolist()) == list(range(cap))
+    assert (win[0, 0], win[0, 1]) == (21 % cap, cap) and (win[1, 0], win[1, 1]) == (5, 5)
 
 
 @pytest.mark.parametrize("model", [0, 3, -1])
