@@ -16,9 +16,13 @@ int psb_launch_worker_simt(const PsbSolver*, const CommCtx&, int, const void*, c
                            float*, float*, int*, float*, cudaStream_t);
 int psb_launch_worker_tc(const PsbSolver*, const CommCtx&, int, const void*, const int*, const int*, const float*,
                          float*, float*, int*, float*, cudaStream_t);
-int psb_launch_eval_simt(const void*, const int*, int, const float*, int, int, int*, cudaStream_t);
-int psb_launch_eval_tc(const void*, const int*, int, const float*, int, int, int*, cudaStream_t);
-int psb_launch_eval_finalize(const int*, float*, cudaStream_t);
+int psb_worker_simt_resident(const PsbSolver*);
+int psb_worker_tc_resident(const PsbSolver*, int);
+int psb_launch_eval_simt(const void*, const int*, int, const float*, const float*, size_t, int, int, int, int*,
+                         cudaStream_t);
+int psb_launch_eval_tc(const void*, const int*, int, const float*, const float*, size_t, int, int, int, int*,
+                       cudaStream_t);
+int psb_launch_eval_finalize(const int*, float*, int, cudaStream_t);
 int psb_launch_ring_scatter(const uint32_t*, int, int, void*, int*, int, int, cudaStream_t);
 int psb_launch_ring_store_dense(const void*, int, const int*, const int*, int, void*, int*, int, int, cudaStream_t);
 int psb_launch_ring_store_bitmap(const uint32_t*, const int*, const void*, const int*, const int*, int, void*, int*, int, int,
@@ -68,6 +72,45 @@ unsigned int* psb_comm_status(void* d_block, int num_features, int num_ranks) {
     return CommBlock(d_block, CommLayout::make(num_features, num_ranks)).status();
 }
 
+unsigned int* psb_comm_version_words(void* d_block, int num_features, int num_ranks) {
+    return CommBlock(d_block, CommLayout::make(num_features, num_ranks)).version();
+}
+unsigned int* psb_comm_rank_clocks(void* d_block, int num_features, int num_ranks) {
+    return CommBlock(d_block, CommLayout::make(num_features, num_ranks)).clocks();
+}
+unsigned int* psb_comm_worker_clocks(void* d_block, int num_features, int num_ranks) {
+    return CommBlock(d_block, CommLayout::make(num_features, num_ranks)).wclocks();
+}
+
+__global__ void psb_comm_set_clocks_kernel(CommBlock blk, unsigned int clock) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < PSB_MAX_RANKS) blk.version()[i] = clock, blk.clocks()[i] = clock;
+    if (i < PSB_MAX_WORKERS) blk.wclocks()[i] = clock;
+}
+int psb_comm_set_clocks(void* d_block, int num_features, int num_ranks, unsigned int clock, void* stream) {
+    PSB_REQUIRE(d_block, "psb_comm_set_clocks: null block");
+    psb_comm_set_clocks_kernel<<<(PSB_MAX_WORKERS + 255) / 256, 256, 0, (cudaStream_t)stream>>>(
+        CommBlock(d_block, CommLayout::make(num_features, num_ranks)), clock);
+    PSB_CHECK_CUDA(cudaGetLastError());
+    return 0;
+}
+
+// One warp waits (bounded) until every shard's version word of this block has reached `clock`: work enqueued behind it
+// on the stream (evaluation, checkpoint copies) then reads the complete weights of that clock from the replica.
+__global__ void psb_comm_wait_version_kernel(CommBlock blk, int num_ranks, unsigned int clock,
+                                             unsigned long long spin_limit) {
+    if ((int)threadIdx.x < num_ranks)
+        wait_ge_sys(blk.version() + threadIdx.x, clock, spin_limit, blk.status(), PSB_ERR_PULL_TIMEOUT);
+}
+int psb_comm_wait_version(void* d_block, int num_features, int num_ranks, unsigned int clock,
+                          unsigned long long spin_limit, void* stream) {
+    PSB_REQUIRE(d_block && num_ranks >= 1 && num_ranks <= PSB_MAX_RANKS, "psb_comm_wait_version: bad arguments");
+    psb_comm_wait_version_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(
+        CommBlock(d_block, CommLayout::make(num_features, num_ranks)), num_ranks, clock, spin_limit);
+    PSB_CHECK_CUDA(cudaGetLastError());
+    return 0;
+}
+
 // Reads the block's status word (synchronises the stream): 0, or PSB_E_TIMEOUT with the reason in psb_last_error().
 int psb_comm_check(void* d_block, int num_features, int num_ranks, void* stream) {
     PSB_REQUIRE(d_block, "psb_comm_check: null block");
@@ -104,15 +147,40 @@ int psb_worker_step(const PsbSolver* s, const PsbComm* comm, int num_workers, in
     } else {
         PSB_REQUIRE(comm->num_ranks >= 1 && comm->num_ranks <= PSB_MAX_RANKS, "num_ranks out of range");
         PSB_REQUIRE(comm->rank >= 0 && comm->rank < comm->num_ranks, "rank out of range");
-        PSB_REQUIRE(comm->workers_per_rank == num_workers, "workers_per_rank must equal num_workers");
         for (int q = 0; q < comm->num_ranks; ++q) PSB_REQUIRE(comm->peers[q], "peer block %d is null", q);
         cx.L = CommLayout::make(s->num_features, comm->num_ranks);
+        if (comm->mode == PSB_COMM_WORKER) {
+            // a launch is any group of this rank's workers: [worker_base, worker_base + num_workers)
+            PSB_REQUIRE(comm->total_workers >= 1 && comm->total_workers <= PSB_MAX_WORKERS,
+                        "total_workers must be in [1,%d] (got %d)", PSB_MAX_WORKERS, comm->total_workers);
+            PSB_REQUIRE(comm->worker_base >= 0 && comm->worker_base + num_workers <= comm->total_workers,
+                        "workers [%d,%d) are outside the clock table of %d workers", comm->worker_base,
+                        comm->worker_base + num_workers, comm->total_workers);
+            PSB_REQUIRE(comm->num_clocks >= 0 && comm->num_clocks <= 1 << 20, "num_clocks out of range");
+        } else {
+            PSB_REQUIRE(comm->workers_per_rank == num_workers, "workers_per_rank must equal num_workers");
+            PSB_REQUIRE(comm->num_clocks <= 1, "several clocks per launch need comm mode PSB_COMM_WORKER");
+        }
+    }
+    if (comm->mode == PSB_COMM_WORKER && comm->max_delay >= 0) {
+        // gated workers spin on each other's clock words: every CTA of the launch has to be on the GPU at once
+        const int fit = psb_worker_max_resident(s, impl, num_workers);
+        if (num_workers > fit) {
+            psb_set_error("bounded-delay launch of %d workers, but only %d worker CTAs of this shape are resident at "
+                          "once on this device: launch fewer workers per GPU", num_workers, fit);
+            return PSB_E_LIMIT;
+        }
     }
     if (impl == 0)
         return psb_launch_worker_simt(s, cx, num_workers, d_X, d_labels, d_win, d_w_in, d_delta, d_loss, d_info,
                                       d_scratch, (cudaStream_t)stream);
     return psb_launch_worker_tc(s, cx, num_workers, d_X, d_labels, d_win, d_w_in, d_delta, d_loss, d_info, d_scratch,
                                 (cudaStream_t)stream);
+}
+
+int psb_worker_max_resident(const PsbSolver* s, int impl, int num_workers) {
+    PSB_REQUIRE(s && num_workers >= 1, "psb_worker_max_resident: bad arguments");
+    return impl == 0 ? psb_worker_simt_resident(s) : psb_worker_tc_resident(s, num_workers);
 }
 
 int psb_apply_delta(float* d_w, const float* d_delta, float lr, int num_features, int skip_class, void* stream) {
@@ -125,19 +193,33 @@ int psb_eval(const void* d_X, const int* d_labels, int n, const float* d_w, int 
     PSB_REQUIRE(d_X && d_labels && d_w && d_conf && d_out, "psb_eval: null pointer");
     PSB_REQUIRE(n >= 0 && num_features >= 2 && num_features % 2 == 0, "psb_eval: bad shape");
     PSB_REQUIRE(num_class_rows >= 2 && num_class_rows <= PSB_CLASS_PAD, "num_class_rows must be in [2,8]");
+    return psb_eval_models(d_X, d_labels, n, d_w, nullptr, 0, 1, num_features, num_class_rows, d_conf, d_out, impl,
+                           stream);
+}
+
+int psb_eval_models(const void* d_X, const int* d_labels, int n, const float* d_w, const float* d_w_add,
+                    size_t model_stride_floats, int num_models, int num_features, int num_class_rows, int* d_conf,
+                    float* d_out, int impl, void* stream) {
+    PSB_REQUIRE(d_X && d_labels && d_w && d_conf && d_out, "psb_eval_models: null pointer");
+    PSB_REQUIRE(n >= 0 && num_features >= 2 && num_features % 2 == 0, "psb_eval_models: bad shape");
+    PSB_REQUIRE(num_class_rows >= 2 && num_class_rows <= PSB_CLASS_PAD, "num_class_rows must be in [2,8]");
+    PSB_REQUIRE(num_models >= 1 && num_models <= 65535, "num_models must be in [1,65535]");
+    PSB_REQUIRE(model_stride_floats % 4 == 0, "model stride must be a multiple of 4 floats");
     cudaStream_t st = (cudaStream_t)stream;
-    PSB_CHECK_CUDA(cudaMemsetAsync(d_conf, 0, 64 * sizeof(int), st));
+    PSB_CHECK_CUDA(cudaMemsetAsync(d_conf, 0, (size_t)num_models * 64 * sizeof(int), st));
     int rc = 0;
     if (n > 0)
-        rc = impl == 0 ? psb_launch_eval_simt(d_X, d_labels, n, d_w, num_features, num_class_rows, d_conf, st)
-                       : psb_launch_eval_tc(d_X, d_labels, n, d_w, num_features, num_class_rows, d_conf, st);
+        rc = impl == 0 ? psb_launch_eval_simt(d_X, d_labels, n, d_w, d_w_add, model_stride_floats, num_models,
+                                              num_features, num_class_rows, d_conf, st)
+                       : psb_launch_eval_tc(d_X, d_labels, n, d_w, d_w_add, model_stride_floats, num_models,
+                                            num_features, num_class_rows, d_conf, st);
     if (rc) return rc;
-    return psb_launch_eval_finalize(d_conf, d_out, st);
+    return psb_launch_eval_finalize(d_conf, d_out, num_models, st);
 }
 
 int psb_eval_finalize(const int* d_conf, float* d_out, void* stream) {
     PSB_REQUIRE(d_conf && d_out, "psb_eval_finalize: null pointer");
-    return psb_launch_eval_finalize(d_conf, d_out, (cudaStream_t)stream);
+    return psb_launch_eval_finalize(d_conf, d_out, 1, (cudaStream_t)stream);
 }
 
 int psb_ring_scatter(const uint32_t* d_stage, int n, int stride_words, void* d_X, int* d_labels, int cap,

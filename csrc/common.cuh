@@ -35,7 +35,7 @@ struct CommLayout {
     int num_ranks;
     // byte offsets
     size_t off_status, off_arrivals, off_ticket, off_version, off_clocks;
-    size_t off_rep, off_auth, off_acc, off_inbox, bytes;
+    size_t off_rep, off_auth, off_acc, off_inbox, off_wclocks, bytes;
 
     __host__ __device__ static CommLayout make(int num_features, int num_ranks) {
         CommLayout L;
@@ -53,6 +53,8 @@ struct CommLayout {
         L.off_auth = o;     o += (size_t)L.slice4 * 16;
         L.off_acc = o;      o += (size_t)2 * L.nv * 4;
         L.off_inbox = o;    o += (size_t)2 * num_ranks * L.slice4 * 16;
+        o = (o + 127) & ~(size_t)127;
+        L.off_wclocks = o;  o += (size_t)PSB_MAX_WORKERS * 4;  // uint32[PSB_MAX_WORKERS]: per-worker clocks
         L.bytes = (o + 255) & ~(size_t)255;
         return L;
     }
@@ -69,6 +71,7 @@ struct CommBlock {
     __host__ __device__ unsigned int* ticket(int parity) const { return (unsigned int*)(base + L.off_ticket + parity * 128); }
     __host__ __device__ unsigned int* version() const { return (unsigned int*)(base + L.off_version); }
     __host__ __device__ unsigned int* clocks() const { return (unsigned int*)(base + L.off_clocks); }
+    __host__ __device__ unsigned int* wclocks() const { return (unsigned int*)(base + L.off_wclocks); }
     __host__ __device__ float4* rep(int parity) const { return (float4*)(base + L.off_rep) + (size_t)parity * L.n4; }
     __host__ __device__ float4* auth() const { return (float4*)(base + L.off_auth); }
     __host__ __device__ float4* acc(int parity) const { return (float4*)(base + L.off_acc) + (size_t)parity * L.n4; }
@@ -86,6 +89,11 @@ __device__ __forceinline__ unsigned int ld_acquire_sys(const unsigned int* p) {
 }
 __device__ __forceinline__ void st_release_sys(unsigned int* p, unsigned int v) {
     asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ unsigned int ld_relaxed_sys(const unsigned int* p) {
+    unsigned int v;
+    asm volatile("ld.relaxed.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
 }
 __device__ __forceinline__ void st_relaxed_sys(unsigned int* p, unsigned int v) {
     asm volatile("st.relaxed.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");

@@ -266,6 +266,35 @@ extern "C" int psb_buffer_on_event(void* bp, double now_ms, int* head, int* coun
 
 extern "C" long long psb_buffer_inserted(void* bp) { return ((Buffer*)bp)->inserted; }
 
+// state layout: [window, n_deltas, pos, total, last, has_last, head, count, inserted(lo 2^32 units), deltas...]
+extern "C" int psb_buffer_get_state(void* bp, double* state, int capacity) {
+    const Buffer* b = (const Buffer*)bp;
+    if (!b || !state) return -1;
+    const int n = 9 + b->window;
+    if (capacity < n) return -1;
+    state[0] = b->window, state[1] = b->n_deltas, state[2] = b->pos, state[3] = b->total, state[4] = b->last;
+    state[5] = b->has_last ? 1.0 : 0.0, state[6] = b->head, state[7] = b->count, state[8] = (double)b->inserted;
+    for (int i = 0; i < b->window; ++i) state[9 + i] = b->deltas[(size_t)i];
+    return n;
+}
+extern "C" int psb_buffer_set_state(void* bp, const double* state, int n) {
+    Buffer* b = (Buffer*)bp;
+    if (!b || !state || n < 9 || (int)state[0] != b->window || n != 9 + b->window) {
+        psb_set_error("psb_buffer_set_state: state does not fit this buffer (window %d)", b ? b->window : -1);
+        return PSB_E_INVALID;
+    }
+    b->n_deltas = (int)state[1], b->pos = (int)state[2], b->total = state[3], b->last = state[4];
+    b->has_last = state[5] != 0.0, b->head = (int)state[6], b->count = (int)state[7];
+    b->inserted = (long long)state[8];
+    if (b->head < 0 || b->head >= b->max_size || b->count < 0 || b->count > b->max_size || b->pos < 0 ||
+        b->pos >= b->window || b->n_deltas < 0 || b->n_deltas > b->window) {
+        psb_set_error("psb_buffer_set_state: cursors out of range");
+        return PSB_E_INVALID;
+    }
+    for (int i = 0; i < b->window; ++i) b->deltas[(size_t)i] = state[9 + i];
+    return 0;
+}
+
 // Batch form used by the ingestion hot path: n events -> (worker, slot) table + the new (head, count)
 // window of every worker that received a row.  `buffers` is an array of psb_buffer_create handles.
 // (Splitting the workers of a batch over a small thread pool was measured: 0.33 -> 0.8-1.2 ms for 37,888 events —

@@ -5,14 +5,26 @@
 // (ps_eval_tc.cu) produces the same confusion matrix; both share the finalise kernel below.
 #include "common.cuh"
 
+// blockIdx.y = model when several weight sets are scored in one launch; W2 (optional) is added element-wise.
 __global__ void __launch_bounds__(256) psb_eval_simt_kernel(const __half* __restrict__ X, const int* __restrict__ labels,
-                                                           int n, const float* __restrict__ W, int F, int R,
-                                                           int* __restrict__ conf) {
+                                                           int n, const float* __restrict__ W,
+                                                           const float* __restrict__ W2, size_t model_stride, int F,
+                                                           int R, int* __restrict__ conf) {
     extern __shared__ __align__(16) unsigned char smem[];
     float* Ws = (float*)smem;
     __shared__ int cm[64];
+    W += (size_t)blockIdx.y * model_stride;
+    if (W2) W2 += (size_t)blockIdx.y * model_stride;
+    conf += (size_t)blockIdx.y * 64;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nwarp = blockDim.x >> 5;
-    for (int i = tid; i < (F + 1) * 2; i += blockDim.x) ((float4*)Ws)[i] = ((const float4*)W)[i];
+    for (int i = tid; i < (F + 1) * 2; i += blockDim.x) {
+        float4 v = ((const float4*)W)[i];
+        if (W2) {
+            const float4 u = ((const float4*)W2)[i];
+            v.x += u.x, v.y += u.y, v.z += u.z, v.w += u.w;
+        }
+        ((float4*)Ws)[i] = v;
+    }
     if (tid < 64) cm[tid] = 0;
     __syncthreads();
     const float4* W4 = (const float4*)Ws;
@@ -49,8 +61,9 @@ __global__ void __launch_bounds__(256) psb_eval_simt_kernel(const __half* __rest
     if (tid < 64 && cm[tid]) atomicAdd(&conf[tid], cm[tid]);
 }
 
-// Support-weighted F1 over the true-label classes + accuracy, from the 8x8 confusion matrix.
+// Support-weighted F1 over the true-label classes + accuracy, from the 8x8 confusion matrix (one block per model).
 __global__ void psb_eval_finalize_kernel(const int* __restrict__ conf, float* __restrict__ out) {
+    conf += (size_t)blockIdx.x * 64, out += (size_t)blockIdx.x * 2;
     const int c = threadIdx.x;                 // 32 threads; classes 0..7
     float tp = 0.f, sup = 0.f, pred = 0.f;
     if (c < 8) {
@@ -71,8 +84,8 @@ __global__ void psb_eval_finalize_kernel(const int* __restrict__ conf, float* __
     }
 }
 
-int psb_launch_eval_simt(const void* d_X, const int* d_labels, int n, const float* d_w, int F, int R, int* d_conf,
-                         cudaStream_t stream) {
+int psb_launch_eval_simt(const void* d_X, const int* d_labels, int n, const float* d_w, const float* d_w2,
+                         size_t model_stride, int num_models, int F, int R, int* d_conf, cudaStream_t stream) {
     const size_t smem = (size_t)(F + 1) * 32;
     if (smem > 200 * 1024) {
         psb_set_error("evaluation kernel: num_features %d does not fit shared memory", F);
@@ -80,15 +93,17 @@ int psb_launch_eval_simt(const void* d_X, const int* d_labels, int n, const floa
     }
     PSB_CHECK_CUDA(cudaFuncSetAttribute(psb_eval_simt_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     int blocks = (n + 7) / 8;
-    if (blocks > 148 * 2) blocks = 148 * 2;
+    const int cap_blocks = num_models > 1 ? 16 : 148 * 2;        // many models: the models fill the device
+    if (blocks > cap_blocks) blocks = cap_blocks;
     if (blocks < 1) blocks = 1;
-    psb_eval_simt_kernel<<<blocks, 256, smem, stream>>>((const __half*)d_X, d_labels, n, d_w, F, R, d_conf);
+    psb_eval_simt_kernel<<<dim3(blocks, num_models), 256, smem, stream>>>((const __half*)d_X, d_labels, n, d_w, d_w2,
+                                                                           model_stride, F, R, d_conf);
     PSB_CHECK_CUDA(cudaGetLastError());
     return 0;
 }
 
-int psb_launch_eval_finalize(const int* d_conf, float* d_out, cudaStream_t stream) {
-    psb_eval_finalize_kernel<<<1, 32, 0, stream>>>(d_conf, d_out);
+int psb_launch_eval_finalize(const int* d_conf, float* d_out, int num_models, cudaStream_t stream) {
+    psb_eval_finalize_kernel<<<num_models, 32, 0, stream>>>(d_conf, d_out);
     PSB_CHECK_CUDA(cudaGetLastError());
     return 0;
 }

@@ -2,7 +2,9 @@
 // epilogue fused.  logits[128 rows x 16] = X_tile[128 x F] (fp16, streamed by TMA, SWIZZLE_128B) times
 // Wsp[F x 16] where columns 0-7 hold the fp16 high parts of the 8 class columns and 8-15 the low parts
 // (hi + lo carries ~22 bits of the fp32 weight); the accumulator lives in TMEM (128 lanes x 16 columns).
-// One CTA per 128 rows; W is staged once per CTA and stays resident in shared memory.
+// One CTA per 128 rows and model; W is staged once per CTA and stays resident in shared memory.  blockIdx.y picks the
+// model when several weight sets are scored in one launch (the worker log rows: every locally fitted model is
+// scored on the test set, LogisticRegressionTaskSpark.java:186) — the test set is then served from L2.
 // Replaces LogisticRegressionTaskSpark.calculateEvaluationMetric (LogisticRegressionTaskSpark.java:236-251).
 #define PSB_HAVE_TC_EVAL 1
 #include "tc.cuh"
@@ -56,9 +58,15 @@ constexpr int kABytes = kTileM * kBlockK * 2;     // 16 KB per stage
 constexpr int kBChunkBytes = 16 * kBlockK * 2;    // 2 KB of Wsp per K block
 
 // Stage Wsp (hi/lo split, K-major SWIZZLE_128B, 16 rows per K block) from fp32 W[(F+1)][8].
-__device__ __forceinline__ void stage_wsp(unsigned char* sB, const float* __restrict__ W, int F) {
+// W2 (optional) is added element-wise: a worker's local model is its start weights plus its delta.
+__device__ __forceinline__ void stage_wsp(unsigned char* sB, const float* __restrict__ W, const float* __restrict__ W2,
+                                          int F) {
     for (int f = threadIdx.x; f < F; f += blockDim.x) {
-        const float4 a = ((const float4*)W)[2 * f], b = ((const float4*)W)[2 * f + 1];
+        float4 a = ((const float4*)W)[2 * f], b = ((const float4*)W)[2 * f + 1];
+        if (W2) {
+            const float4 a2 = ((const float4*)W2)[2 * f], b2 = ((const float4*)W2)[2 * f + 1];
+            a.x += a2.x, a.y += a2.y, a.z += a2.z, a.w += a2.w, b.x += b2.x, b.y += b2.y, b.z += b2.z, b.w += b2.w;
+        }
         const float w[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
         const int kb = f >> 6, k = f & 63, j = k >> 3, e = k & 7;
         unsigned char* chunk = sB + (size_t)kb * kBChunkBytes;
@@ -76,7 +84,13 @@ __device__ __forceinline__ void stage_wsp(unsigned char* sB, const float* __rest
 
 __global__ void __launch_bounds__(128, 1)
 psb_eval_tc_kernel(const __grid_constant__ CUtensorMap tmX, const int* __restrict__ labels, int n,
-                   const float* __restrict__ W, int F, int R, int* __restrict__ conf, unsigned int* __restrict__ err) {
+                   const float* __restrict__ W, const float* __restrict__ W2, size_t model_stride, int F, int R,
+                   int* __restrict__ conf) {
+    W += (size_t)blockIdx.y * model_stride;
+    if (W2) W2 += (size_t)blockIdx.y * model_stride;
+    conf += (size_t)blockIdx.y * 64;
+    // conf[63] (class 7 x class 7) can never be hit by labels 0..5: it doubles as the model's error word
+    unsigned int* err = (unsigned int*)conf + 63;
     extern __shared__ __align__(1024) unsigned char smem_raw[];
     unsigned char* smem = (unsigned char*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
     const int nkb = F / kBlockK;
@@ -102,9 +116,9 @@ psb_eval_tc_kernel(const __grid_constant__ CUtensorMap tmX, const int* __restric
         tc::mbar_fence_init();
     }
     if (tid < 64) cm[tid] = 0;
-    if (tid < 8) sbias[tid] = W[F * 8 + tid];
+    if (tid < 8) sbias[tid] = W[F * 8 + tid] + (W2 ? W2[F * 8 + tid] : 0.f);
     if (warp == 0) tc::tmem_alloc(tmem_slot, 32);
-    stage_wsp(sB, W, F);
+    stage_wsp(sB, W, W2, F);
     tc::fence_proxy_async_smem();
     tc::tc_fence_before();
     __syncthreads();
@@ -173,8 +187,8 @@ psb_eval_tc_kernel(const __grid_constant__ CUtensorMap tmX, const int* __restric
     if (warp == 0) tc::tmem_dealloc(tmem, 32);
 }
 
-int psb_launch_eval_tc(const void* d_X, const int* d_labels, int n, const float* d_w, int F, int R, int* d_conf,
-                       cudaStream_t stream) {
+int psb_launch_eval_tc(const void* d_X, const int* d_labels, int n, const float* d_w, const float* d_w2,
+                       size_t model_stride, int num_models, int F, int R, int* d_conf, cudaStream_t stream) {
     if (F % kBlockK != 0) {
         psb_set_error("tcgen05 evaluation kernel needs num_features %% 64 == 0 (got %d)", F);
         return PSB_E_INVALID;
@@ -188,9 +202,8 @@ int psb_launch_eval_tc(const void* d_X, const int* d_labels, int n, const float*
     int rc = psb_make_tmap_2d_f16(&tm, d_X, (uint64_t)n, (uint64_t)F, kTileM, kBlockK);
     if (rc) return rc;
     PSB_CHECK_CUDA(cudaFuncSetAttribute(psb_eval_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    // conf[63] (class 7 x class 7) can never be hit by labels 0..5: it doubles as the error word
-    psb_eval_tc_kernel<<<(n + kTileM - 1) / kTileM, 128, smem, stream>>>(tm, d_labels, n, d_w, F, R, d_conf,
-                                                                          (unsigned int*)d_conf + 63);
+    psb_eval_tc_kernel<<<dim3((n + kTileM - 1) / kTileM, num_models), 128, smem, stream>>>(
+        tm, d_labels, n, d_w, d_w2, model_stride, F, R, d_conf);
     PSB_CHECK_CUDA(cudaGetLastError());
     return 0;
 }

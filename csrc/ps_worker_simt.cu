@@ -107,19 +107,21 @@ struct SimtEval {
 };
 
 // ------------------------------------------------------------------ kernel
-__global__ void __launch_bounds__(512, 1)
-psb_worker_simt_kernel(PsbSolver sv, CommCtx cx, const __half* __restrict__ X, const int* __restrict__ labels,
-                       const int* __restrict__ win, const float* __restrict__ w_in, float* __restrict__ delta_out,
-                       float* __restrict__ loss_out, int* __restrict__ info_out, float* __restrict__ scratch) {
-    extern __shared__ __align__(16) unsigned char smem[];
+// One clock of one worker; false when an in-kernel wait gave up (the CTA stops).
+__device__ bool simt_clock(const PsbSolver& sv, const CommCtx& cx, int clock, int it, const __half* __restrict__ X,
+                           const int* __restrict__ labels, const int* __restrict__ win, const float* __restrict__ w_in,
+                           float* __restrict__ delta_out, float* __restrict__ loss_out, int* __restrict__ info_out,
+                           float* __restrict__ scratch, unsigned char* smem) {
     const int F = sv.num_features, R = sv.num_class_rows, cap = sv.cap;
     const int nv = (F + 1) * 8, n4 = nv / 4;
-    const int w = blockIdx.x;
+    const int w = blockIdx.x, gw = cx.c.worker_base + w;
     float* Ws = (float*)smem;
     float* Rs = Ws + nv;
     float* inv = Rs + (size_t)cap * 8;
     float* sred = inv + F;
     double* red = (double*)(sred + 16);
+    PsbClockRecord* rec = cx.c.mode == PSB_COMM_WORKER && cx.c.hist
+                              ? (PsbClockRecord*)cx.c.hist + (size_t)it * gridDim.x + w : nullptr;
 
     WorkerScratch ws(scratch + (size_t)w * PSB_SCRATCH_VECS * nv, nv);
     const int head = win[2 * w], count = win[2 * w + 1];
@@ -134,20 +136,17 @@ psb_worker_simt_kernel(PsbSolver sv, CommCtx cx, const __half* __restrict__ X, c
     if (cx.c.mode == PSB_COMM_NONE) {
         for (int i = threadIdx.x; i < n4; i += blockDim.x) ((float4*)w0)[i] = ((const float4*)w_in)[i];
         __syncthreads();
-    } else if (!comm_pull(cx, (float4*)w0)) {
-        return;
+    } else if (!comm_pull(cx, clock, gw, (float4*)w0, rec)) {
+        return false;
     }
     if (count <= 0) {                       // "There is no data for partition" (WorkerTrainingProcessor.java:131)
         if (threadIdx.x == 0) {
             loss_out[w] = nanf("");
             info_out[8 * w + 2] = -1, info_out[8 * w + 3] = 0;
+            if (rec) rec->loss = nanf("");
         }
-        if (cx.c.mode != PSB_COMM_NONE) {   // still take part in the protocol with a zero delta
-            for (int i = threadIdx.x; i < n4; i += blockDim.x) ((float4*)ws.vec[5])[i] = make_float4(0, 0, 0, 0);
-            __syncthreads();
-            comm_push(cx, (const float4*)ws.vec[5]);
-        }
-        return;
+        if (cx.c.mode != PSB_COMM_NONE) comm_push(cx, clock, gw, nullptr);   // still takes part in the protocol
+        return true;
     }
 
     // ---- standardisation statistics (unbiased sample std over the window)
@@ -172,6 +171,7 @@ psb_worker_simt_kernel(PsbSolver sv, CommCtx cx, const __half* __restrict__ X, c
     __syncthreads();
     if (threadIdx.x == 0) {
         loss_out[w] = (float)res.loss;
+        if (rec) rec->loss = (float)res.loss;
         info_out[8 * w + 0] = res.evals, info_out[8 * w + 1] = res.iterations;
         info_out[8 * w + 2] = res.status, info_out[8 * w + 3] = count;
         info_out[8 * w + 4] = (int)((t_stats - t_begin) >> 6), info_out[8 * w + 5] = (int)((t_solve - t_stats) >> 6);
@@ -180,16 +180,46 @@ psb_worker_simt_kernel(PsbSolver sv, CommCtx cx, const __half* __restrict__ X, c
         float4* out = (float4*)(delta_out + (size_t)w * nv);
         for (int i = threadIdx.x; i < n4; i += blockDim.x) out[i] = ((const float4*)delta)[i];
     } else {
-        comm_push(cx, (const float4*)delta);
+        comm_push(cx, clock, gw, (const float4*)delta);
     }
     if (threadIdx.x == 0) info_out[8 * w + 6] = (int)((clock64() - t_solve) >> 6), info_out[8 * w + 7] = (int)((clock64() - t_begin) >> 6);
+    return true;
+}
+
+__global__ void __launch_bounds__(512, 1)
+psb_worker_simt_kernel(PsbSolver sv, CommCtx cx, const __half* __restrict__ X, const int* __restrict__ labels,
+                       const int* __restrict__ win, const float* __restrict__ w_in, float* __restrict__ delta_out,
+                       float* __restrict__ loss_out, int* __restrict__ info_out, float* __restrict__ scratch) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    const int nclk = cx.c.mode == PSB_COMM_WORKER && cx.c.num_clocks > 1 ? cx.c.num_clocks : 1;
+    for (int it = 0; it < nclk; ++it) {
+        if (!simt_clock(sv, cx, cx.c.clock + it, it, X, labels, win, w_in, delta_out, loss_out, info_out, scratch, smem))
+            return;
+        __syncthreads();
+    }
+}
+
+static size_t simt_smem_bytes(const PsbSolver* s) {
+    const int nv = (s->num_features + 1) * 8;
+    return (size_t)nv * 4 + (size_t)s->cap * 32 + (size_t)s->num_features * 4 + 64 + 34 * 8;
+}
+
+// worker CTAs of this shape that can be resident on the current device at the same time
+int psb_worker_simt_resident(const PsbSolver* s) {
+    const size_t smem = simt_smem_bytes(s);
+    if (smem > 226 * 1024) return 0;
+    int dev = 0, sms = 0, per_sm = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess) return 0;
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    cudaFuncSetAttribute(psb_worker_simt_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, psb_worker_simt_kernel, 512, smem);
+    return sms * per_sm;
 }
 
 int psb_launch_worker_simt(const PsbSolver* s, const CommCtx& cx, int num_workers, const void* d_X,
                            const int* d_labels, const int* d_win, const float* d_w_in, float* d_delta,
                            float* d_loss, int* d_info, float* d_scratch, cudaStream_t stream) {
-    const int nv = (s->num_features + 1) * 8;
-    const size_t smem = (size_t)nv * 4 + (size_t)s->cap * 32 + (size_t)s->num_features * 4 + 64 + 34 * 8;
+    const size_t smem = simt_smem_bytes(s);
     PSB_REQUIRE(s->num_features % 2 == 0, "num_features must be even (got %d)", s->num_features);
     if (smem > 226 * 1024) {
         psb_set_error("SIMT worker kernel needs %zu bytes of shared memory (> 227 KB): lower max_buffer_size (%d) "

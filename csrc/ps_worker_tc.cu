@@ -703,15 +703,22 @@ psb_worker_tc_kernel(const __grid_constant__ CUtensorMap tmX, PsbSolver sv, Comm
     __syncthreads();
     PSB_TRACE(0);
 #endif
-    if (tid == 0) {
-        psb_tc_fail = 0, psb_tc_chunk_base = 0, psb_tc_need_redo = 0;
-        tc::tma_prefetch_desc(&tmX);
+    // Every clock starts from fresh barriers and ring counters (the roles' use counts restart with the clock), so a
+    // launch that runs several clocks per worker (PSB_COMM_WORKER) re-initialises them between two clocks.
+    auto init_barriers = [&](bool again) {
+        if (again)
+            for (int i = 0; i < 3 * kNS + 6; ++i) tc::mbar_inval(sh.bars() + i);
         for (int s = 0; s < kNS; ++s) tc::mbar_init(sh.full() + s, 1), tc::mbar_init(sh.empty() + s, 1);
         for (int i = 0; i < 2; ++i) tc::mbar_init(sh.z_full() + i, 1), tc::mbar_init(sh.r_full() + i, 4);
         tc::mbar_init(sh.g_full(), 1);
         for (int s = 0; s < kNS; ++s) tc::mbar_init(sh.sdone() + s, 1);
         tc::mbar_init(sh.inv_ready(), 2);
         tc::mbar_fence_init();
+    };
+    if (tid == 0) {
+        psb_tc_fail = 0, psb_tc_chunk_base = 0, psb_tc_need_redo = 0;
+        tc::tma_prefetch_desc(&tmX);
+        init_barriers(false);
     }
     if (warp == 0) tc::tmem_alloc(sh.tmem_slot(), kTmemCols);
     tc::tc_fence_before();
@@ -724,7 +731,23 @@ psb_worker_tc_kernel(const __grid_constant__ CUtensorMap tmX, PsbSolver sv, Comm
     int start = head - count;
     if (start < 0) start += cap;
     const int* lw = labels + (size_t)w * cap;
+    const int gw = cx.c.worker_base + w;
+    const int nclk = cx.c.mode == PSB_COMM_WORKER && cx.c.num_clocks > 1 ? cx.c.num_clocks : 1;
 
+  for (int it = 0; it < nclk; ++it) {
+    const int clock = cx.c.clock + it;
+    PsbClockRecord* rec = cx.c.mode == PSB_COMM_WORKER && cx.c.hist
+                              ? (PsbClockRecord*)cx.c.hist + (size_t)it * gridDim.x + w : nullptr;
+    if (it > 0) {
+        tc::tc_fence_before();
+        __syncthreads();
+        if (tid == 0) {
+            psb_tc_chunk_base = 0, psb_tc_need_redo = 0;
+            init_barriers(true);
+        }
+        __syncthreads();
+        tc::tc_fence_after();
+    }
     // ---- pull
     PSB_TRACE(1);
     const long long t_begin = clock64();
@@ -734,18 +757,16 @@ psb_worker_tc_kernel(const __grid_constant__ CUtensorMap tmX, PsbSolver sv, Comm
         for (int i = tid; i < n4; i += blockDim.x) ((float4*)w0)[i] = ((const float4*)w_in)[i];
         __syncthreads();
     } else {
-        alive = comm_pull(cx, (float4*)w0);
+        alive = comm_pull(cx, clock, gw, (float4*)w0, rec);
+        if (!alive) break;                                        // an in-kernel wait gave up: the CTA stops
     }
     if (alive && count <= 0) {
         if (tid == 0) {
             loss_out[w] = nanf("");
             info_out[8 * w + 2] = -1, info_out[8 * w + 3] = 0;
+            if (rec) rec->loss = nanf("");
         }
-        if (cx.c.mode != PSB_COMM_NONE) {
-            for (int i = tid; i < n4; i += blockDim.x) ((float4*)ws.vec[5])[i] = make_float4(0, 0, 0, 0);
-            __syncthreads();
-            comm_push(cx, (const float4*)ws.vec[5]);
-        }
+        if (cx.c.mode != PSB_COMM_NONE) comm_push(cx, clock, gw, nullptr);   // still takes part in the protocol
         alive = false;
     }
     if (alive) {
@@ -800,6 +821,7 @@ psb_worker_tc_kernel(const __grid_constant__ CUtensorMap tmX, PsbSolver sv, Comm
         PSB_TRACE(6);
         if (tid == 0) {
             loss_out[w] = psb_tc_fail ? nanf("") : (float)res.loss;
+            if (rec) rec->loss = loss_out[w];
             info_out[8 * w + 0] = res.evals, info_out[8 * w + 1] = res.iterations;
             info_out[8 * w + 2] = psb_tc_fail ? -2 : res.status, info_out[8 * w + 3] = count;
             info_out[8 * w + 4] = (int)((t_stats - t_begin) >> 6), info_out[8 * w + 5] = (int)((t_solve - t_stats) >> 6);
@@ -808,7 +830,7 @@ psb_worker_tc_kernel(const __grid_constant__ CUtensorMap tmX, PsbSolver sv, Comm
             float4* out = (float4*)(delta_out + (size_t)w * nv);
             for (int i = tid; i < n4; i += blockDim.x) out[i] = ((const float4*)delta)[i];
         } else {
-            comm_push(cx, (const float4*)delta);
+            comm_push(cx, clock, gw, (const float4*)delta);
         }
         if (tid == 0) info_out[8 * w + 6] = (int)((clock64() - t_solve) >> 6), info_out[8 * w + 7] = (int)((clock64() - t_begin) >> 6);
         PSB_TRACE(7);
@@ -822,6 +844,8 @@ psb_worker_tc_kernel(const __grid_constant__ CUtensorMap tmX, PsbSolver sv, Comm
         if (tid == (PSB_TC_PROFILE >= 2 ? 0 : 32)) for (int k = 0; k < 4; ++k) info_out[8 * w + 4 + k] = (int)(ev.prof[k] >> 6);
 #endif
     }
+    if (psb_tc_fail) break;                                       // (uniform: written before the last barrier of the clock)
+  }
     tc::tc_fence_before();
     __syncthreads();
     if (warp == 0) tc::tmem_dealloc(tmem, kTmemCols);
@@ -834,24 +858,11 @@ psb_worker_tc_kernel(const __grid_constant__ CUtensorMap tmX, PsbSolver sv, Comm
 #endif
 }
 
-int psb_launch_worker_tc(const PsbSolver* s, const CommCtx& cx, int num_workers, const void* d_X, const int* d_labels,
-                         const int* d_win, const float* d_w_in, float* d_delta, float* d_loss, int* d_info,
-                         float* d_scratch, cudaStream_t stream) {
-    const int F = s->num_features, cap = s->cap;
-    if (F % 128 != 0 || F > 1024 || cap % kSlabRows != 0) {
-        psb_set_error("tcgen05 worker kernel needs num_features %% 128 == 0, <= 1024 and max_buffer_size %% 128 == 0 "
-                      "(got %d, %d): use the SIMT kernel for this shape", F, cap);
-        return PSB_E_INVALID;
-    }
+// Ring depth and dynamic shared memory for a launch of `num_workers` CTAs on a device with `num_sms` SMs.
+// More workers than SMs: 4-slot rings so that two CTAs share an SM and one worker's vector / epilogue phases
+// overlap the other's streaming; otherwise one CTA per SM with a deep ring.
+static void tc_launch_shape(int F, int num_workers, int num_sms, int* kNS_out, size_t* smem_out) {
     const int nkb = F / kBlockK;
-    // More workers than SMs: 4-slot rings so that two CTAs share an SM and one worker's vector / epilogue
-    // phases overlap the other's streaming; otherwise one CTA per SM with a deep ring.
-    int num_sms = 148;
-    {
-        int dev = 0;
-        cudaGetDevice(&dev);
-        cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, dev);
-    }
     auto smem_for = [&](int ns) {
         return 1024 + (size_t)ns * kChunkBytes + (size_t)nkb * kBChunkBytes + 2 * kRBytes + (size_t)F * 4 + 32 * 4 +
                34 * 8 + (size_t)(3 * ns + 6) * 8 + 64;
@@ -862,7 +873,40 @@ int psb_launch_worker_tc(const PsbSolver* s, const CommCtx& cx, int num_workers,
         kNS = 4;
         while (kNS > 2 && 2 * (smem_for(kNS) + 1024) > 227 * 1024) kNS -= 2;
     }
-    const size_t smem = smem_for(kNS);
+    *kNS_out = kNS, *smem_out = smem_for(kNS);
+}
+
+// worker CTAs that can be resident at the same time when `num_workers` of them are launched together
+int psb_worker_tc_resident(const PsbSolver* s, int num_workers) {
+    int dev = 0, sms = 0, per_sm = 0, kNS = 0;
+    size_t smem = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess) return 0;
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    tc_launch_shape(s->num_features, num_workers, sms, &kNS, &smem);
+    cudaFuncSetAttribute(psb_worker_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, psb_worker_tc_kernel, kThreads, smem);
+    if (per_sm > 512 / kTmemCols) per_sm = 512 / kTmemCols;           // tensor memory: kTmemCols of 512 columns per CTA
+    return sms * per_sm;
+}
+
+int psb_launch_worker_tc(const PsbSolver* s, const CommCtx& cx, int num_workers, const void* d_X, const int* d_labels,
+                         const int* d_win, const float* d_w_in, float* d_delta, float* d_loss, int* d_info,
+                         float* d_scratch, cudaStream_t stream) {
+    const int F = s->num_features, cap = s->cap;
+    if (F % 128 != 0 || F > 1024 || cap % kSlabRows != 0) {
+        psb_set_error("tcgen05 worker kernel needs num_features %% 128 == 0, <= 1024 and max_buffer_size %% 128 == 0 "
+                      "(got %d, %d): use the SIMT kernel for this shape", F, cap);
+        return PSB_E_INVALID;
+    }
+    int num_sms = 148;
+    {
+        int dev = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, dev);
+    }
+    int kNS = 0;
+    size_t smem = 0;
+    tc_launch_shape(F, num_workers, num_sms, &kNS, &smem);
     CUtensorMap tm;
     int rc = psb_make_tmap_2d_f16(&tm, d_X, (uint64_t)num_workers * cap, (uint64_t)F, kSlabRows, kBlockK);
     if (rc) return rc;

@@ -42,6 +42,10 @@ extern "C" {
 #define PSB_COMM_NONE 0            /* write delta to d_delta (host applies)                     */
 #define PSB_COMM_SEQUENTIAL 1      /* mailbox push + last-arriver apply + replica broadcast      */
 #define PSB_COMM_ASYNC 2           /* red.add lr*delta into owner shard + clock table (k or inf) */
+#define PSB_COMM_WORKER 3          /* as ASYNC, but every WORKER owns a clock word, applies its own delta and is
+                                      gated on its own: the reference's per-partition MessageTracker state
+                                      (MessageTracker.java:42-88) evaluated by each worker CTA            */
+#define PSB_MAX_WORKERS 4096       /* entries of the per-worker clock table in a peer-memory block          */
 
 const char* psb_last_error(void);
 int psb_version(void);
@@ -71,7 +75,24 @@ typedef struct PsbComm {
     float lr;                      /* server learning rate 1/numWorkers (ServerProcessor.java:36) */
     unsigned long long spin_limit; /* clock64 cycles before a wait gives up (watchdog)      */
     void* peers[PSB_MAX_RANKS];
+    /* ---- PSB_COMM_WORKER only (leave zero otherwise) */
+    int num_clocks;                /* clocks every worker of this launch runs back to back, each at its own pace
+                                      (0 counts as 1); the window of a worker is read once per launch        */
+    int worker_base;               /* global id of the launch's worker 0 (clock table index)                 */
+    int total_workers;             /* workers of all ranks = live entries of the clock table (<= PSB_MAX_WORKERS) */
+    int delay_worker;              /* straggler injection: this global worker id sleeps delay_cycles before   */
+    unsigned long long delay_cycles; /* every clock (0: off)                                                  */
+    void* hist;                    /* optional PsbClockRecord[num_clocks][num_workers] of this launch (device) */
+    int home_remote;               /* peers[rank] lives on another GPU (server process' block): the intra-rank
+                                      reduction and ticket then use system-scope operations                   */
 } PsbComm;
+
+/* What a worker saw when it started clock `clock`: lag = clock - min over all workers' clocks at the moment the
+ * gate let it through (<= max_delay under bounded delay), lead = max over all workers' clocks - clock. */
+typedef struct PsbClockRecord {
+    float loss;
+    int clock, lag, lead;
+} PsbClockRecord;
 
 size_t psb_comm_block_bytes(int num_features, int num_ranks);
 /* zero the block and write the initial weights into both replicas and the owned shard */
@@ -80,7 +101,16 @@ int psb_comm_init_block(void* d_block, const float* d_w0, int num_features, int 
 float* psb_comm_replica(void* d_block, int num_features, int num_ranks, int parity);
 float* psb_comm_shard_weights(void* d_block, int num_features, int num_ranks);
 unsigned int* psb_comm_status(void* d_block, int num_features, int num_ranks);   /* [0]=error flag, [1..]=debug */
+unsigned int* psb_comm_version_words(void* d_block, int num_features, int num_ranks);   /* [PSB_MAX_RANKS] */
+unsigned int* psb_comm_rank_clocks(void* d_block, int num_features, int num_ranks);     /* [PSB_MAX_RANKS] */
+unsigned int* psb_comm_worker_clocks(void* d_block, int num_features, int num_ranks);   /* [PSB_MAX_WORKERS] */
+/* after a resume: every version / rank-clock / worker-clock word of the block restarts at `clock` */
+int psb_comm_set_clocks(void* d_block, int num_features, int num_ranks, unsigned int clock, void* stream);
 
+/* Sequential mode: enqueue a (bounded) device-side wait until all shards of clock `clock` have been published into
+ * this block's replica (version words >= clock); later work on `stream` sees the complete snapshot. */
+int psb_comm_wait_version(void* d_block, int num_features, int num_ranks, unsigned int clock,
+                          unsigned long long spin_limit, void* stream);
 /* 0, or PSB_E_TIMEOUT when an in-kernel wait of this rank gave up (synchronises `stream`) */
 int psb_comm_check(void* d_block, int num_features, int num_ranks, void* stream);
 
@@ -100,6 +130,12 @@ int psb_worker_step(const PsbSolver* s, const PsbComm* comm, int num_workers, in
                     const void* d_X, const int* d_labels, const int* d_win,
                     const float* d_w_in, float* d_delta, float* d_loss, int* d_info,
                     float* d_scratch, void* stream);
+
+/* Worker CTAs of this shape that fit on the current device at the same time when `num_workers` are launched
+ * together.  Bounded-delay PSB_COMM_WORKER launches spin on each other's clock words inside the kernel, so all
+ * workers that can be in flight on a GPU together (all groups, all streams) must fit; psb_worker_step checks its
+ * own launch and returns PSB_E_LIMIT otherwise. */
+int psb_worker_max_resident(const PsbSolver* s, int impl, int num_workers);
 
 /* The same step for callers that must not allocate device memory (a host process whose GPU memory
  * belongs to another framework's pool, a real-time loop that cannot afford cudaMalloc's device-wide
@@ -171,6 +207,14 @@ int psb_sparse_step_slab(const PsbSlabComm* comm, int step_index, const long lon
 int psb_eval(const void* d_X, const int* d_labels, int n, const float* d_w, int num_features,
              int num_class_rows, int* d_conf, float* d_out, int impl, void* stream);
 
+/* The same for `num_models` weight sets in ONE launch: model m is d_w + m * model_stride_floats, plus, element-wise,
+ * d_w_add + m * model_stride_floats when d_w_add is given (a worker's locally fitted model = the weights it pulled +
+ * its delta: the worker log row of WorkerTrainingProcessor.java:85-92 scores that model on the test set,
+ * LogisticRegressionTaskSpark.java:186).  d_conf: int[num_models][64]; d_out: float[num_models][2]. */
+int psb_eval_models(const void* d_X, const int* d_labels, int n, const float* d_w, const float* d_w_add,
+                    size_t model_stride_floats, int num_models, int num_features, int num_class_rows, int* d_conf,
+                    float* d_out, int impl, void* stream);
+
 /* weighted F1 + accuracy from an 8x8 confusion matrix (shared by the dense and the sparse evaluation) */
 int psb_eval_finalize(const int* d_conf, float* d_out, void* stream);
 
@@ -231,6 +275,10 @@ void* psb_buffer_create(int min_size, int max_size, float bc, int window);
 void psb_buffer_destroy(void* b);
 int psb_buffer_on_event(void* b, double now_ms, int* head, int* count, int* target);
 long long psb_buffer_inserted(void* b);   /* rows ever inserted == numTuplesSeen of the worker log */
+/* Checkpoint of a buffer's policy state: the inter-arrival window and the ring cursors.  state: double[window + 8];
+ * get returns the number of doubles written (-1: capacity too small), set returns 0 or PSB_E_INVALID. */
+int psb_buffer_get_state(void* b, double* state, int capacity);
+int psb_buffer_set_state(void* b, const double* state, int n);
 /* n events at once: fills worker_slot[n][2] and updates win[num_buffers][2] for the touched workers */
 int psb_buffers_on_batch(void** buffers, int num_buffers, const int* workers, const double* now_ms, int n,
                          int* worker_slot, int* win);

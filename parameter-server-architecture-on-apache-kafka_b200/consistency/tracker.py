@@ -12,7 +12,7 @@ turns a received gradient into the set of workers to answer:
 
 This module is the host-side, pure-Python statement of that contract.  The same
 predicate is evaluated inside the kernels on clock words in peer memory
-(``csrc/ps_comm.cuh``: ``wait_clock_gate``) and in the C++ runtime
+(``csrc/comm.cuh``: ``comm_pull`` / ``wait_ge_sys``) and in the C++ runtime
 (``csrc/host_runtime.cpp``); tests check all three against each other.
 """
 from __future__ import annotations

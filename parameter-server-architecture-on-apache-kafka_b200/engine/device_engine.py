@@ -14,6 +14,15 @@ JVM and three Kafka topics:
 solve -> push -> apply (``psb_worker_step``).  Nothing is synchronised with the
 host unless the caller asks for the loss.
 
+Asynchrony comes in two granularities (``async_granularity``).  ``"rank"``: the
+workers of a GPU advance in lockstep and the relaxed models hold between GPUs.
+``"worker"``: every worker CTA owns a clock word and is gated on its own, as the
+reference's ``MessageTracker`` does per partition (``MessageTracker.java:42-88``);
+``step(num_clocks=n)`` then lets each worker run n clocks at its own pace inside
+one launch, and ``groups > 1`` launches the workers of a GPU as several
+independent groups, each on its own stream (``step_group``), so that a slow
+group never holds back a launch boundary of a fast one.
+
 Multi-GPU: one engine per process, blocks exchanged with ``cudaIpc`` through
 ``torch.distributed`` (``connect()``).  Tests on fewer GPUs than ranks build several
 engines on one device (``VirtualCluster``) and step them in clock order, which
@@ -35,11 +44,19 @@ from ..ops import native
 class DeviceEngine:
     def __init__(self, cfg: PSConfig, workers_per_rank: int, rank: int = 0, world: int = 1, impl: int = native.IMPL_SIMT,
                  device: Optional[torch.device] = None, w0: Optional[np.ndarray] = None, stage_rows: int = 0,
-                 stage_sets: int = 3, spin_limit_cycles: int = 20_000_000_000):
+                 stage_sets: int = 3, spin_limit_cycles: int = 20_000_000_000, async_granularity: str = "rank",
+                 groups: int = 1, max_clocks_per_launch: int = 64, external_block: Optional[int] = None,
+                 home_remote: bool = False):
         if not torch.cuda.is_available():
             raise native.NativeError("DeviceEngine needs a CUDA device")
+        if async_granularity not in ("rank", "worker"):
+            raise ValueError("async_granularity must be 'rank' or 'worker'")
+        if groups < 1 or workers_per_rank % groups:
+            raise ValueError(f"groups ({groups}) must divide workers_per_rank ({workers_per_rank})")
         native.lib()
         self.cfg, self.W, self.rank, self.world, self.impl = cfg, workers_per_rank, rank, world, impl
+        self.async_granularity, self.groups, self.home_remote = async_granularity, groups, bool(home_remote)
+        self.max_clocks_per_launch = max(1, int(max_clocks_per_launch))
         self.device = device or torch.device("cuda", torch.cuda.current_device())
         self.layout = LogRegLayout(cfg.num_features, cfg.num_classes)
         F, cap = cfg.num_features, cfg.max_buffer_size
@@ -62,13 +79,24 @@ class DeviceEngine:
         self.spin_limit = spin_limit_cycles
         w0 = self.layout.zeros() if w0 is None else np.asarray(w0, dtype=np.float32)
         self.w0 = torch.from_numpy(w0.reshape(-1).copy()).to(dev)
-        # peer-memory block (raw cudaMalloc so it can be exported over IPC)
+        if self.total_workers > native.MAX_WORKERS and async_granularity == "worker":
+            raise ValueError(f"per-worker clocks support at most {native.MAX_WORKERS} workers")
+        # peer-memory block (raw cudaMalloc so it can be exported over IPC); `external_block`: the block was
+        # allocated and initialised by another process (the server app) and is only mapped here
         self.block_bytes = native.comm_block_bytes(F, world)
-        self.block = native.device_malloc(self.block_bytes)
+        self.owns_block = external_block is None
+        self.block = native.device_malloc(self.block_bytes) if self.owns_block else int(external_block)
         self.peers: List[int] = [0] * world
         self.peers[rank] = self.block
-        native.check(native.lib().psb_comm_init_block(self.block, self.w0.data_ptr(), F, world, rank,
-                                                      native._stream()), "psb_comm_init_block")
+        if self.owns_block:
+            native.check(native.lib().psb_comm_init_block(self.block, self.w0.data_ptr(), F, world, rank,
+                                                          native._stream()), "psb_comm_init_block")
+        # per-worker asynchrony: one clock per launch group, a record of every (clock, worker) of a launch
+        self.gsize = self.W // groups
+        self.group_clock = [0] * groups
+        self.group_streams = [torch.cuda.Stream(device=dev) for _ in range(groups)] if groups > 1 else [None]
+        self.hist = None
+        self.delay_worker, self.delay_cycles = -1, 0
         # ingestion: host-side window bookkeeping + a ring of staging sets.  begin() fills set `head` over the
         # copy stream, commit() drains set `tail` into the rings over the ingest stream; with S sets the H2D of
         # batch k+S-1 overlaps the step that trains on batch k.
@@ -128,13 +156,26 @@ class DeviceEngine:
         c.clock, c.lr, c.spin_limit = self.clock, self.lr, self.spin_limit
         cm = self.cfg.consistency_model
         c.max_delay = cm if cm > 0 else -1
+        c.home_remote = int(self.home_remote)
+        c.delay_worker = -1
         for q in range(self.world):
             c.peers[q] = self.peers[q]
         return c
 
     @property
     def comm_mode(self) -> int:
-        return native.COMM_SEQUENTIAL if self.cfg.consistency_model == 0 else native.COMM_ASYNC
+        if self.cfg.consistency_model == 0:
+            return native.COMM_SEQUENTIAL
+        return native.COMM_WORKER if self.async_granularity == "worker" else native.COMM_ASYNC
+
+    def inject_delay(self, global_worker: int, cycles: int) -> None:
+        """Straggler injection for the per-worker modes: that worker sleeps `cycles` SM cycles before every clock."""
+        self.delay_worker, self.delay_cycles = int(global_worker), int(cycles)
+
+    def max_resident_workers(self) -> int:
+        """Worker CTAs of this shape that fit on the device at once (gated per-worker launches need all W resident)."""
+        return int(native.check(native.lib().psb_worker_max_resident(self.solver, self.impl, self.W),
+                                "psb_worker_max_resident"))
 
     # ------------------------------------------------------------------ ingestion
     def load_test(self, test: CSRBatch) -> None:
@@ -301,16 +342,24 @@ class DeviceEngine:
         torch.cuda.nvtx.range_pop()
 
     # ------------------------------------------------------------------ the step
-    def step(self, mode: Optional[int] = None) -> None:
-        """Enqueue one parameter-server clock (one kernel).  NVTX range 'psb.step' for timeline tools."""
+    def step(self, mode: Optional[int] = None, num_clocks: int = 1) -> None:
+        """Enqueue one parameter-server clock (one kernel); per-worker mode: `num_clocks` clocks of every group.
+        NVTX range 'psb.step' for timeline tools."""
         torch.cuda.nvtx.range_push("psb.step")
         try:
-            self._step(mode)
+            self._step(mode, num_clocks)
         finally:
             torch.cuda.nvtx.range_pop()
 
-    def _step(self, mode: Optional[int] = None) -> None:
+    def _step(self, mode: Optional[int] = None, num_clocks: int = 1) -> None:
         mode = self.comm_mode if mode is None else mode
+        if mode == native.COMM_WORKER:
+            for g in range(self.groups):
+                self.step_group(g, num_clocks, stream=False if self.groups == 1 else None)
+            self.clock = min(self.group_clock)
+            return
+        if num_clocks != 1:
+            raise ValueError("several clocks per launch need async_granularity='worker' and consistency_model != 0")
         comm = self._comm(mode)
         native.worker_step(self.solver, comm, self.W, self.impl, self.X, self.labels, self.win,
                            self.w0 if mode == native.COMM_NONE else None,
@@ -318,6 +367,52 @@ class DeviceEngine:
                            self.loss, self.info, self.scratch)
         self.kernel_launches += 1
         self.clock += 1
+
+    def step_group(self, g: int, num_clocks: int = 1, stream=None) -> None:
+        """Per-worker mode: enqueue `num_clocks` clocks of the workers of group g — one launch on the group's own
+        stream (``stream=False``: the current stream).  Every worker of the group runs its clocks back to back at its
+        own pace, gated against ALL workers' clock words; a (loss, clock, lag, lead) record per clock and worker is
+        kept for ``read_hist``."""
+        if self.comm_mode != native.COMM_WORKER:
+            raise native.NativeError("step_group needs async_granularity='worker' and consistency_model != 0")
+        n = int(num_clocks)
+        if not 1 <= n <= self.max_clocks_per_launch:
+            raise ValueError(f"num_clocks must be in [1, {self.max_clocks_per_launch}]")
+        if self.hist is None:
+            self.hist = torch.zeros((self.groups, self.max_clocks_per_launch, self.gsize, 4), dtype=torch.int32,
+                                    device=self.device)
+            self.hist_n = [0] * self.groups
+            if self.cfg.consistency_model > 0 and self.W > self.max_resident_workers():
+                raise native.NativeError(
+                    f"bounded delay with per-worker clocks: {self.W} workers per GPU, but only "
+                    f"{self.max_resident_workers()} worker CTAs are resident at once (they wait on each other)")
+        gs, lo = self.gsize, g * self.gsize
+        comm = self._comm(native.COMM_WORKER)
+        comm.clock, comm.num_clocks = self.group_clock[g], n
+        comm.worker_base, comm.total_workers = self.rank * self.W + lo, self.total_workers
+        comm.delay_worker, comm.delay_cycles = self.delay_worker, self.delay_cycles
+        comm.hist = self.hist[g].data_ptr()
+        st = torch.cuda.current_stream() if stream is False else (stream or self.group_streams[g]
+                                                                  or torch.cuda.current_stream())
+        native.worker_step(self.solver, comm, gs, self.impl, self.X[lo:lo + gs], self.labels[lo:lo + gs],
+                           self.win[lo:lo + gs], None, None, self.loss[lo:lo + gs], self.info[lo:lo + gs],
+                           self.scratch[lo:lo + gs], stream=st)
+        self.hist_n[g] = n
+        self.kernel_launches += 1
+        self.group_clock[g] += n
+
+    def read_hist(self, g: int = 0) -> np.ndarray:
+        """Records of group g's last launch as a structured array [num_clocks, group size] with fields loss, clock,
+        lag (clock - slowest worker's clock when the gate opened) and lead (fastest worker's clock - clock).
+        Synchronises the device."""
+        torch.cuda.synchronize(self.device)
+        raw = self.hist[g, : self.hist_n[g]].cpu().numpy()
+        return raw.view(native.CLOCK_RECORD_DTYPE).reshape(self.hist_n[g], self.gsize)
+
+    def worker_clocks(self) -> np.ndarray:
+        """This rank's copy of the per-worker clock table (clocks completed by every worker of every rank)."""
+        ptr = native.lib().psb_comm_worker_clocks(self.block, self.F, self.world)
+        return _view(ptr, self.total_workers, self.device, torch.int32).cpu().numpy()
 
     def read_loss(self) -> torch.Tensor:
         """Device -> pinned host copy of the per-worker losses of the last step (synchronises)."""
@@ -348,10 +443,20 @@ class DeviceEngine:
         if self.comm_mode == native.COMM_SEQUENTIAL:
             ptr = L.psb_comm_replica(self.block, self.F, self.world, self.clock & 1)
             return _view(ptr, self.nv, self.device).view(self.layout.device_rows, 8)
-        if self.world != 1:
-            raise NotImplementedError("gather of async shards across ranks: use weights_gathered()")
-        ptr = L.psb_comm_shard_weights(self.block, self.F, self.world)
-        return _view(ptr, self.nv, self.device).view(self.layout.device_rows, 8)
+        if self.world == 1:
+            ptr = L.psb_comm_shard_weights(self.block, self.F, self.world)
+            return _view(ptr, self.nv, self.device).view(self.layout.device_rows, 8)
+        # relaxed models on several ranks: the authoritative weights are the owners' shards — read each over its
+        # peer mapping into one local tensor (an unsynchronised snapshot, like a reply of the reference's server
+        # in these models: ServerProcessor.java:172-182 sends whatever has been applied so far)
+        out = torch.empty(self.nv, dtype=torch.float32, device=self.device)
+        slice_f = ((self.nv // 4 + self.world - 1) // self.world) * 4
+        for q in range(self.world):
+            b, e = min(q * slice_f, self.nv), min((q + 1) * slice_f, self.nv)
+            if e > b:
+                src = L.psb_comm_shard_weights(self.peers[q], self.F, self.world)
+                out[b:e].copy_(_view(src, e - b, self.device))
+        return out.view(self.layout.device_rows, 8)
 
     def worker_local_weights(self, j: int) -> torch.Tensor:
         """Weights of worker j's locally fitted model of the LAST step (pulled weights + its delta) — what the
@@ -363,11 +468,9 @@ class DeviceEngine:
 
     def reset_clock_words(self, clock: int) -> None:
         """After a resume: every version / clock word of this rank's block restarts at `clock`."""
-        words = torch.full((2 * 32,), int(clock), dtype=torch.int32, device=self.device)
-        L = native.lib()
-        st = L.psb_comm_status(self.block, self.F, self.world)
-        # layout (csrc/common.cuh): status 256 B | arrivals 256 B | tickets 256 B | version 128 B | clocks 128 B
-        _view(st + 768, 64, self.device, torch.int32).copy_(words)
+        native.check(native.lib().psb_comm_set_clocks(self.block, self.F, self.world, int(clock), native._stream()),
+                     "psb_comm_set_clocks")
+        self.group_clock = [int(clock)] * self.groups
         torch.cuda.synchronize(self.device)
 
     def check(self) -> None:
@@ -390,6 +493,85 @@ class DeviceEngine:
         torch.cuda.nvtx.range_pop()
         return float(self.metrics_host[0]), float(self.metrics_host[1])
 
+    def wait_version(self, clock: Optional[int] = None) -> None:
+        """Sequential mode, several ranks: enqueue a bounded device-side wait until every shard of `clock` (default:
+        the clock after the last step) has reached this rank's replica.  A step only waits for the weights it pulls;
+        whoever reads the replica right behind a step (evaluation, checkpoint) needs this first, because the last
+        shards are written by whichever rank arrived last."""
+        if self.comm_mode != native.COMM_SEQUENTIAL or self.world == 1:
+            return
+        native.check(native.lib().psb_comm_wait_version(self.block, self.F, self.world,
+                                                        self.clock if clock is None else int(clock), self.spin_limit,
+                                                        native._stream()), "psb_comm_wait_version")
+        self.kernel_launches += 1
+
+    def evaluate_workers(self, impl: Optional[int] = None):
+        """Weighted F1 / accuracy of every worker's locally fitted model of the LAST step (weights it pulled + its
+        delta; the worker log row, LogisticRegressionTaskSpark.java:186) — all W models in one launch, the sum formed
+        while the weights are staged.  Returns (f1[W], accuracy[W]) as numpy arrays; synchronises."""
+        nv, W = self.nv, self.W
+        if not hasattr(self, "_wconf"):
+            self._wconf = torch.zeros((W, 64), dtype=torch.int32, device=self.device)
+            self._wmetrics = torch.zeros((W, 2), dtype=torch.float32, device=self.device)
+            self._wmetrics_host = torch.zeros((W, 2), dtype=torch.float32).pin_memory()
+        delta = self.scratch[:, 5 * nv: 6 * nv]              # solver scratch vector 5 = delta (csrc/worker_common.cuh)
+        w0 = self.scratch[:, 6 * nv: 7 * nv]                 # vector 6 = the weights the step started from
+        torch.cuda.nvtx.range_push("psb.eval_workers")
+        native.evaluate_models(self.test_X, self.test_y, self.test_X.shape[0], w0, delta, self.scratch.shape[1], W,
+                               self.F, self.layout.R, self._wconf, self._wmetrics,
+                               self.impl if impl is None else impl)
+        self.kernel_launches += 2
+        self._wmetrics_host.copy_(self._wmetrics, non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+        torch.cuda.nvtx.range_pop()
+        m = self._wmetrics_host.numpy()
+        return m[:, 0].copy(), m[:, 1].copy()
+
+    # ------------------------------------------------------------------ checkpoint / resume
+    def state_dict(self) -> dict:
+        """Everything this rank needs to continue: ring contents and windows, the buffer policy state (inter-arrival
+        statistics), clocks and — for the relaxed models — this rank's authoritative shard.  Synchronises."""
+        self._wait_slot_thread()
+        torch.cuda.synchronize(self.device)
+        L = native.lib()
+        shard_f = ((self.nv // 4 + self.world - 1) // self.world) * 4
+        shard = _view(L.psb_comm_shard_weights(self.block, self.F, self.world), shard_f, self.device)
+        return {"rank": self.rank, "world": self.world, "W": self.W, "clock": self.clock,
+                "group_clock": list(self.group_clock), "rows_ingested": self.rows_ingested,
+                "X": self.X.cpu(), "labels": self.labels.cpu(), "win": self.win_host.clone(),
+                "buffers": np.stack([b.get_state() for b in self.buffers]),
+                "shard": shard.cpu(), "comm_mode": self.comm_mode,
+                "worker_clocks": torch.from_numpy(self.worker_clocks().copy())}
+
+    def load_state_dict(self, sd: dict, weights: Optional[np.ndarray] = None) -> None:
+        """Inverse of state_dict (same rank / world / W).  `weights` [(F+1), 8]: the global weights of the
+        checkpoint, written into both replicas (sequential mode); the relaxed modes restore the saved shard."""
+        if (sd["rank"], sd["world"], sd["W"]) != (self.rank, self.world, self.W):
+            raise ValueError("checkpoint was written by a different rank layout")
+        self._wait_slot_thread()
+        self.X.copy_(sd["X"]), self.labels.copy_(sd["labels"])
+        self.win_host.copy_(sd["win"]), self.win.copy_(self.win_host)
+        for b, st in zip(self.buffers, sd["buffers"]):
+            b.set_state(st)
+        self._buf_handles = None
+        self.rows_ingested = int(sd["rows_ingested"])
+        self.clock = int(sd["clock"])
+        L = native.lib()
+        if weights is not None:
+            w = torch.from_numpy(np.asarray(weights, dtype=np.float32).reshape(-1).copy()).to(self.device)
+            for parity in (0, 1):
+                _view(L.psb_comm_replica(self.block, self.F, self.world, parity), self.nv, self.device).copy_(w)
+        shard = sd["shard"].to(self.device)
+        _view(L.psb_comm_shard_weights(self.block, self.F, self.world), shard.numel(), self.device).copy_(shard)
+        self.reset_clock_words(self.clock)
+        if sd.get("group_clock") and len(sd["group_clock"]) == self.groups:
+            self.group_clock = [int(c) for c in sd["group_clock"]]
+        if self.comm_mode == native.COMM_WORKER and "worker_clocks" in sd:      # workers resume at their own clocks
+            tab = sd["worker_clocks"].to(torch.int32).to(self.device)
+            _view(L.psb_comm_worker_clocks(self.block, self.F, self.world), tab.numel(), self.device,
+                  torch.int32).copy_(tab)
+        torch.cuda.synchronize(self.device)
+
     def close(self) -> None:
         if self._slot_thread is not None:
             self._wait_slot_thread()
@@ -400,7 +582,8 @@ class DeviceEngine:
             for q, p in enumerate(self.peers):
                 if q != self.rank and p and p != self.block and self._imported:
                     native.lib().psb_ipc_close(p)
-            native.device_free(self.block)
+            if self.owns_block:
+                native.device_free(self.block)
             self.block = 0
 
     _imported = False
@@ -419,8 +602,10 @@ def _view(ptr: int, n: int, device, dtype=torch.float32) -> torch.Tensor:
 class VirtualCluster:
     """N ranks on ONE device, stepped in clock order (tests / single-GPU emulation of the protocol)."""
 
-    def __init__(self, cfg: PSConfig, num_ranks: int, workers_per_rank: int, impl: int = native.IMPL_SIMT, w0=None):
-        self.engines = [DeviceEngine(cfg, workers_per_rank, r, num_ranks, impl, w0=w0) for r in range(num_ranks)]
+    def __init__(self, cfg: PSConfig, num_ranks: int, workers_per_rank: int, impl: int = native.IMPL_SIMT, w0=None,
+                 **engine_kw):
+        self.engines = [DeviceEngine(cfg, workers_per_rank, r, num_ranks, impl, w0=w0, **engine_kw)
+                        for r in range(num_ranks)]
         peers = [e.block for e in self.engines]
         for e in self.engines:
             e.set_peers(peers)
@@ -428,6 +613,22 @@ class VirtualCluster:
     def step(self) -> None:
         for e in self.engines:
             e.step()
+
+    def step_concurrent(self, num_clocks: int = 1) -> None:
+        """Per-worker mode: every virtual rank's launch on its own stream, so that the kernels are on the device
+        together and really wait on each other's clock words (all worker CTAs must fit on the GPU at once)."""
+        if not hasattr(self, "_streams"):
+            self._streams = [[torch.cuda.Stream() for _ in range(e.groups)] for e in self.engines]
+        cur = torch.cuda.current_stream()
+        for e, sts in zip(self.engines, self._streams):
+            for g, st in enumerate(sts):
+                st.wait_stream(cur)
+                e.step_group(g, num_clocks, stream=st)
+        for sts in self._streams:
+            for st in sts:
+                cur.wait_stream(st)
+        for e in self.engines:
+            e.clock = min(e.group_clock)
 
     def close(self) -> None:
         for e in self.engines:

@@ -22,7 +22,8 @@ MAX_RANKS = 8
 HIST = 4
 SCRATCH_VECS = 7 + 2 * HIST
 SOLVER_LBFGS, SOLVER_SGD = 0, 1
-COMM_NONE, COMM_SEQUENTIAL, COMM_ASYNC = 0, 1, 2
+COMM_NONE, COMM_SEQUENTIAL, COMM_ASYNC, COMM_WORKER = 0, 1, 2, 3
+MAX_WORKERS = 4096
 IMPL_SIMT, IMPL_TC = 0, 1
 
 
@@ -50,7 +51,18 @@ class PsbSlabComm(C.Structure):
 class PsbComm(C.Structure):
     _fields_ = [("mode", C.c_int), ("rank", C.c_int), ("num_ranks", C.c_int), ("workers_per_rank", C.c_int),
                 ("clock", C.c_int), ("max_delay", C.c_int), ("lr", C.c_float), ("spin_limit", C.c_ulonglong),
-                ("peers", C.c_void_p * MAX_RANKS)]
+                ("peers", C.c_void_p * MAX_RANKS),
+                # PSB_COMM_WORKER only (zero otherwise)
+                ("num_clocks", C.c_int), ("worker_base", C.c_int), ("total_workers", C.c_int),
+                ("delay_worker", C.c_int), ("delay_cycles", C.c_ulonglong), ("hist", C.c_void_p),
+                ("home_remote", C.c_int)]
+
+
+class PsbClockRecord(C.Structure):
+    _fields_ = [("loss", C.c_float), ("clock", C.c_int), ("lag", C.c_int), ("lead", C.c_int)]
+
+
+CLOCK_RECORD_DTYPE = np.dtype([("loss", "<f4"), ("clock", "<i4"), ("lag", "<i4"), ("lead", "<i4")])
 
 
 _lib: Optional[C.CDLL] = None
@@ -76,9 +88,12 @@ def lib() -> C.CDLL:
     for name in ("psb_comm_replica",):
         getattr(L, name).restype = C.c_void_p
         getattr(L, name).argtypes = [vp, C.c_int, C.c_int, C.c_int]
-    for name in ("psb_comm_shard_weights", "psb_comm_status"):
+    for name in ("psb_comm_shard_weights", "psb_comm_status", "psb_comm_version_words", "psb_comm_rank_clocks",
+                 "psb_comm_worker_clocks"):
         getattr(L, name).restype = C.c_void_p
         getattr(L, name).argtypes = [vp, C.c_int, C.c_int]
+    L.psb_comm_set_clocks.argtypes = [vp, C.c_int, C.c_int, C.c_uint, vp]
+    L.psb_worker_max_resident.argtypes = [C.POINTER(PsbSolver), C.c_int, C.c_int]
     L.psb_comm_check.argtypes = [vp, C.c_int, C.c_int, vp]
     L.psb_worker_scratch_bytes.restype = C.c_size_t
     L.psb_worker_scratch_bytes.argtypes = [C.c_int]
@@ -120,6 +135,10 @@ def lib() -> C.CDLL:
     L.psb_buffer_inserted.restype = C.c_longlong
     L.psb_buffer_inserted.argtypes = [vp]
     L.psb_buffers_on_batch.argtypes = [vp, C.c_int, vp, vp, C.c_int, vp, vp]
+    L.psb_buffer_get_state.argtypes = [vp, vp, C.c_int]
+    L.psb_buffer_set_state.argtypes = [vp, vp, C.c_int]
+    L.psb_comm_wait_version.argtypes = [vp, C.c_int, C.c_int, C.c_uint, C.c_ulonglong, vp]
+    L.psb_eval_models.argtypes = [vp, ip, C.c_int, fp, fp, C.c_size_t, C.c_int, C.c_int, C.c_int, ip, fp, C.c_int, vp]
     L.psb_producer_start.restype = C.c_void_p
     L.psb_producer_start.argtypes = [C.c_char_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
                                      vp, vp, vp, vp, C.c_int]
@@ -318,6 +337,7 @@ class NativeBuffer:
         self.h = lib().psb_buffer_create(min_size, max_size, bc, window)
         if not self.h:
             raise NativeError("psb_buffer_create failed")
+        self.window = window if window > 0 else 500
         self.head = self.count = self.target = 0
 
     def ring_total(self) -> int:
@@ -329,6 +349,19 @@ class NativeBuffer:
         slot = lib().psb_buffer_on_event(self.h, float(now_ms), C.byref(h), C.byref(c), C.byref(t))
         self.head, self.count, self.target = h.value, c.value, t.value
         return slot
+
+    def get_state(self) -> np.ndarray:
+        """Policy state (inter-arrival window + ring cursors) as a float64 vector, for checkpoints."""
+        out = np.zeros(9 + self.window, dtype=np.float64)
+        n = lib().psb_buffer_get_state(self.h, out.ctypes.data, len(out))
+        if n != len(out):
+            raise NativeError("psb_buffer_get_state failed")
+        return out
+
+    def set_state(self, state: np.ndarray) -> None:
+        state = np.ascontiguousarray(state, dtype=np.float64)
+        check(lib().psb_buffer_set_state(self.h, state.ctypes.data, len(state)), "psb_buffer_set_state")
+        self.head, self.count = int(state[6]), int(state[7])
 
     def __del__(self):
         if getattr(self, "h", None) and _lib is not None:
@@ -456,6 +489,13 @@ def apply_delta(w, delta, lr: float, num_features: int, skip_class: int = -1, st
 def evaluate(X, labels, n: int, w, num_features: int, num_class_rows: int, conf, out, impl: int = 0, stream=None):
     check(lib().psb_eval(_ptr(X), _ptr(labels), n, _ptr(w), num_features, num_class_rows, _ptr(conf), _ptr(out), impl,
                          _stream(stream)), "psb_eval")
+
+
+def evaluate_models(X, labels, n: int, w, w_add, model_stride: int, num_models: int, num_features: int,
+                    num_class_rows: int, conf, out, impl: int = 0, stream=None):
+    """Weighted F1 / accuracy of `num_models` weight sets in one launch (conf int32[M, 64], out float32[M, 2])."""
+    check(lib().psb_eval_models(_ptr(X), _ptr(labels), n, _ptr(w), _ptr(w_add), model_stride, num_models, num_features,
+                                num_class_rows, _ptr(conf), _ptr(out), impl, _stream(stream)), "psb_eval_models")
 
 
 def ring_scatter(stage, n: int, stride_words: int, X, labels, cap: int, num_features: int, stream=None) -> None:

@@ -12,7 +12,7 @@ plus STOP.
 The exchange is a lock-step pair of broadcasts (server batch out, worker batch
 back), which cannot deadlock the way two blocking point-to-point sends can.
 On a GPU box this link is only the control plane of CLI-parity runs; the
-throughput path never leaves the device (``psb200.parallel.p2p``).
+throughput path never leaves the device (``psb200.engine.device_engine``, ``csrc/comm.cuh``).
 """
 from __future__ import annotations
 
