@@ -363,6 +363,7 @@ struct Producer {
     std::atomic<int> eof{0}, stop{0};
     std::thread th;
     int read_cursor = 0;                      // consumer side: next batch to poll
+    int held = 0;                             // consumer side: batches polled and not yet released
     Producer(int nb) : ready(nb) {
         for (auto& r : ready) r.store(-1);
     }
@@ -515,23 +516,29 @@ static void* producer_start_impl(const char* path, int has_header, int num_worke
     P->th = std::thread(producer_main, P);
     return P;
 }
-// 1: *batch holds *n rows (release it after the copy); 0: nothing ready.  *eof: 1 when the file is done
-// AND every batch was consumed ("CSV Producer sent all records!"), 2 when the file could not be opened.
+// 1: *batch holds *n rows and now belongs to the caller until it is released (several batches may be held at
+// once, e.g. while their host->device copies are in flight; release them in the order they were polled).
+// 0: nothing ready.  *eof: 1 when the file is done AND every batch was polled ("CSV Producer sent all
+// records!"), 2 when the file could not be opened.
 extern "C" int psb_producer_poll(void* h, int* batch, int* n, int* eof) {
     Producer* P = (Producer*)h;
-    const int r = P->ready[P->read_cursor].load(std::memory_order_acquire);
-    if (r >= 0) {
-        *batch = P->read_cursor, *n = r, *eof = 0;
-        return 1;
+    if (P->held < P->num_batches) {
+        const int r = P->ready[P->read_cursor].load(std::memory_order_acquire);
+        if (r >= 0) {
+            *batch = P->read_cursor, *n = r, *eof = 0;
+            P->read_cursor = (P->read_cursor + 1) % P->num_batches;
+            ++P->held;
+            return 1;
+        }
     }
     const int e = P->eof.load();
-    *eof = (e && P->ready[P->read_cursor].load(std::memory_order_acquire) < 0) ? e : 0;
+    *eof = (e && P->held < P->num_batches && P->ready[P->read_cursor].load(std::memory_order_acquire) < 0) ? e : 0;
     return 0;
 }
 extern "C" void psb_producer_release(void* h, int batch) {
     Producer* P = (Producer*)h;
     P->ready[batch].store(-1, std::memory_order_release);
-    P->read_cursor = (batch + 1) % P->num_batches;
+    if (P->held > 0) --P->held;
 }
 extern "C" long long psb_producer_rows_sent(void* h) { return ((Producer*)h)->rows_sent.load(); }
 extern "C" void psb_producer_stop(void* h) {

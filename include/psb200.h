@@ -287,7 +287,8 @@ int psb_buffers_on_batch(void** buffers, int num_buffers, const int* workers, co
  * keeps the rows of partitions [worker_begin, worker_begin + worker_count), converts them to dense fp16
  * and fills a ring of `num_batches` caller-provided PINNED batches (h_rows_f16[num_batches][batch_rows][F],
  * h_labels / h_workers / h_times [num_batches][batch_rows]); -p pacing as in the reference.
- * poll: 1 = batch ready (*batch, *n), 0 = nothing; *eof = 1 once the file is exhausted and drained. */
+ * poll: 1 = batch ready (*batch, *n) and handed to the caller until psb_producer_release (several may be held,
+ * released in poll order), 0 = nothing; *eof = 1 once the file is exhausted and every batch was polled. */
 void* psb_producer_start(const char* path, int has_header, int num_workers_total, int worker_begin,
                          int worker_count, int num_features, int p_ms, int batch_rows, int num_batches,
                          void* h_rows_f16, int* h_labels, int* h_workers, double* h_times, int flush_ms);

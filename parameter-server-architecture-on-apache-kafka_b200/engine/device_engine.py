@@ -313,6 +313,9 @@ class DeviceEngine:
         torch.cuda.nvtx.range_push("psb.ingest_commit")
         self.stage_future[j].result()                       # slot tables of this batch are written (helper thread)
         s.wait_stream(torch.cuda.current_stream())          # the previous step must be done with the rings
+        for gs in self.group_streams:                       # ... on whichever stream its groups ran
+            if gs is not None:
+                s.wait_stream(gs)
         s.wait_event(self.h2d_done[j])
         tables = [(self.win, self.stage_win_host[j], self.W * 8)]
         if self.stage_kind[j] != "csr":
@@ -394,6 +397,8 @@ class DeviceEngine:
         comm.hist = self.hist[g].data_ptr()
         st = torch.cuda.current_stream() if stream is False else (stream or self.group_streams[g]
                                                                   or torch.cuda.current_stream())
+        if st != torch.cuda.current_stream():
+            st.wait_stream(torch.cuda.current_stream())     # fills / ring stores ordered on the caller's stream
         native.worker_step(self.solver, comm, gs, self.impl, self.X[lo:lo + gs], self.labels[lo:lo + gs],
                            self.win[lo:lo + gs], None, None, self.loss[lo:lo + gs], self.info[lo:lo + gs],
                            self.scratch[lo:lo + gs], stream=st)

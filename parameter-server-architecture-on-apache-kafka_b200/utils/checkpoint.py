@@ -5,7 +5,10 @@ The reference keeps server weights and the message tracker only in JVM memory
 asserts.  Here a checkpoint is the weights in the reference key layout
 (``weights-<clock>.csv``: ``key;value`` rows, keys as in
 ``LogisticRegressionTaskSpark.java:98-140``) plus a small JSON with the clocks and the
-ingestion cursors; ``load`` restores both.
+ingestion cursors; ``load`` restores both.  Every rank additionally writes ``rank-<r>.pt``
+(``save_rank_state``): its input rings and windows, the buffer policy state (inter-arrival
+statistics), its clocks and, for the relaxed consistency models, its authoritative shard — so a
+resumed run trains on the same buffers instead of refilling empty rings.
 """
 from __future__ import annotations
 
@@ -45,3 +48,22 @@ def load(directory: str, layout: LogRegLayout) -> Tuple[np.ndarray, Dict]:
         raise ValueError("checkpoint was written for a different model shape")
     keys = np.loadtxt(os.path.join(directory, meta["weights"]), delimiter=";", skiprows=1, dtype=np.float64)[:, 1]
     return layout.keys_to_device(keys.astype(np.float32)), meta
+
+
+def save_rank_state(directory: str, rank: int, state: Dict) -> str:
+    """Atomically writes one rank's engine state (``DeviceEngine.state_dict()``)."""
+    import torch
+    os.makedirs(directory, exist_ok=True)
+    path = os.path.join(directory, f"rank-{rank}.pt")
+    torch.save(state, path + ".tmp")
+    os.replace(path + ".tmp", path)
+    return path
+
+
+def load_rank_state(directory: str, rank: int) -> Optional[Dict]:
+    """The rank's saved engine state, or None when the checkpoint holds weights only."""
+    import torch
+    path = os.path.join(directory, f"rank-{rank}.pt")
+    if not os.path.exists(path):
+        return None
+    return torch.load(path, map_location="cpu", weights_only=False)
