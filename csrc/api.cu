@@ -45,6 +45,7 @@ __global__ void psb_comm_init_kernel(CommBlock blk, const float4* __restrict__ w
         const float4 v = w0[i];
         blk.rep(0)[i] = v;
         blk.rep(1)[i] = v;
+        blk.pub()[i] = v;
         const int b = L.slice_begin(rank), e = L.slice_end(rank);
         if (i >= b && i < e) blk.auth()[i - b] = v;
     }
@@ -82,9 +83,17 @@ unsigned int* psb_comm_worker_clocks(void* d_block, int num_features, int num_ra
     return CommBlock(d_block, CommLayout::make(num_features, num_ranks)).wclocks();
 }
 
+float* psb_comm_published(void* d_block, int num_features, int num_ranks) {
+    return (float*)CommBlock(d_block, CommLayout::make(num_features, num_ranks)).pub();
+}
+unsigned int* psb_comm_published_seq(void* d_block, int num_features, int num_ranks) {
+    return CommBlock(d_block, CommLayout::make(num_features, num_ranks)).pub_seq();
+}
+
 __global__ void psb_comm_set_clocks_kernel(CommBlock blk, unsigned int clock) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i < PSB_MAX_RANKS) blk.version()[i] = clock, blk.clocks()[i] = clock;
+    if (i == 0) *blk.pub_seq() = 2u * clock;
     if (i < PSB_MAX_WORKERS) blk.wclocks()[i] = clock;
 }
 int psb_comm_set_clocks(void* d_block, int num_features, int num_ranks, unsigned int clock, void* stream) {
@@ -160,6 +169,8 @@ int psb_worker_step(const PsbSolver* s, const PsbComm* comm, int num_workers, in
         } else {
             PSB_REQUIRE(comm->workers_per_rank == num_workers, "workers_per_rank must equal num_workers");
             PSB_REQUIRE(comm->num_clocks <= 1, "several clocks per launch need comm mode PSB_COMM_WORKER");
+            PSB_REQUIRE(!comm->publish || (comm->mode == PSB_COMM_SEQUENTIAL && comm->num_ranks == 1),
+                        "the published snapshot is kept in sequential mode on one rank only");
         }
     }
     if (comm->mode == PSB_COMM_WORKER && comm->max_delay >= 0) {
@@ -265,6 +276,20 @@ int psb_h2d_copies(int n, void* const* d_dst, const void* const* h_src, const si
         PSB_REQUIRE(d_dst[i] && h_src[i], "psb_h2d_copies: null pointer in entry %d", i);
         PSB_CHECK_CUDA(cudaMemcpyAsync(d_dst[i], h_src[i], bytes[i], cudaMemcpyHostToDevice, (cudaStream_t)stream));
     }
+    return 0;
+}
+
+// One device -> host copy on `stream` (pinned destination for an asynchronous copy): control words and batch
+// headers of the two-process transport.
+int psb_d2h_copy(void* h_dst, const void* d_src, size_t bytes, void* stream) {
+    PSB_REQUIRE(h_dst && d_src, "psb_d2h_copy: null pointer");
+    PSB_CHECK_CUDA(cudaMemcpyAsync(h_dst, d_src, bytes, cudaMemcpyDeviceToHost, (cudaStream_t)stream));
+    return 0;
+}
+// device -> device copy on `stream` (snapshots of weights that live in another process' block)
+int psb_d2d_copy(void* d_dst, const void* d_src, size_t bytes, void* stream) {
+    PSB_REQUIRE(d_dst && d_src, "psb_d2d_copy: null pointer");
+    PSB_CHECK_CUDA(cudaMemcpyAsync(d_dst, d_src, bytes, cudaMemcpyDeviceToDevice, (cudaStream_t)stream));
     return 0;
 }
 

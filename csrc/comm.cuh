@@ -198,6 +198,12 @@ __device__ __forceinline__ void comm_push(const CommCtx& cx, int clock, int gw, 
         //    One flat loop over all parameters so that every thread has its N remote inbox loads of several
         //    elements in flight at once (one NVLink round trip for the whole apply, not one per shard).
         const float4* w_old = me.rep(p);
+        const bool publish = c.publish && c.num_ranks == 1;      // seqlock: odd while the snapshot is being written
+        if (publish) {
+            if (threadIdx.x == 0) st_relaxed_sys(me.pub_seq(), 2u * (unsigned)clock + 1u);
+            fence_acq_rel_sys();
+            __syncthreads();
+        }
         for (int i = threadIdx.x; i < L.n4; i += blockDim.x) {
             const int s = i / L.slice4;
             if (!(mask & (1u << s))) continue;
@@ -216,9 +222,11 @@ __device__ __forceinline__ void comm_push(const CommCtx& cx, int clock, int gw, 
 #pragma unroll
             for (int q = 0; q < PSB_MAX_RANKS; ++q)
                 if (q < c.num_ranks) st_cg_v4(CommBlock(c.peers[q], L).rep(p ^ 1) + i, nw);
+            if (publish) st_cg_v4(me.pub() + i, nw);
         }
         fence_acq_rel_sys();
         __syncthreads();
+        if (publish && threadIdx.x == 0) st_release_sys(me.pub_seq(), 2u * (unsigned)clock + 2u);
         if (threadIdx.x < c.num_ranks && (mask & (1u << threadIdx.x))) {
             const int s = threadIdx.x;
             st_relaxed_sys(CommBlock(c.peers[s], L).arrivals(p), 0u);

@@ -35,7 +35,7 @@ struct CommLayout {
     int num_ranks;
     // byte offsets
     size_t off_status, off_arrivals, off_ticket, off_version, off_clocks;
-    size_t off_rep, off_auth, off_acc, off_inbox, off_wclocks, bytes;
+    size_t off_rep, off_auth, off_acc, off_inbox, off_wclocks, off_pub, bytes;
 
     __host__ __device__ static CommLayout make(int num_features, int num_ranks) {
         CommLayout L;
@@ -55,6 +55,7 @@ struct CommLayout {
         L.off_inbox = o;    o += (size_t)2 * num_ranks * L.slice4 * 16;
         o = (o + 127) & ~(size_t)127;
         L.off_wclocks = o;  o += (size_t)PSB_MAX_WORKERS * 4;  // uint32[PSB_MAX_WORKERS]: per-worker clocks
+        L.off_pub = o;      o += (size_t)L.nv * 4;             // published snapshot (seqlock word: status()[8])
         L.bytes = (o + 255) & ~(size_t)255;
         return L;
     }
@@ -72,6 +73,8 @@ struct CommBlock {
     __host__ __device__ unsigned int* version() const { return (unsigned int*)(base + L.off_version); }
     __host__ __device__ unsigned int* clocks() const { return (unsigned int*)(base + L.off_clocks); }
     __host__ __device__ unsigned int* wclocks() const { return (unsigned int*)(base + L.off_wclocks); }
+    __host__ __device__ float4* pub() const { return (float4*)(base + L.off_pub); }
+    __host__ __device__ unsigned int* pub_seq() const { return status() + 8; }
     __host__ __device__ float4* rep(int parity) const { return (float4*)(base + L.off_rep) + (size_t)parity * L.n4; }
     __host__ __device__ float4* auth() const { return (float4*)(base + L.off_auth); }
     __host__ __device__ float4* acc(int parity) const { return (float4*)(base + L.off_acc) + (size_t)parity * L.n4; }

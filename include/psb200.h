@@ -85,6 +85,10 @@ typedef struct PsbComm {
     void* hist;                    /* optional PsbClockRecord[num_clocks][num_workers] of this launch (device) */
     int home_remote;               /* peers[rank] lives on another GPU (server process' block): the intra-rank
                                       reduction and ticket then use system-scope operations                   */
+    int publish;                   /* sequential mode, one rank: the applier also writes the new weights into the
+                                      block's published snapshot under a seqlock word (2v+1 while clock v's weights
+                                      are being written, 2v+2 once complete) — what a server process that does
+                                      not take part in the clocks reads (psb_comm_published)                  */
 } PsbComm;
 
 /* What a worker saw when it started clock `clock`: lag = clock - min over all workers' clocks at the moment the
@@ -104,6 +108,9 @@ unsigned int* psb_comm_status(void* d_block, int num_features, int num_ranks);  
 unsigned int* psb_comm_version_words(void* d_block, int num_features, int num_ranks);   /* [PSB_MAX_RANKS] */
 unsigned int* psb_comm_rank_clocks(void* d_block, int num_features, int num_ranks);     /* [PSB_MAX_RANKS] */
 unsigned int* psb_comm_worker_clocks(void* d_block, int num_features, int num_ranks);   /* [PSB_MAX_WORKERS] */
+/* published snapshot ([(F+1)*8] floats) and its seqlock word (see PsbComm.publish) */
+float* psb_comm_published(void* d_block, int num_features, int num_ranks);
+unsigned int* psb_comm_published_seq(void* d_block, int num_features, int num_ranks);
 /* after a resume: every version / rank-clock / worker-clock word of the block restarts at `clock` */
 int psb_comm_set_clocks(void* d_block, int num_features, int num_ranks, unsigned int clock, void* stream);
 
@@ -243,6 +250,10 @@ int psb_ring_store_palette(const uint32_t* d_bitmap, const int* d_row_off, const
 
 /* n host -> device copies on `stream` with one call (pinned sources for asynchronous copies) */
 int psb_h2d_copies(int n, void* const* d_dst, const void* const* h_src, const size_t* bytes, void* stream);
+
+/* single device -> host / device -> device copies on `stream` (control words, weight snapshots) */
+int psb_d2h_copy(void* h_dst, const void* d_src, size_t bytes, void* stream);
+int psb_d2d_copy(void* d_dst, const void* d_src, size_t bytes, void* stream);
 
 /* ---------------------------------------------------------------- host runtime (C++) */
 /* Dense fp16 rows -> presence bitmap + per-row palette (the <= 16 distinct fp16 values of the row) + one 4-bit

@@ -44,8 +44,12 @@ class BaseApp:
     def run(self) -> None:
         raise NotImplementedError
 
+    on_close = None                               # hook of the running transport (p2p: raise its stop flag)
+
     def close(self) -> None:
         self._closing = True
+        if self.on_close is not None:
+            self.on_close()
 
     def call(self) -> None:
         def _hook(signum, frame):

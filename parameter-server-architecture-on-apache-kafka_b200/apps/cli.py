@@ -15,6 +15,7 @@ import argparse
 import sys
 from typing import List, Optional
 
+from ..parallel import RUNNER_TRANSPORTS
 from ..config import (NUM_CLASSES_DEFAULT, NUM_FEATURES_DEFAULT, NUM_WORKERS_DEFAULT, PSConfig,
                       TEST_DATA_FILE_PATH_DEFAULT, TRAINING_DATA_FILE_PATH_DEFAULT)
 
@@ -41,7 +42,15 @@ def _common(p: argparse.ArgumentParser) -> None:
     p.add_argument("--seed", type=int, default=0)
     p.add_argument("--backend", choices=["numpy", "cuda"], default="numpy",
                    help="math backend: CPU oracle or sm_100a kernels")
-    p.add_argument("--transport", choices=["loopback", "p2p", "nccl"], default="loopback")
+    p.add_argument("--transport", choices=list(RUNNER_TRANSPORTS), default="auto",
+                   help="p2p: device peer-memory mailboxes between the two apps (default of --backend cuda); "
+                        "loopback: host event loop (default of --backend numpy)")
+    p.add_argument("--device", type=int, default=0, help="CUDA device of this app (p2p transport)")
+    p.add_argument("--impl", choices=["tc", "simt"], default="tc", help="worker kernel flavour (p2p transport)")
+    p.add_argument("--clocks_per_launch", type=int, default=1,
+                   help="relaxed consistency models, p2p transport: clocks every worker runs per launch at its own pace")
+    p.add_argument("--no_worker_metrics", action="store_true",
+                   help="p2p transport: leave F1 / accuracy of the worker rows at -1 instead of scoring every local model")
     p.add_argument("--rendezvous", default=None, help="override the rendezvous address host:port")
     p.add_argument("--no_standardize", action="store_true")
     p.add_argument("--compat_q1", action="store_true", help="replicate the reference's off-by-one on key 6149")
@@ -60,6 +69,9 @@ def server_parser() -> argparse.ArgumentParser:
     _common(p)
     p.add_argument("--in_process", action="store_true", help="host the workers in this process (no WorkerAppRunner)")
     p.add_argument("--max_clock", type=int, default=-1, help="stop after this many server clocks")
+    p.add_argument("--free_running", action="store_true",
+                   help="p2p transport: workers do not wait for the server's log row of a clock before the next one "
+                        "(the server then logs the clocks it gets to see)")
     p.add_argument("--start_delay_ms", type=float, default=0.0,
                    help="delay before the training loop starts (reference: 20000)")
     p.add_argument("--virtual_clock", action="store_true", help="deterministic virtual time instead of wall clock")
@@ -104,4 +116,8 @@ def parse(parser: argparse.ArgumentParser, argv: Optional[List[str]]):
     if ns.help:
         parser.print_help(sys.stdout)
         raise SystemExit(0)
+    if getattr(ns, "transport", None) == "auto":
+        ns.transport = "p2p" if getattr(ns, "backend", "numpy") == "cuda" else "loopback"
+    if getattr(ns, "transport", None) == "p2p" and getattr(ns, "backend", "cuda") != "cuda":
+        parser.error("--transport p2p needs --backend cuda")
     return ns

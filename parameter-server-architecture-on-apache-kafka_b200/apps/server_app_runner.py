@@ -40,7 +40,7 @@ def main(argv: Optional[List[str]] = None) -> int:
         import psb200.config as c
         c.RENDEZVOUS_LOCAL = c.RENDEZVOUS_REMOTE = ns.rendezvous
     app = ServerApp(cfg, in_process=ns.in_process, backend=ns.backend, server_log=server_log,
-                    worker_log=worker_log, virtual=ns.virtual_clock, start_delay_ms=ns.start_delay_ms)
+                    worker_log=worker_log, virtual=ns.virtual_clock, start_delay_ms=ns.start_delay_ms, ns=ns)
     app.call()
     server_log.close()
     if worker_log is not None:

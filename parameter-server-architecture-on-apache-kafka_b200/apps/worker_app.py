@@ -24,12 +24,17 @@ from .server_app import make_backend
 class WorkerApp(BaseApp):
     application_id = "parameter-server-worker"        # WorkerApp.java:46-48
 
-    def __init__(self, cfg: PSConfig, backend: str = "numpy", worker_log: Optional[LogSink] = None):
+    def __init__(self, cfg: PSConfig, backend: str = "numpy", worker_log: Optional[LogSink] = None, ns=None):
         super().__init__(cfg)
         self.backend_name = backend
         self.worker_log = worker_log or LogSink()
+        self.ns = ns
 
     def run(self) -> None:
+        if self.cfg.transport == "p2p":               # product path (psb200.apps.p2p_apps.P2PWorker)
+            from .p2p_apps import run_worker
+            run_worker(self, self.cfg, self.ns, self.worker_log)
+            return
         from ..parallel.link import GRADIENT, ROW, STOP, WEIGHTS, WORKER_RANK, WorkerLink, init_link
         cfg = self.cfg
         test = load_csv_or_synthetic(cfg.test_data_file_path, cfg, "test")

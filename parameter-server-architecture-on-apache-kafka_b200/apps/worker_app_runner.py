@@ -36,7 +36,7 @@ def main(argv: Optional[List[str]] = None) -> int:
     if ns.rendezvous:
         import psb200.config as c
         c.RENDEZVOUS_LOCAL = c.RENDEZVOUS_REMOTE = ns.rendezvous
-    app = WorkerApp(cfg, backend=ns.backend, worker_log=worker_log)
+    app = WorkerApp(cfg, backend=ns.backend, worker_log=worker_log, ns=ns)
     app.call()
     worker_log.close()
     return 0

@@ -64,7 +64,7 @@ class PSConfig:
     compat_q1: bool = False            # replicate the off-by-one on key 6149
     init: str = "zero"                 # reference zero-inits despite the method name (Q3)
     seed: int = 0
-    transport: str = "loopback"        # loopback | p2p | nccl
+    transport: str = "loopback"        # loopback (host event loop) | p2p (device peer memory)
     remote: bool = False
     verbose: bool = False
     logging: bool = False

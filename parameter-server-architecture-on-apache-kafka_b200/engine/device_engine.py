@@ -97,6 +97,7 @@ class DeviceEngine:
         self.group_streams = [torch.cuda.Stream(device=dev) for _ in range(groups)] if groups > 1 else [None]
         self.hist = None
         self.delay_worker, self.delay_cycles = -1, 0
+        self.publish = False                  # sequential, one rank: keep the block's published snapshot current
         # ingestion: host-side window bookkeeping + a ring of staging sets.  begin() fills set `head` over the
         # copy stream, commit() drains set `tail` into the rings over the ingest stream; with S sets the H2D of
         # batch k+S-1 overlaps the step that trains on batch k.
@@ -157,6 +158,7 @@ class DeviceEngine:
         cm = self.cfg.consistency_model
         c.max_delay = cm if cm > 0 else -1
         c.home_remote = int(self.home_remote)
+        c.publish = int(self.publish and mode == native.COMM_SEQUENTIAL and self.world == 1)
         c.delay_worker = -1
         for q in range(self.world):
             c.peers[q] = self.peers[q]
@@ -302,6 +304,35 @@ class DeviceEngine:
         self.h2d_done[j].record(s)
         self._end_set(j, n, ("palette" if rows_f16.palette else "bitmap") if packed else "dense",
                       nbytes + n * 8 + self.W * 8)
+
+    def ingest_from_device(self, n: int, workers: np.ndarray, now_ms: Optional[np.ndarray], bitmap: int, row_off: int,
+                           payload: int, labels: int, wait: bool = True):
+        """ingest() for a palette-packed batch that ALREADY sits in device memory (raw device addresses; e.g. a slot
+        of the INPUT_DATA topic written by the server process, ``psb200.parallel.p2p``): slot assignment on the host,
+        one copy of the (worker, slot) table, one store kernel that reads the batch in place.  Returns the ingestion
+        stream so that the caller can order its 'slot consumed' signal behind the store."""
+        if self.stage_pending:
+            raise native.NativeError("ingest_from_device: commit the begun batches first")
+        j = self._begin_set(n, workers, now_ms, sync=True)
+        s = self.ingest_stream
+        s.wait_stream(torch.cuda.current_stream())
+        for gs in self.group_streams:
+            if gs is not None:
+                s.wait_stream(gs)
+        native.h2d_copies([(self.win, self.stage_win_host[j], self.W * 8),
+                           (self.stage_ws_dev[j], self.stage_ws_host[j], n * 8)], stream=s)
+        native.ring_store_palette(int(bitmap), int(row_off), int(payload), int(labels), self.stage_ws_dev[j], n, self.X,
+                                  self.labels, self.cap, self.F, stream=s)
+        self.store_done[j].record(s)
+        self.ingest_done.record(s)
+        self.kernel_launches += 1
+        self.stage_head = (j + 1) % self.stage_sets
+        self.stage_tail = self.stage_head
+        self.rows_ingested += n
+        self.h2d_bytes += n * 8 + self.W * 8
+        if wait:
+            torch.cuda.current_stream().wait_event(self.ingest_done)
+        return s
 
     def ingest_commit(self, wait: bool = True) -> None:
         """Second half: store the oldest begun batch into the rings (after the running step, before the next)."""

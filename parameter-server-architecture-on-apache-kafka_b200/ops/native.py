@@ -55,7 +55,7 @@ class PsbComm(C.Structure):
                 # PSB_COMM_WORKER only (zero otherwise)
                 ("num_clocks", C.c_int), ("worker_base", C.c_int), ("total_workers", C.c_int),
                 ("delay_worker", C.c_int), ("delay_cycles", C.c_ulonglong), ("hist", C.c_void_p),
-                ("home_remote", C.c_int)]
+                ("home_remote", C.c_int), ("publish", C.c_int)]
 
 
 class PsbClockRecord(C.Structure):
@@ -89,7 +89,7 @@ def lib() -> C.CDLL:
         getattr(L, name).restype = C.c_void_p
         getattr(L, name).argtypes = [vp, C.c_int, C.c_int, C.c_int]
     for name in ("psb_comm_shard_weights", "psb_comm_status", "psb_comm_version_words", "psb_comm_rank_clocks",
-                 "psb_comm_worker_clocks"):
+                 "psb_comm_worker_clocks", "psb_comm_published", "psb_comm_published_seq"):
         getattr(L, name).restype = C.c_void_p
         getattr(L, name).argtypes = [vp, C.c_int, C.c_int]
     L.psb_comm_set_clocks.argtypes = [vp, C.c_int, C.c_int, C.c_uint, vp]
@@ -119,6 +119,8 @@ def lib() -> C.CDLL:
     L.psb_pack_bitmap_dense.restype = C.c_longlong
     L.psb_pack_bitmap_dense.argtypes = [vp, C.c_longlong, C.c_int, vp, vp, vp]
     L.psb_h2d_copies.argtypes = [C.c_int, vp, vp, vp, vp]
+    L.psb_d2h_copy.argtypes = [vp, vp, C.c_size_t, vp]
+    L.psb_d2d_copy.argtypes = [vp, vp, C.c_size_t, vp]
     L.psb_pack_palette_dense.restype = C.c_longlong
     L.psb_pack_palette_dense.argtypes = [vp, C.c_longlong, C.c_int, vp, vp, vp, C.c_longlong]
     L.psb_ring_store_palette.argtypes = [vp, ip, vp, ip, ip, C.c_int, vp, ip, C.c_int, C.c_int, vp]
@@ -169,6 +171,8 @@ def _ptr(t) -> int:
     """Device/host pointer of a torch tensor or numpy array (None -> NULL)."""
     if t is None:
         return None
+    if isinstance(t, int):                      # raw device address (memory mapped from another process)
+        return t
     if isinstance(t, np.ndarray):
         return t.ctypes.data
     return t.data_ptr()

@@ -1,29 +1,14 @@
 """Transports.  The reference has exactly one (Kafka producers built by ``ProducerBuilder.build``,
-``ProducerBuilder.java:15-23``); here the choice is explicit:
+``ProducerBuilder.java:15-23``); here the Runner CLIs choose with ``--transport``:
 
-* ``loopback`` — in-process event queue (``psb200.engine.sim.PSSimulation`` with inline workers);
-* ``gloo``     — two-process control plane between the Runner CLIs (``psb200.parallel.link``);
-* ``p2p``      — NVLink peer-memory mailboxes, the product path (``psb200.engine.device_engine``,
-  ``psb200.engine.sparse_engine``; device side ``csrc/comm.cuh``, ``csrc/ps_sparse.cu``);
-* ``nccl``     — library collectives, the measured baseline (``psb200.parallel.nccl_baseline``).
+* ``p2p``      — NVLink / device peer-memory mailboxes, the product path: ``psb200.parallel.p2p`` (rendezvous, CUDA
+  IPC hand-over, INPUT_DATA topic in device memory) + ``csrc/comm.cuh`` (pull / push / apply inside the kernels);
+  the default of ``--backend cuda``;
+* ``loopback`` — the host event loop ``psb200.engine.sim.PSSimulation`` (exact reference scheduling, virtual or wall
+  clock), in one process or as two processes over the gloo control plane ``psb200.parallel.link``; the default of
+  ``--backend numpy`` and the CPU oracle of the tests.
+
+``psb200.parallel.nccl_baseline`` is the library-collective baseline that ``bench.py --transport nccl`` measures
+against; it is not reachable from the Runner CLIs.
 """
-from typing import Any
-
-TRANSPORTS = ("loopback", "gloo", "p2p", "nccl")
-
-
-def build(name: str, *args: Any, **kwargs: Any):
-    """Factory in the spirit of ``ProducerBuilder.build``: returns the engine / link class for a transport."""
-    if name == "loopback":
-        from ..engine.sim import PSSimulation
-        return PSSimulation(*args, **kwargs)
-    if name == "gloo":
-        from .link import ServerLink
-        return ServerLink(*args, **kwargs)
-    if name == "p2p":
-        from ..engine.device_engine import DeviceEngine
-        return DeviceEngine(*args, **kwargs)
-    if name == "nccl":
-        from .nccl_baseline import NcclBaselineEngine
-        return NcclBaselineEngine(*args, **kwargs)
-    raise ValueError(f"unknown transport {name!r}; choose one of {TRANSPORTS}")
+RUNNER_TRANSPORTS = ("auto", "p2p", "loopback")

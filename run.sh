@@ -3,8 +3,9 @@
 # to ./logs-worker.csv / ./logs-server.csv — the two-process deployment of the reference's run.sh
 # (worker first, server with `-l -p 200`).  Ctrl-C stops both.
 #
-#   ./run.sh                      two processes over the local rendezvous (CPU oracle math)
-#   BACKEND=cuda ./run.sh         same, sm_100a kernels for the math
+#   ./run.sh                      two processes over the local rendezvous (CPU oracle math, host event loop)
+#   BACKEND=cuda ./run.sh         two processes sharing device memory (CUDA IPC): rows through the INPUT_DATA topic,
+#                                 weights / gradients through the server's peer-memory block inside the sm_100a kernels
 #   GPUS=8 WORKERS_PER_GPU=1 ./run.sh   fused engine: one process per GPU under torchrun
 trap killgroup SIGINT
 killgroup() {

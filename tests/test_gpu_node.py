@@ -190,3 +190,55 @@ def test_all_workers_local_models_scored_in_one_launch():
             assert abs(f1j - f1[j]) < 1e-6 and abs(accj - acc[j]) < 1e-6
         assert len(set(np.round(f1, 6))) > 1                  # the local models differ
         e.close()
+
+
+@pytest.mark.parametrize("model", [0, -1, 3])
+def test_two_runner_processes_train_through_device_peer_memory(tmp_path, model):
+    """WorkerAppRunner and ServerAppRunner as two processes (run.sh with BACKEND=cuda): the rendezvous hands over two
+    CUDA IPC handles, rows travel through the INPUT_DATA topic in device memory, weights and gradients through the
+    server's peer-memory block inside the worker kernels; both logs come out in the reference format."""
+    import socket
+    with socket.socket() as so:
+        so.bind(("127.0.0.1", 0))
+        port = so.getsockname()[1]
+    addr = f"127.0.0.1:{port}"
+    wcmd = [sys.executable, "-m", "psb200.apps.worker_app_runner", "-l", "-test", "synthetic:600", "--backend", "cuda",
+            "-max", "256", "--rendezvous", addr]
+    scmd = [sys.executable, "-m", "psb200.apps.server_app_runner", "-l", "-p", "0", "-training", "synthetic:3000", "-test",
+            "synthetic:600", "--backend", "cuda", "--num_workers", "3", "-c", str(model), "--max_clock", "5",
+            "--rendezvous", addr, "--clocks_per_launch", "1"]
+    wdir, sdir = tmp_path / "w", tmp_path / "s"
+    wdir.mkdir(), sdir.mkdir()
+    wp = subprocess.Popen(wcmd, env=ENV, cwd=wdir, stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True)
+    try:
+        sr = subprocess.run(scmd, env=ENV, cwd=sdir, capture_output=True, text=True, timeout=600)
+        wout, werr = wp.communicate(timeout=120)
+    finally:
+        if wp.poll() is None:
+            wp.kill()
+    assert sr.returncode == 0, sr.stdout[-1500:] + sr.stderr[-3000:]
+    assert wp.returncode == 0, wout[-1500:] + werr[-3000:]
+    s = open(sdir / "logs-server.csv").read().splitlines()
+    w = open(wdir / "logs-worker.csv").read().splitlines()
+    assert s[0] == SERVER_LOG_HEADER and w[0] == WORKER_LOG_HEADER
+    srows, wrows = parse_log(s, "server"), parse_log(w, "worker")
+    assert len(wrows) == 15 and sorted(set(wrows[:, 1])) == [0, 1, 2] and sorted(set(wrows[:, 2])) == [0, 1, 2, 3, 4]
+    assert np.all(np.isfinite(wrows[:, 3])) and np.all((wrows[:, 4] > 0) & (wrows[:, 4] <= 1))    # local models scored
+    assert list(srows[:, 2]) == [0, 1, 2, 3, 4]            # a server row for every clock of worker 0 (Q6)
+    assert srows[-1, 4] > 0.2 and np.all(srows[:, 1] == -1) and np.all(srows[:, 3] == -1)
+
+
+def test_runner_cli_streams_a_csv_file_over_the_p2p_transport(tmp_path):
+    """ServerAppRunner --in_process --backend cuda on a real CSV: C++ producer thread -> topic slots -> rings."""
+    from psb200.data import ReviewGenerator, write_csv
+    gen = ReviewGenerator(num_features=256, vocab=2000, mean_len=60.0)
+    write_csv(str(tmp_path / "train.csv"), gen.train_split(1200))
+    write_csv(str(tmp_path / "test.csv"), gen.test_split(300))
+    cmd = [sys.executable, "-m", "psb200.apps.server_app_runner", "-training", "train.csv", "-test", "test.csv", "-p", "0",
+           "--num_features", "256", "--num_workers", "2", "--in_process", "-l", "--backend", "cuda", "-max", "256"]
+    r = subprocess.run(cmd, env=ENV, cwd=tmp_path, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-1500:] + r.stderr[-3000:]
+    s = open(tmp_path / "logs-server.csv").read().splitlines()
+    assert "CSV Producer sent all records!" in s
+    w = parse_log(str(tmp_path / "logs-worker.csv"), "worker")
+    assert w[:, 6].max() == 600 and np.all(np.isfinite(w[:, 3])) and parse_log(s, "server")[-1, 4] > 0.15
