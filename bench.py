@@ -52,6 +52,8 @@ def parse():
                    help="e2e wire format of the fresh rows (all lossless w.r.t. the fp16 rings): presence bitmap + per-row "
                         "palette and 4-bit codes, presence bitmap + fp16 non-zeros, or dense fp16")
     p.add_argument("--no_e2e", action="store_true")
+    p.add_argument("--no_overlap", action="store_true",
+                   help="e2e run: store every batch between two steps instead of into spare ring slots while a step runs")
     p.add_argument("--events_per_min", type=float, default=0.0,
                    help="e2e run: per-worker arrival rate used for the dynamic buffer size bc x events/min (0: unthrottled -> max)")
     p.add_argument("--transport", default="p2p", choices=["p2p", "nccl"],
@@ -167,7 +169,8 @@ def main():
         from psb200.parallel.nccl_baseline import NcclBaselineEngine as Engine
     else:
         Engine = DeviceEngine
-    eng = Engine(cfg, W, rank, world, impl, dev, w0=w0, stage_rows=W * a.ingest_rows)
+    kw = {} if a.no_overlap or a.no_e2e else {"ring_spare_rows": a.ingest_rows}
+    eng = Engine(cfg, W, rank, world, impl, dev, w0=w0, stage_rows=W * a.ingest_rows, **kw)
     eng.connect()
     X, y = synth_buffers(torch, W, cap, F, a.density, 1234 + rank, dev)
     eng.fill(X, y)
@@ -233,20 +236,22 @@ def main():
             tick[0] += 1
             return base + np.tile(np.arange(a.ingest_rows) * gap_ms, W)
 
-        # Software pipeline through the public API: the host->device copies of batches i+1 and i+2
-        # (ingest_begin, copy stream, three staging sets) are in flight while step i trains; ingest_commit stores
-        # batch i into the rings between two steps.  Every step still pays its own H2D (pinned host -> device)
-        # and its own D2H read of the losses.
+        # Software pipeline through the public API: the host->device copies of batches i+2 and i+3
+        # (ingest_begin, copy stream, three staging sets) are in flight while step i trains, and batch i+1 is stored
+        # into the rings WHILE step i runs: the rings hold `ingest_rows` spare slots per worker, so the new rows land
+        # outside the windows step i reads (ingest_commit(overlap=True)); step i+1 waits for that store.  Every step
+        # still pays its own H2D (pinned host -> device) and its own D2H read of the losses.
         # The result read is pipelined the same way: step i's losses are copied device -> host behind step i and
         # consumed on the host after step i+1 has been queued (read_loss_begin / read_loss_end).
         pending = [None]
         seen = [0.0]
+        overlap = not a.no_overlap
 
         def one(i):
-            eng.ingest_commit()                                                            # batch i -> rings
             eng.step()                                                                     # enqueue clock i
             ticket = eng.read_loss_begin()                                                 # D2H of clock i's result
-            eng.ingest_begin(host_rows[(i + 2) % pool], host_lab[(i + 2) % pool], workers, stamps())   # H2D of i+2
+            eng.ingest_commit(overlap=overlap)                                             # batch i+1 -> rings
+            eng.ingest_begin(host_rows[(i + 3) % pool], host_lab[(i + 3) % pool], workers, stamps())   # H2D of i+3
             if pending[0] is not None:
                 seen[0] = float(eng.read_loss_end(pending[0])[0])                          # clock i-1's result, on the host
             pending[0] = ticket
@@ -257,7 +262,9 @@ def main():
                 pending[0] = None
 
         eng.ingest_begin(host_rows[0], host_lab[0], workers, stamps())
+        eng.ingest_commit()                                              # batch 0 before the first step
         eng.ingest_begin(host_rows[1], host_lab[1], workers, stamps())
+        eng.ingest_begin(host_rows[2], host_lab[2], workers, stamps())
         for i in range(a.warmup):
             one(i)
         drain()
@@ -281,7 +288,11 @@ def main():
                "buffer_rows_effective": rows_eff, "events_per_min_per_worker": a.events_per_min,
                "h2d_bytes_per_step": (eng.h2d_bytes - h0) // a.steps, "d2h_bytes_per_step": W * 4,
                "ms_per_step": ems / a.steps, "ingested_samples_per_sec": n_new * world * a.steps / (ems / 1000.0),
-               "new_rows_per_worker_per_step": a.ingest_rows, "ingest_format": a.ingest_format}
+               "new_rows_per_worker_per_step": a.ingest_rows, "ingest_format": a.ingest_format,
+               "store_overlaps_step": bool(overlap and eng.ring_spare >= a.ingest_rows),
+               "e2e_check": {"inputs_from_pinned_host_every_step": True, "h2d_inside_timed_region": True,
+                             "result_read_on_host_every_step": True, "d2h_inside_timed_region": True,
+                             "timed_by": "max(CUDA events, host wall clock), max over ranks"}}
 
     clocks = sampler.stop() if rank == 0 else None       # sampled across both timed regions
     if rank == 0:

@@ -211,6 +211,7 @@ extern "C" int psb_tracker_clocks(void* tp, int* clocks) {
 namespace {
 struct Buffer {
     int min_size, max_size, window;
+    int ring = 0;                        // physical slots of the device ring (>= max_size; head wraps here)
     float bc;
     std::vector<double> deltas;          // circular: the last `window` inter-arrival times
     int n_deltas = 0, pos = 0;
@@ -225,10 +226,22 @@ extern "C" void* psb_buffer_create(int min_size, int max_size, float bc, int win
     if (min_size < 1 || max_size < min_size) return nullptr;
     Buffer* b = new Buffer();
     b->min_size = min_size, b->max_size = max_size, b->bc = bc, b->window = window > 0 ? window : 500;
+    b->ring = max_size;
     b->deltas.assign((size_t)b->window, 0.0);
     return b;
 }
 extern "C" void psb_buffer_destroy(void* b) { delete (Buffer*)b; }
+// The device ring may hold more slots than the largest window (spare slots let the next batch be stored while
+// a step still trains on the current window): head then wraps at ring_slots instead of max_size.
+extern "C" int psb_buffer_set_ring(void* bp, int ring_slots) {
+    Buffer* b = (Buffer*)bp;
+    if (!b || ring_slots < b->max_size || b->inserted != 0) {
+        psb_set_error("psb_buffer_set_ring: ring must hold at least max_size slots and be set before the first event");
+        return PSB_E_INVALID;
+    }
+    b->ring = ring_slots;
+    return 0;
+}
 
 // Returns the slot to write; head/count describe the window after the event.
 static inline int buffer_on_event(Buffer* b, double now_ms, int* head, int* count, int* target) {
@@ -254,7 +267,7 @@ static inline int buffer_on_event(Buffer* b, double now_ms, int* head, int* coun
     }
     const int tgt = std::max(b->min_size, std::min(b->max_size, calc));
     const int slot = b->head;
-    if (++b->head == b->max_size) b->head = 0;
+    if (++b->head == b->ring) b->head = 0;
     b->count = std::min(b->count + 1, tgt);
     b->inserted++;
     *head = b->head, *count = b->count, *target = tgt;
@@ -286,7 +299,7 @@ extern "C" int psb_buffer_set_state(void* bp, const double* state, int n) {
     b->n_deltas = (int)state[1], b->pos = (int)state[2], b->total = state[3], b->last = state[4];
     b->has_last = state[5] != 0.0, b->head = (int)state[6], b->count = (int)state[7];
     b->inserted = (long long)state[8];
-    if (b->head < 0 || b->head >= b->max_size || b->count < 0 || b->count > b->max_size || b->pos < 0 ||
+    if (b->head < 0 || b->head >= b->ring || b->count < 0 || b->count > b->max_size || b->pos < 0 ||
         b->pos >= b->window || b->n_deltas < 0 || b->n_deltas > b->window) {
         psb_set_error("psb_buffer_set_state: cursors out of range");
         return PSB_E_INVALID;
@@ -317,12 +330,12 @@ extern "C" int psb_buffers_on_batch(void** buffers, int num_buffers, const int* 
     // written: earlier ones get slot -1 and are skipped on the device (the ring then holds the last
     // max_size rows, as a row-by-row replay would leave it).
     int min_cap = 1 << 30;
-    for (int w = 0; w < num_buffers; ++w) min_cap = std::min(min_cap, ((Buffer*)buffers[w])->max_size);
+    for (int w = 0; w < num_buffers; ++w) min_cap = std::min(min_cap, ((Buffer*)buffers[w])->ring);
     if (n > min_cap) {
         std::vector<int> kept((size_t)num_buffers, 0);
         for (int i = n - 1; i >= 0; --i) {
             const int w = worker_slot[2 * i];
-            if (kept[w] >= ((Buffer*)buffers[w])->max_size) worker_slot[2 * i + 1] = -1;
+            if (kept[w] >= ((Buffer*)buffers[w])->ring) worker_slot[2 * i + 1] = -1;
             else ++kept[w];
         }
     }

@@ -106,17 +106,18 @@ struct TcEval {
     TcShared sh;
     unsigned int zuse[2], ruse[2], guse;   // per-thread running barrier use counts (persist across evaluations)
     int pass_no;                           // passes run so far (every thread counts them): parity = slab direction
-    float* Zx;                             // cached logits of the current point / of the direction, [cap][8] each
-    float* Zd;                             // (null: no caching, every trial is a full evaluation)
+    float* Zx;                             // cached logits of the current point / of the direction, [count][8] each,
+    float* Zd;                             // indexed by window position (null: no caching, every trial is a full evaluation)
 #ifdef PSB_TC_PROFILE
     long long prof[4];                     // cycles: [0] wait full(A) [1] wait r_full [2] wait full(B) [3] role total
 #endif
 
-    __device__ __forceinline__ bool row_valid(int slot) const {
+    __device__ __forceinline__ int window_pos(int slot) const {      // position of a ring slot in the window (>= count: outside)
         int d = slot - start;
         if (d < 0) d += cap;
-        return d < count;
+        return d;
     }
+    __device__ __forceinline__ bool row_valid(int slot) const { return window_pos(slot) < count; }
     __device__ __forceinline__ bool slab_active(int b) const {
         const int lo = b * kSlabRows, hi = lo + kSlabRows;
         const int e = start + count;
@@ -444,7 +445,7 @@ struct TcEval {
 #pragma unroll
                 for (int c = 0; c < 8; ++c) z[c] = v[c] + v[8 + c];
                 if (cfg.zstore && valid) {
-                    float4* zo = (float4*)cfg.zstore + 2 * slot;
+                    float4* zo = (float4*)cfg.zstore + 2 * window_pos(slot);
                     zo[0] = make_float4(z[0], z[1], z[2], z[3]);
                     zo[1] = make_float4(z[4], z[5], z[6], z[7]);
                 }
@@ -457,7 +458,7 @@ struct TcEval {
                 }
             }
             if (!cfg.a && valid) {
-                const float4* zi = (const float4*)cfg.zsrc + 2 * slot;
+                const float4* zi = (const float4*)cfg.zsrc + 2 * window_pos(slot);
                 const float4 z0 = zi[0], z1 = zi[1];
                 z[0] = z0.x, z[1] = z0.y, z[2] = z0.z, z[3] = z0.w, z[4] = z1.x, z[5] = z1.y, z[6] = z1.z, z[7] = z1.w;
             }
@@ -617,14 +618,12 @@ struct TcEval {
     __device__ void derive_direction_logits(double t1) {
         const float it = (float)(1.0 / t1);
         for (int i = threadIdx.x; i < count; i += blockDim.x) {
-            int slot = start + i;
-            if (slot >= cap) slot -= cap;
 #pragma unroll
             for (int h = 0; h < 2; ++h) {
-                const float4 a = ((const float4*)Zx)[2 * slot + h];
-                float4 b = ((float4*)Zd)[2 * slot + h];
+                const float4 a = ((const float4*)Zx)[2 * i + h];
+                float4 b = ((float4*)Zd)[2 * i + h];
                 b.x = (b.x - a.x) * it, b.y = (b.y - a.y) * it, b.z = (b.z - a.z) * it, b.w = (b.w - a.w) * it;
-                ((float4*)Zd)[2 * slot + h] = b;
+                ((float4*)Zd)[2 * i + h] = b;
             }
         }
         __syncthreads();
@@ -643,8 +642,8 @@ struct TcEval {
         for (int i = threadIdx.x; i < count; i += blockDim.x) {
             int slot = start + i;
             if (slot >= cap) slot -= cap;
-            const float4 a0 = ((const float4*)Zx)[2 * slot], a1 = ((const float4*)Zx)[2 * slot + 1];
-            const float4 d0 = ((const float4*)Zd)[2 * slot], d1 = ((const float4*)Zd)[2 * slot + 1];
+            const float4 a0 = ((const float4*)Zx)[2 * i], a1 = ((const float4*)Zx)[2 * i + 1];
+            const float4 d0 = ((const float4*)Zd)[2 * i], d1 = ((const float4*)Zd)[2 * i + 1];
             const float zd[8] = {d0.x, d0.y, d0.z, d0.w, d1.x, d1.y, d1.z, d1.w};
             const float z[8] = {fmaf(ft, zd[0], a0.x), fmaf(ft, zd[1], a0.y), fmaf(ft, zd[2], a0.z), fmaf(ft, zd[3], a0.w),
                                 fmaf(ft, zd[4], a1.x), fmaf(ft, zd[5], a1.y), fmaf(ft, zd[6], a1.z), fmaf(ft, zd[7], a1.w)};
@@ -663,14 +662,12 @@ struct TcEval {
     __device__ void advance(double alpha) {                        // Zx <- Zx + alpha Zd
         const float fa = (float)alpha;
         for (int i = threadIdx.x; i < count; i += blockDim.x) {
-            int slot = start + i;
-            if (slot >= cap) slot -= cap;
 #pragma unroll
             for (int h = 0; h < 2; ++h) {
-                float4 a = ((float4*)Zx)[2 * slot + h];
-                const float4 b = ((const float4*)Zd)[2 * slot + h];
+                float4 a = ((float4*)Zx)[2 * i + h];
+                const float4 b = ((const float4*)Zd)[2 * i + h];
                 a.x = fmaf(fa, b.x, a.x), a.y = fmaf(fa, b.y, a.y), a.z = fmaf(fa, b.z, a.z), a.w = fmaf(fa, b.w, a.w);
-                ((float4*)Zx)[2 * slot + h] = a;
+                ((float4*)Zx)[2 * i + h] = a;
             }
         }
     }
@@ -777,8 +774,8 @@ psb_worker_tc_kernel(const __grid_constant__ CUtensorMap tmX, PsbSolver sv, Comm
         ev.zuse[0] = ev.zuse[1] = ev.ruse[0] = ev.ruse[1] = ev.guse = 0;
         ev.pass_no = 0;
         // logit cache in two spare solver vectors (the L-BFGS pairs of index PSB_HIST-1 are never reached when
-        // max_iter <= PSB_HIST-1): [cap][8] floats each must fit one parameter vector
-        const bool cached = sv.solver == PSB_SOLVER_LBFGS && cap * 8 <= nv && sv.max_iter <= PSB_HIST - 1;
+        // max_iter <= PSB_HIST-1): [count][8] floats each (indexed by window position) must fit one parameter vector
+        const bool cached = sv.solver == PSB_SOLVER_LBFGS && count * 8 <= nv && sv.max_iter <= PSB_HIST - 1;
         ev.Zx = cached ? ws.vec[7 + PSB_HIST - 1] : nullptr;
         ev.Zd = cached ? ws.vec[7 + 2 * PSB_HIST - 1] : nullptr;
 #ifdef PSB_TC_PROFILE

@@ -285,6 +285,7 @@ int psb_tracker_clocks(void* t, int* clocks);
 void* psb_buffer_create(int min_size, int max_size, float bc, int window);
 void psb_buffer_destroy(void* b);
 int psb_buffer_on_event(void* b, double now_ms, int* head, int* count, int* target);
+int psb_buffer_set_ring(void* b, int ring_slots);   /* physical ring slots >= max_size (default: max_size) */
 long long psb_buffer_inserted(void* b);   /* rows ever inserted == numTuplesSeen of the worker log */
 /* Checkpoint of a buffer's policy state: the inter-arrival window and the ring cursors.  state: double[window + 8];
  * get returns the number of doubles written (-1: capacity too small), set returns 0 or PSB_E_INVALID. */

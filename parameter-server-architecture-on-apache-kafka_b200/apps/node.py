@@ -38,12 +38,8 @@ def build_parser():
     p = cli.server_parser()
     p.prog = "psb200.apps.node"
     p.add_argument("--workers_per_gpu", type=int, default=1)
-    p.add_argument("--impl", choices=["tc", "simt"], default="tc")
     p.add_argument("--rows_per_clock", type=int, default=0,
                    help="rows each worker ingests per clock when -p 0 (default: min buffer size)")
-    p.add_argument("--clocks_per_launch", type=int, default=0,
-                   help="relaxed models: clocks every worker runs per launch, each at its own pace (default 1: "
-                        "a server log row per clock; larger values let fast workers run ahead inside a launch)")
     p.add_argument("--groups", type=int, default=1,
                    help="relaxed models: launch the workers of a GPU as this many independent groups (own streams)")
     p.add_argument("--checkpoint_dir", default="")

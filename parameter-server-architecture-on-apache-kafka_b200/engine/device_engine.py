@@ -46,7 +46,7 @@ class DeviceEngine:
                  device: Optional[torch.device] = None, w0: Optional[np.ndarray] = None, stage_rows: int = 0,
                  stage_sets: int = 3, spin_limit_cycles: int = 20_000_000_000, async_granularity: str = "rank",
                  groups: int = 1, max_clocks_per_launch: int = 64, external_block: Optional[int] = None,
-                 home_remote: bool = False):
+                 home_remote: bool = False, ring_spare_rows: int = 0):
         if not torch.cuda.is_available():
             raise native.NativeError("DeviceEngine needs a CUDA device")
         if async_granularity not in ("rank", "worker"):
@@ -59,13 +59,24 @@ class DeviceEngine:
         self.max_clocks_per_launch = max(1, int(max_clocks_per_launch))
         self.device = device or torch.device("cuda", torch.cuda.current_device())
         self.layout = LogRegLayout(cfg.num_features, cfg.num_classes)
-        F, cap = cfg.num_features, cfg.max_buffer_size
-        self.F, self.cap, self.nv = F, cap, self.layout.device_size
+        # Ring of every worker: the largest window (max_buffer_size) plus `ring_spare_rows` spare slots.  New rows are
+        # written at the head, i.e. into slots OUTSIDE the current window as long as a batch brings at most
+        # `ring_spare_rows` rows per worker: such a batch may be stored while a step still trains on the current window
+        # (ingest_commit(overlap=True)).  Kept a multiple of 128 rows so that the tcgen05 kernel's slabs stay whole.
+        spare = (int(ring_spare_rows) + 127) // 128 * 128 if ring_spare_rows > 0 else 0
+        F, cap = cfg.num_features, cfg.max_buffer_size + spare
+        self.F, self.cap, self.nv, self.ring_spare = F, cap, self.layout.device_size, spare
         dev = self.device
         self.X = torch.zeros((self.W, cap, F), dtype=torch.float16, device=dev)
         self.labels = torch.zeros((self.W, cap), dtype=torch.int32, device=dev)
         self.win_host = torch.zeros((self.W, 2), dtype=torch.int32).pin_memory()
-        self.win = torch.zeros((self.W, 2), dtype=torch.int32, device=dev)
+        # the windows live twice on the device: a step reads the table that the last commit wrote, an overlapped
+        # commit writes the other one
+        self._win = [torch.zeros((self.W, 2), dtype=torch.int32, device=dev) for _ in range(2)]
+        self._win_i = 0
+        self._commits_since_step = 0
+        self._step_done = [torch.cuda.Event(), torch.cuda.Event()]    # completion of the last two steps
+        self._steps = 0
         self.loss = torch.zeros(self.W, dtype=torch.float32, device=dev)
         self.info = torch.zeros((self.W, 8), dtype=torch.int32, device=dev)
         self.delta = torch.zeros((self.W, self.nv), dtype=torch.float32, device=dev)
@@ -101,8 +112,8 @@ class DeviceEngine:
         # ingestion: host-side window bookkeeping + a ring of staging sets.  begin() fills set `head` over the
         # copy stream, commit() drains set `tail` into the rings over the ingest stream; with S sets the H2D of
         # batch k+S-1 overlaps the step that trains on batch k.
-        self.buffers = [native.NativeBuffer(cfg.min_buffer_size, cap, cfg.buffer_size_coefficient)
-                        for _ in range(self.W)]
+        self.buffers = [native.NativeBuffer(cfg.min_buffer_size, cfg.max_buffer_size, cfg.buffer_size_coefficient,
+                                            ring=cap) for _ in range(self.W)]
         self._buf_handles = None
         self.rows_ingested = 0
         self.stage_rows = stage_rows or self.W * 128
@@ -118,6 +129,7 @@ class DeviceEngine:
         self._slot_thread = None
         self.stage_kind = ["dense"] * S
         self.stage_n = [0] * S
+        self.stage_max_rows = [0] * S
         self.stage_head = self.stage_tail = self.stage_pending = 0
         self.h2d_done = [torch.cuda.Event() for _ in range(S)]       # copies of set j have landed
         self.store_done = [torch.cuda.Event() for _ in range(S)]     # set j has been drained into the rings
@@ -184,21 +196,29 @@ class DeviceEngine:
         self.test_X = torch.from_numpy(test.to_dense(np.float16)).to(self.device)
         self.test_y = torch.from_numpy(test.labels.astype(np.int32)).to(self.device)
 
+    @property
+    def win(self) -> torch.Tensor:
+        """Device table of the workers' (head, count) windows that the next step will read."""
+        return self._win[self._win_i]
+
     def fill(self, rows: torch.Tensor, labels: torch.Tensor) -> None:
-        """Bulk-load every ring: rows fp16 [W, n, F] (device or host), labels int32 [W, n]; n <= cap."""
+        """Bulk-load every ring: rows fp16 [W, n, F] (device or host), labels int32 [W, n]; n <= max_buffer_size."""
         n = rows.shape[1]
+        if n > self.cfg.max_buffer_size:
+            raise ValueError(f"fill: {n} rows per worker exceed max_buffer_size {self.cfg.max_buffer_size}")
         self._wait_slot_thread()
         self.X[:, :n].copy_(rows)
         self.labels[:, :n].copy_(labels)
-        self.buffers = [native.NativeBuffer(self.cfg.min_buffer_size, self.cap, self.cfg.buffer_size_coefficient)
-                        for _ in range(self.W)]
+        self.buffers = [native.NativeBuffer(self.cfg.min_buffer_size, self.cfg.max_buffer_size,
+                                            self.cfg.buffer_size_coefficient, ring=self.cap) for _ in range(self.W)]
         self._buf_handles = None
         for b in self.buffers:                      # replay n unthrottled arrivals so the host mirror agrees
             for _ in range(n):
                 b.on_event(0.0)
         self.win_host[:, 0] = n % self.cap
         self.win_host[:, 1] = n
-        self.win.copy_(self.win_host)
+        for t in self._win:
+            t.copy_(self.win_host)
 
     def ingest(self, rows_f16, labels: Optional[torch.Tensor], workers: np.ndarray,
                now_ms: Optional[np.ndarray] = None, wait: bool = True) -> None:
@@ -240,6 +260,8 @@ class DeviceEngine:
         workers = np.ascontiguousarray(workers[:n], dtype=np.int32)
         now_ms = np.zeros(n, dtype=np.float64) if now_ms is None else np.ascontiguousarray(now_ms[:n], dtype=np.float64)
         handles, buffers = self._buf_handles, self.buffers
+        # most rows any worker receives from this set: decides whether its store may overlap a running step
+        self.stage_max_rows[j] = int(np.bincount(workers, minlength=1).max()) if n else 0
 
         def assign():
             native.buffers_on_batch(buffers, workers, now_ms, self.stage_ws_host[j].numpy(), self.win_host.numpy(),
@@ -319,6 +341,8 @@ class DeviceEngine:
         for gs in self.group_streams:
             if gs is not None:
                 s.wait_stream(gs)
+        self._win_i ^= 1
+        self._commits_since_step += 1
         native.h2d_copies([(self.win, self.stage_win_host[j], self.W * 8),
                            (self.stage_ws_dev[j], self.stage_ws_host[j], n * 8)], stream=s)
         native.ring_store_palette(int(bitmap), int(row_off), int(payload), int(labels), self.stage_ws_dev[j], n, self.X,
@@ -334,8 +358,11 @@ class DeviceEngine:
             torch.cuda.current_stream().wait_event(self.ingest_done)
         return s
 
-    def ingest_commit(self, wait: bool = True) -> None:
-        """Second half: store the oldest begun batch into the rings (after the running step, before the next)."""
+    def ingest_commit(self, wait: bool = True, overlap: bool = False) -> None:
+        """Second half: store the oldest begun batch into the rings — after the step that is running (default), or,
+        with ``overlap=True``, WHILE the most recently enqueued step runs: the new rows go into ring slots outside that
+        step's windows (needs ``ring_spare_rows`` >= the rows any worker receives from the batch, one overlapped commit
+        per step; otherwise the call quietly orders itself behind the step).  The next step waits for the store."""
         if self.stage_pending == 0:
             return
         j = self.stage_tail
@@ -343,11 +370,20 @@ class DeviceEngine:
         s = self.ingest_stream
         torch.cuda.nvtx.range_push("psb.ingest_commit")
         self.stage_future[j].result()                       # slot tables of this batch are written (helper thread)
-        s.wait_stream(torch.cuda.current_stream())          # the previous step must be done with the rings
-        for gs in self.group_streams:                       # ... on whichever stream its groups ran
-            if gs is not None:
-                s.wait_stream(gs)
+        overlap = (overlap and self.groups == 1 and self._commits_since_step == 0 and self._steps >= 1
+                   and 0 < self.stage_max_rows[j] <= self.ring_spare)
+        if overlap:
+            # the slots written now were inside the window of the step BEFORE the running one: wait for that one only
+            if self._steps >= 2:
+                s.wait_event(self._step_done[self._steps & 1])
+        else:
+            s.wait_stream(torch.cuda.current_stream())      # the previous step must be done with the rings
+            for gs in self.group_streams:                   # ... on whichever stream its groups ran
+                if gs is not None:
+                    s.wait_stream(gs)
         s.wait_event(self.h2d_done[j])
+        self._win_i ^= 1                                    # the running step keeps reading the other table
+        self._commits_since_step += 1
         tables = [(self.win, self.stage_win_host[j], self.W * 8)]
         if self.stage_kind[j] != "csr":
             tables.append((self.stage_ws_dev[j], self.stage_ws_host[j], n * 8))
@@ -399,6 +435,9 @@ class DeviceEngine:
                            self.w0 if mode == native.COMM_NONE else None,
                            self.delta if mode == native.COMM_NONE else None,
                            self.loss, self.info, self.scratch)
+        self._step_done[self._steps & 1].record()
+        self._steps += 1
+        self._commits_since_step = 0
         self.kernel_launches += 1
         self.clock += 1
 
@@ -434,6 +473,7 @@ class DeviceEngine:
                            self.win[lo:lo + gs], None, None, self.loss[lo:lo + gs], self.info[lo:lo + gs],
                            self.scratch[lo:lo + gs], stream=st)
         self.hist_n[g] = n
+        self._commits_since_step = 0
         self.kernel_launches += 1
         self.group_clock[g] += n
 
@@ -586,7 +626,9 @@ class DeviceEngine:
             raise ValueError("checkpoint was written by a different rank layout")
         self._wait_slot_thread()
         self.X.copy_(sd["X"]), self.labels.copy_(sd["labels"])
-        self.win_host.copy_(sd["win"]), self.win.copy_(self.win_host)
+        self.win_host.copy_(sd["win"])
+        for t in self._win:
+            t.copy_(self.win_host)
         for b, st in zip(self.buffers, sd["buffers"]):
             b.set_state(st)
         self._buf_handles = None

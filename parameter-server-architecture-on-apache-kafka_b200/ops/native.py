@@ -138,6 +138,7 @@ def lib() -> C.CDLL:
     L.psb_buffer_inserted.argtypes = [vp]
     L.psb_buffers_on_batch.argtypes = [vp, C.c_int, vp, vp, C.c_int, vp, vp]
     L.psb_buffer_get_state.argtypes = [vp, vp, C.c_int]
+    L.psb_buffer_set_ring.argtypes = [vp, C.c_int]
     L.psb_buffer_set_state.argtypes = [vp, vp, C.c_int]
     L.psb_comm_wait_version.argtypes = [vp, C.c_int, C.c_int, C.c_uint, C.c_ulonglong, vp]
     L.psb_eval_models.argtypes = [vp, ip, C.c_int, fp, fp, C.c_size_t, C.c_int, C.c_int, C.c_int, ip, fp, C.c_int, vp]
@@ -337,11 +338,14 @@ class NativeTracker:
 
 
 class NativeBuffer:
-    def __init__(self, min_size: int, max_size: int, bc: float, window: int = 500):
+    def __init__(self, min_size: int, max_size: int, bc: float, window: int = 500, ring: int = 0):
+        """ring: physical slots of the device ring when it holds more than max_size (spare slots)."""
         self.h = lib().psb_buffer_create(min_size, max_size, bc, window)
         if not self.h:
             raise NativeError("psb_buffer_create failed")
         self.window = window if window > 0 else 500
+        if ring and ring != max_size:
+            check(lib().psb_buffer_set_ring(self.h, ring), "psb_buffer_set_ring")
         self.head = self.count = self.target = 0
 
     def ring_total(self) -> int:

@@ -33,6 +33,9 @@ class NcclBaselineEngine(DeviceEngine):
         if self.world > 1:
             dist.all_reduce(self.sum_delta)
         native.apply_delta(self.w_dev, self.sum_delta, self.lr, self.F, -1)
+        self._step_done[self._steps & 1].record()         # (overlapped ring stores order themselves on these)
+        self._steps += 1
+        self._commits_since_step = 0
         self.kernel_launches += 2
         self.clock += 1
 

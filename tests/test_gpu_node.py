@@ -242,3 +242,41 @@ def test_runner_cli_streams_a_csv_file_over_the_p2p_transport(tmp_path):
     assert "CSV Producer sent all records!" in s
     w = parse_log(str(tmp_path / "logs-worker.csv"), "worker")
     assert w[:, 6].max() == 600 and np.all(np.isfinite(w[:, 3])) and parse_log(s, "server")[-1, 4] > 0.15
+
+
+def test_store_into_spare_ring_slots_while_a_step_runs_gives_the_serialized_result():
+    """ring_spare_rows + ingest_commit(overlap=True): batch i+1 is stored while step i trains; every step must see
+    exactly the windows (and produce exactly the losses / weights) of the engine that stores between two steps."""
+    from psb200.config import PSConfig
+    from psb200.data import ReviewGenerator
+    from psb200.engine.device_engine import DeviceEngine
+    F, cap, W, r, steps = 256, 256, 4, 64, 9
+    cfg = PSConfig(num_workers=W, num_features=F, max_buffer_size=cap, min_buffer_size=16)
+    gen = ReviewGenerator(F, 5, vocab=3000, mean_len=120.0)
+    batches = []
+    for i in range(steps + 1):
+        b = gen.train_split(W * r, seed=100 + i)
+        batches.append((torch.from_numpy(b.to_dense(np.float16)).pin_memory(),
+                        torch.from_numpy(b.labels.astype(np.int32)).pin_memory()))
+    workers = np.repeat(np.arange(W, dtype=np.int32), r)
+    out = []
+    for spare in (0, r):
+        e = DeviceEngine(cfg, W, impl=1, stage_rows=W * r, ring_spare_rows=spare)
+        assert e.cap == cap + (128 if spare else 0)
+        e.ingest_begin(*batches[0], workers)
+        e.ingest_commit()
+        losses = []
+        for i in range(steps):
+            e.ingest_begin(*batches[i + 1], workers)
+            e.step()
+            t = e.read_loss_begin()
+            e.ingest_commit(overlap=bool(spare))              # spare == 0: orders itself behind the step
+            losses.append(e.read_loss_end(t).numpy().copy())
+        torch.cuda.synchronize()
+        out.append((np.asarray(losses), e.weights().cpu().numpy().copy(), e.win_host.clone()))
+        assert e.status() == 0
+        e.close()
+    # same rows, same windows; the rows sit in other ring slots, so only the summation order inside the GEMMs differs
+    assert np.allclose(out[0][0], out[1][0], rtol=3e-4, atol=3e-5)
+    assert np.abs(out[0][1] - out[1][1]).max() < 3e-4 * max(1e-2, np.abs(out[0][1]).max())
+    assert out[0][2][:, 1].tolist() == [cap] * W               # the windows filled up and wrapped: (steps+1)*r > cap
