@@ -52,6 +52,10 @@ def parse():
                    help="e2e wire format of the fresh rows (all lossless w.r.t. the fp16 rings): presence bitmap + per-row "
                         "palette and 4-bit codes, presence bitmap + fp16 non-zeros, or dense fp16")
     p.add_argument("--no_e2e", action="store_true")
+    p.add_argument("--stats", choices=["fused", "ingest"], default="fused",
+                   help="standardisation statistics: recomputed by every step, fused into its first pass over the buffer "
+                        "(what the reference's fit does), or kept current at ingestion time (windows that did not change "
+                        "cost nothing)")
     p.add_argument("--no_overlap", action="store_true",
                    help="e2e run: store every batch between two steps instead of into spare ring slots while a step runs")
     p.add_argument("--events_per_min", type=float, default=0.0,
@@ -169,7 +173,7 @@ def main():
         from psb200.parallel.nccl_baseline import NcclBaselineEngine as Engine
     else:
         Engine = DeviceEngine
-    kw = {} if a.no_overlap or a.no_e2e else {"ring_spare_rows": a.ingest_rows}
+    kw = {} if a.no_overlap or a.no_e2e else {"ring_spare_rows": a.ingest_rows, "stats_at_ingest": a.stats == "ingest"}
     eng = Engine(cfg, W, rank, world, impl, dev, w0=w0, stage_rows=W * a.ingest_rows, **kw)
     eng.connect()
     X, y = synth_buffers(torch, W, cap, F, a.density, 1234 + rank, dev)
@@ -308,7 +312,7 @@ def main():
                        "global_batch": W * world * cap, "seq_len": None,
                        "parallelism": f"ps-dp{world} ({W} workers/GPU, {world} server shards)",
                        "num_workers": W * world, "buffer_rows": cap, "density": a.density,
-                       "local_solver": a.solver, "consistency_model": a.consistency_model,
+                       "local_solver": a.solver, "consistency_model": a.consistency_model, "statistics": a.stats,
                        "l2": f"inputs larger than L2 ({W * cap * F * 2 / 2**20:.0f} MiB of rows per GPU streamed per pass)",
                        "evals_per_step": float(info[:, 0].mean()), "status": status,
                        "cycles64_stats_solve_push_total": [float(info[:, k].mean()) for k in (4, 5, 6, 7)],

@@ -30,6 +30,7 @@ int psb_launch_ring_store_bitmap(const uint32_t*, const int*, const void*, const
 int psb_launch_ring_store_palette(const uint32_t*, const int*, const void*, const int*, const int*, int, void*, int*, int, int,
                                   cudaStream_t);
 int psb_launch_apply_delta(float*, const float*, float, int, int, cudaStream_t);
+int psb_launch_window_stats(const void*, const int*, int, int, int, double*, float*, cudaStream_t);
 
 extern "C" {
 
@@ -265,6 +266,14 @@ int psb_ring_store_palette(const uint32_t* d_bitmap, const int* d_row_off, const
     PSB_REQUIRE(num_features % 32 == 0, "psb_ring_store_palette: num_features must be a multiple of 32");
     return psb_launch_ring_store_palette(d_bitmap, d_row_off, d_payload, d_labels_in, d_worker_slot, n, d_X, d_labels,
                                          cap, num_features, (cudaStream_t)stream);
+}
+
+int psb_window_stats_update(const void* d_X, const int* d_change, int num_workers, int cap, int num_features,
+                            double* d_sums, float* d_inv_std, void* stream) {
+    PSB_REQUIRE(d_X && d_change && d_sums && d_inv_std, "psb_window_stats_update: null pointer");
+    PSB_REQUIRE(num_features % 4 == 0 && cap >= 1, "psb_window_stats_update: num_features must be a multiple of 4");
+    return psb_launch_window_stats(d_X, d_change, num_workers, cap, num_features, d_sums, d_inv_std,
+                                   (cudaStream_t)stream);
 }
 
 // Several host -> device copies with one call (the ingestion path issues 2-4 small copies per batch; from Python

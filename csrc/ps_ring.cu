@@ -141,13 +141,30 @@ __global__ void __launch_bounds__(256, 4) psb_ring_store_palette_kernel(const ui
             int k = base + incl - cnt;
             __align__(16) unsigned short out[32];
             if (npal > 0) {                                                    // warp-uniform branch
+                // This lane's <= 32 codes are nibbles [k, k + cnt) of the row's code stream.  Fetch the <= 20 bytes
+                // that hold them with five aligned word loads (all issued at once) and line them up so that nibble
+                // t of the lane sits at bit 4 (t & 7) of A[t >> 3]; a set bit b then finds its code with a popcount
+                // instead of a dependent byte load per bit.
+                const unsigned char* cb = codes + (k >> 1);
+                const uintptr_t a0 = (uintptr_t)cb & ~(uintptr_t)3;
+                const uint32_t* wp = (const uint32_t*)a0;
+                const int nwords = cnt ? (int)(((uintptr_t)cb + (size_t)((cnt + (k & 1) + 1) >> 1) - a0 + 3) >> 2) : 0;
+                uint32_t wd[6];
+#pragma unroll
+                for (int i = 0; i < 6; ++i) wd[i] = i < nwords ? __ldg(wp + i) : 0u;
+                const uint32_t sh = (uint32_t)(((uintptr_t)cb & 3) * 8 + (k & 1) * 4);      // < 32
+                uint32_t A[4];
+#pragma unroll
+                for (int i = 0; i < 4; ++i) A[i] = __funnelshift_r(wd[i], wd[i + 1], sh);
 #pragma unroll
                 for (int b = 0; b < 32; ++b) {
                     const bool on = (bits >> b) & 1u;
-                    const unsigned int code = on ? (codes[k >> 1] >> ((k & 1) * 4)) & 15u : 0u;
+                    const uint32_t t = (uint32_t)__popc(bits & ((1u << b) - 1u));          // codes before bit b
+                    const uint32_t lo = (t & 8u) ? A[1] : A[0], hi = (t & 8u) ? A[3] : A[2];
+                    const uint32_t word = (t & 16u) ? hi : lo;
+                    const uint32_t code = on ? (word >> ((t & 7u) * 4u)) & 15u : 0u;
                     const unsigned int v = __shfl_sync(0xffffffffu, pal, (int)code);
                     out[b] = on ? (unsigned short)v : (unsigned short)0;
-                    k += on;
                 }
             } else {
 #pragma unroll
@@ -166,6 +183,74 @@ __global__ void __launch_bounds__(256, 4) psb_ring_store_palette_kernel(const ui
         }
         if (lane == 0) labels[(size_t)worker * cap + slot] = labels_in[r];
     }
+}
+
+// Incremental window statistics: one block per (worker, 128-feature strip).  The rows that left / entered the window are
+// dealt round-robin to the block's 8 warps; a lane owns 4 adjacent features (one 8-byte load per row, 256 contiguous
+// bytes per warp) and keeps their partial sums in doubles; the warps' partials are combined through shared memory.
+__global__ void __launch_bounds__(256) psb_window_stats_kernel(const __half* __restrict__ X,
+                                                              const int4* __restrict__ change, int cap, int F,
+                                                              double* __restrict__ sums, float* __restrict__ inv_std) {
+    __shared__ double part[8][128][2];
+    const int w = blockIdx.y, warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int f0 = blockIdx.x * 128 + 4 * lane;                  // first of this lane's 4 features
+    const bool live = f0 < F;                                    // (F % 4 == 0 is checked on the host)
+    const int4 ch = change[w];
+    const int old_head = ch.x, old_count = ch.y, added = ch.z, new_count = ch.w;
+    const bool full = added < 0 || added > cap - old_count || new_count > old_count + added;
+    // unwrapped coordinates: old window [oh - oc, oh), new window [nh - nc, nh) with nh = oh + added
+    const int oh = old_head, nh = old_head + (added > 0 ? added : 0);
+    int leave_lo = oh - old_count, leave_hi = min(oh, nh - new_count);       // rows that left
+    int enter_lo = max(oh, nh - new_count), enter_hi = nh;                   // rows that entered
+    if (full) leave_lo = leave_hi = 0, enter_lo = nh - new_count;
+    double s1[4] = {0.0, 0.0, 0.0, 0.0}, s2[4] = {0.0, 0.0, 0.0, 0.0};
+    const __half* base = X + (size_t)w * cap * F + f0;
+    auto walk = [&](int lo, int hi, double sign) {
+        for (int u0 = lo + warp; u0 < hi; u0 += 32) {           // 4 rows of this warp in flight
+            uint2 raw[4];
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                const int u = u0 + 8 * k;
+                int slot = u % cap;
+                if (slot < 0) slot += cap;
+                raw[k] = (u < hi && live) ? *(const uint2*)(base + (size_t)slot * F) : make_uint2(0u, 0u);
+            }
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                const float2 a = __half22float2(*(const __half2*)&raw[k].x), b = __half22float2(*(const __half2*)&raw[k].y);
+                const double x[4] = {(double)a.x, (double)a.y, (double)b.x, (double)b.y};
+#pragma unroll
+                for (int e = 0; e < 4; ++e) s1[e] += sign * x[e], s2[e] += sign * x[e] * x[e];
+            }
+        }
+    };
+    walk(leave_lo, leave_hi, -1.0);
+    walk(enter_lo, enter_hi, 1.0);
+#pragma unroll
+    for (int e = 0; e < 4; ++e) part[warp][4 * lane + e][0] = s1[e], part[warp][4 * lane + e][1] = s2[e];
+    __syncthreads();
+    if (threadIdx.x < 128) {
+        const int f = blockIdx.x * 128 + threadIdx.x;
+        if (f < F) {
+            double2* sp = (double2*)sums + ((size_t)w * F + f);
+            double2 acc = full ? make_double2(0.0, 0.0) : *sp;
+#pragma unroll
+            for (int g = 0; g < 8; ++g) acc.x += part[g][threadIdx.x][0], acc.y += part[g][threadIdx.x][1];
+            *sp = acc;
+            const double n = (double)new_count;
+            const double var = new_count > 1 ? (acc.y - acc.x * acc.x / n) / (n - 1.0) : 0.0;
+            inv_std[(size_t)w * F + f] = var > 1e-12 ? (float)(1.0 / sqrt(var)) : 0.f;
+        }
+    }
+}
+
+int psb_launch_window_stats(const void* d_X, const int* d_change, int num_workers, int cap, int F, double* d_sums,
+                            float* d_inv_std, cudaStream_t stream) {
+    if (num_workers <= 0) return 0;
+    psb_window_stats_kernel<<<dim3((F + 127) / 128, num_workers), 256, 0, stream>>>(
+        (const __half*)d_X, (const int4*)d_change, cap, F, d_sums, d_inv_std);
+    PSB_CHECK_CUDA(cudaGetLastError());
+    return 0;
 }
 
 __global__ void psb_apply_delta_kernel(float* __restrict__ w, const float* __restrict__ delta, float lr, int n4,

@@ -150,7 +150,11 @@ __device__ bool simt_clock(const PsbSolver& sv, const CommCtx& cx, int clock, in
     }
 
     // ---- standardisation statistics (unbiased sample std over the window)
-    feature_inv_std(Xw, start, count, cap, F, sv.standardize, inv);
+    if (sv.standardize && sv.inv_std) {      // statistics maintained at ingestion time (psb_window_stats_update)
+        for (int f = threadIdx.x; f < F; f += blockDim.x) inv[f] = sv.inv_std[(size_t)w * F + f];
+    } else {
+        feature_inv_std(Xw, start, count, cap, F, sv.standardize, inv);
+    }
     __syncthreads();
     const long long t_stats = clock64();
 

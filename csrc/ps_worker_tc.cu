@@ -790,7 +790,12 @@ psb_worker_tc_kernel(const __grid_constant__ CUtensorMap tmX, PsbSolver sv, Comm
         bool have_f0 = false;
         double f0 = 0.0;
         PSB_TRACE(2);
-        if (sv.standardize) {
+        if (sv.standardize && sv.inv_std) {
+            // statistics maintained at ingestion time (psb_window_stats_update): no statistics pass, the first
+            // evaluation is an ordinary one at the scaled start point
+            for (int f = tid; f < F; f += blockDim.x) sh.inv()[f] = sv.inv_std[(size_t)w * F + f];
+            __syncthreads();
+        } else if (sv.standardize) {
             f0 = ev.eval_first_fused(w0, v.g);
             have_f0 = !psb_tc_need_redo;
         } else {

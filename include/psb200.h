@@ -60,6 +60,9 @@ typedef struct PsbSolver {
     int standardize;               /* Spark standardization=true semantics                  */
     int center;                    /* centre coefficients / intercepts across classes       */
     float sgd_lr;
+    const float* inv_std;          /* optional (device): precomputed 1/std per worker and feature, [num_workers][F],
+                                      kept current by psb_window_stats_update; NULL: the kernel computes the
+                                      statistics of the window itself, fused into its first pass              */
 } PsbSolver;
 
 /* Peer-memory block of one rank.  The same layout lives on every GPU; `peers[q]` is
@@ -247,6 +250,17 @@ int psb_ring_store_bitmap(const uint32_t* d_bitmap, const int* d_row_off, const 
 int psb_ring_store_palette(const uint32_t* d_bitmap, const int* d_row_off, const void* d_payload,
                            const int* d_labels_in, const int* d_worker_slot, int n, void* d_X, int* d_labels,
                            int cap, int num_features, void* stream);
+
+/* Per-feature statistics of every worker's window, maintained incrementally at ingestion time (Spark recomputes
+ * them on every fit, LogisticRegressionTaskSpark.java:179-184 with standardization=true; the window of a streaming
+ * buffer changes by a few rows per iteration).  d_change [num_workers][4] ints: {old_head, old_count, rows_added,
+ * new_count}; the new head is (old_head + rows_added) mod cap.  The kernel subtracts the rows that left the window
+ * and adds the rows that entered it — both must still be in the ring, i.e. rows_added <= cap - old_count; a worker
+ * whose change says rows_added < 0 (or violates that) is recomputed from its whole new window.  d_sums
+ * [num_workers][F][2] doubles (sum, sum of squares; exact products of fp16 values), d_inv_std [num_workers][F]
+ * floats out: 1/std (unbiased), 0 for constant columns. */
+int psb_window_stats_update(const void* d_X, const int* d_change, int num_workers, int cap, int num_features,
+                            double* d_sums, float* d_inv_std, void* stream);
 
 /* n host -> device copies on `stream` with one call (pinned sources for asynchronous copies) */
 int psb_h2d_copies(int n, void* const* d_dst, const void* const* h_src, const size_t* bytes, void* stream);

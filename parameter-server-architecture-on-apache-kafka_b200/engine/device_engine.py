@@ -46,13 +46,17 @@ class DeviceEngine:
                  device: Optional[torch.device] = None, w0: Optional[np.ndarray] = None, stage_rows: int = 0,
                  stage_sets: int = 3, spin_limit_cycles: int = 20_000_000_000, async_granularity: str = "rank",
                  groups: int = 1, max_clocks_per_launch: int = 64, external_block: Optional[int] = None,
-                 home_remote: bool = False, ring_spare_rows: int = 0):
+                 home_remote: bool = False, ring_spare_rows: int = 0, stats_at_ingest: Optional[bool] = None):
         if not torch.cuda.is_available():
             raise native.NativeError("DeviceEngine needs a CUDA device")
         if async_granularity not in ("rank", "worker"):
             raise ValueError("async_granularity must be 'rank' or 'worker'")
         if groups < 1 or workers_per_rank % groups:
             raise ValueError(f"groups ({groups}) must divide workers_per_rank ({workers_per_rank})")
+        if groups > 1 and cfg.consistency_model > 0:
+            # gated workers wait on each other inside the kernel: they must be ONE launch per GPU (nothing guarantees
+            # that separate launches run at the same time)
+            raise ValueError("bounded delay runs the workers of a GPU as one launch: groups must be 1")
         native.lib()
         self.cfg, self.W, self.rank, self.world, self.impl = cfg, workers_per_rank, rank, world, impl
         self.async_granularity, self.groups, self.home_remote = async_granularity, groups, bool(home_remote)
@@ -74,6 +78,16 @@ class DeviceEngine:
         # commit writes the other one
         self._win = [torch.zeros((self.W, 2), dtype=torch.int32, device=dev) for _ in range(2)]
         self._win_i = 0
+        # Standardisation statistics kept current at ingestion time (psb_window_stats_update) when the rings have spare
+        # slots (the rows that leave a window are then still in the ring when the batch that pushes them out has been
+        # stored); otherwise the worker kernel computes them itself, fused into its first pass.  Tables flip with `win`.
+        # (pays when clocks outnumber arriving batches — the reference's regime: seconds between rows, the buffers
+        # unchanged for most clocks; with a batch per clock the fused pass is as cheap.)  Default: on with spare slots.
+        want = spare > 0 if stats_at_ingest is None else bool(stats_at_ingest)
+        self.stats_at_ingest = bool(want and spare > 0 and cfg.standardize and F % 4 == 0)
+        if self.stats_at_ingest:
+            self.stat_sums = torch.zeros((self.W, F, 2), dtype=torch.float64, device=dev)
+            self._inv = [torch.zeros((self.W, F), dtype=torch.float32, device=dev) for _ in range(2)]
         self._commits_since_step = 0
         self._step_done = [torch.cuda.Event(), torch.cuda.Event()]    # completion of the last two steps
         self._steps = 0
@@ -120,6 +134,8 @@ class DeviceEngine:
         S = self.stage_sets = max(2, int(stage_sets))
         self.stage_ws_host = [torch.zeros((self.stage_rows, 2), dtype=torch.int32).pin_memory() for _ in range(S)]
         self.stage_win_host = [torch.zeros((self.W, 2), dtype=torch.int32).pin_memory() for _ in range(S)]
+        self.stage_change_host = [torch.zeros((self.W, 4), dtype=torch.int32).pin_memory() for _ in range(S)]
+        self.stage_change_dev = [torch.zeros((self.W, 4), dtype=torch.int32, device=dev) for _ in range(S)]
         self.stage_dev = [torch.zeros((self.stage_rows, F), dtype=torch.float16, device=dev) for _ in range(S)]
         self.stage_lab_dev = [torch.zeros(self.stage_rows, dtype=torch.int32, device=dev) for _ in range(S)]
         self.stage_ws_dev = [torch.zeros((self.stage_rows, 2), dtype=torch.int32, device=dev) for _ in range(S)]
@@ -219,6 +235,7 @@ class DeviceEngine:
         self.win_host[:, 1] = n
         for t in self._win:
             t.copy_(self.win_host)
+        self._recompute_stats()
 
     def ingest(self, rows_f16, labels: Optional[torch.Tensor], workers: np.ndarray,
                now_ms: Optional[np.ndarray] = None, wait: bool = True) -> None:
@@ -264,8 +281,12 @@ class DeviceEngine:
         self.stage_max_rows[j] = int(np.bincount(workers, minlength=1).max()) if n else 0
 
         def assign():
+            ch = self.stage_change_host[j].numpy()
+            ch[:, 0:2] = self.win_host.numpy()                   # windows before the batch
+            ch[:, 2] = np.bincount(workers, minlength=self.W)[: self.W] if n else 0
             native.buffers_on_batch(buffers, workers, now_ms, self.stage_ws_host[j].numpy(), self.win_host.numpy(),
                                     handles=handles)
+            ch[:, 3] = self.win_host.numpy()[:, 1]               # ... and the window sizes after it
             self.stage_win_host[j].copy_(self.win_host)
 
         if self._slot_thread is None:
@@ -347,6 +368,7 @@ class DeviceEngine:
                            (self.stage_ws_dev[j], self.stage_ws_host[j], n * 8)], stream=s)
         native.ring_store_palette(int(bitmap), int(row_off), int(payload), int(labels), self.stage_ws_dev[j], n, self.X,
                                   self.labels, self.cap, self.F, stream=s)
+        self._update_stats(j, s)
         self.store_done[j].record(s)
         self.ingest_done.record(s)
         self.kernel_launches += 1
@@ -357,6 +379,27 @@ class DeviceEngine:
         if wait:
             torch.cuda.current_stream().wait_event(self.ingest_done)
         return s
+
+    def _update_stats(self, j: int, s) -> None:
+        """Behind the store of staging set j (stream s): subtract the rows that left each window, add the rows that
+        entered it, refresh 1/std in the table that flipped with `win`."""
+        if not self.stats_at_ingest:
+            return
+        native.h2d_copies([(self.stage_change_dev[j], self.stage_change_host[j], self.W * 16)], stream=s)
+        native.window_stats_update(self.X, self.stage_change_dev[j], self.W, self.cap, self.F, self.stat_sums,
+                                   self._inv[self._win_i], stream=s)
+        self.kernel_launches += 1
+
+    def _recompute_stats(self) -> None:
+        """Statistics of every window from scratch (after fill / load_state_dict), into both tables."""
+        if not self.stats_at_ingest:
+            return
+        ch = torch.zeros((self.W, 4), dtype=torch.int32)
+        ch[:, 0], ch[:, 2], ch[:, 3] = self.win_host[:, 0], -1, self.win_host[:, 1]
+        ch = ch.to(self.device)
+        for t in self._inv:
+            native.window_stats_update(self.X, ch, self.W, self.cap, self.F, self.stat_sums, t)
+        torch.cuda.current_stream().synchronize()
 
     def ingest_commit(self, wait: bool = True, overlap: bool = False) -> None:
         """Second half: store the oldest begun batch into the rings — after the step that is running (default), or,
@@ -402,6 +445,7 @@ class DeviceEngine:
         else:
             native.ring_store_dense(self.stage_dev[j], self.stage_lab_dev[j], self.stage_ws_dev[j], n, self.X,
                                     self.labels, self.cap, self.F, stream=s)
+        self._update_stats(j, s)
         self.store_done[j].record(s)
         self.ingest_done.record(s)
         self.kernel_launches += 1
@@ -431,6 +475,7 @@ class DeviceEngine:
         if num_clocks != 1:
             raise ValueError("several clocks per launch need async_granularity='worker' and consistency_model != 0")
         comm = self._comm(mode)
+        self.solver.inv_std = self._inv[self._win_i].data_ptr() if self.stats_at_ingest else None
         native.worker_step(self.solver, comm, self.W, self.impl, self.X, self.labels, self.win,
                            self.w0 if mode == native.COMM_NONE else None,
                            self.delta if mode == native.COMM_NONE else None,
@@ -465,6 +510,7 @@ class DeviceEngine:
         comm.worker_base, comm.total_workers = self.rank * self.W + lo, self.total_workers
         comm.delay_worker, comm.delay_cycles = self.delay_worker, self.delay_cycles
         comm.hist = self.hist[g].data_ptr()
+        self.solver.inv_std = self._inv[self._win_i][lo:lo + gs].data_ptr() if self.stats_at_ingest else None
         st = torch.cuda.current_stream() if stream is False else (stream or self.group_streams[g]
                                                                   or torch.cuda.current_stream())
         if st != torch.cuda.current_stream():
@@ -629,6 +675,7 @@ class DeviceEngine:
         self.win_host.copy_(sd["win"])
         for t in self._win:
             t.copy_(self.win_host)
+        self._recompute_stats()
         for b, st in zip(self.buffers, sd["buffers"]):
             b.set_state(st)
         self._buf_handles = None
@@ -693,8 +740,11 @@ class VirtualCluster:
             e.step()
 
     def step_concurrent(self, num_clocks: int = 1) -> None:
-        """Per-worker mode: every virtual rank's launch on its own stream, so that the kernels are on the device
-        together and really wait on each other's clock words (all worker CTAs must fit on the GPU at once)."""
+        """Per-worker mode, eventual consistency: every virtual rank's launch on its own stream.  (Bounded delay makes
+        the launches wait on one another; ranks that share a GPU are not guaranteed to run at the same time, so that
+        model is exercised with one rank per GPU.)"""
+        if self.engines[0].cfg.consistency_model > 0:
+            raise native.NativeError("step_concurrent: bounded delay needs one rank per GPU")
         if not hasattr(self, "_streams"):
             self._streams = [[torch.cuda.Stream() for _ in range(e.groups)] for e in self.engines]
         cur = torch.cuda.current_stream()

@@ -33,7 +33,8 @@ class NativeError(RuntimeError):
 
 class PsbSolver(C.Structure):
     _fields_ = [("num_features", C.c_int), ("num_class_rows", C.c_int), ("cap", C.c_int), ("solver", C.c_int),
-                ("max_iter", C.c_int), ("standardize", C.c_int), ("center", C.c_int), ("sgd_lr", C.c_float)]
+                ("max_iter", C.c_int), ("standardize", C.c_int), ("center", C.c_int), ("sgd_lr", C.c_float),
+                ("inv_std", C.c_void_p)]
 
 
 class PsbSparseComm(C.Structure):
@@ -119,6 +120,7 @@ def lib() -> C.CDLL:
     L.psb_pack_bitmap_dense.restype = C.c_longlong
     L.psb_pack_bitmap_dense.argtypes = [vp, C.c_longlong, C.c_int, vp, vp, vp]
     L.psb_h2d_copies.argtypes = [C.c_int, vp, vp, vp, vp]
+    L.psb_window_stats_update.argtypes = [vp, ip, C.c_int, C.c_int, C.c_int, vp, fp, vp]
     L.psb_d2h_copy.argtypes = [vp, vp, C.c_size_t, vp]
     L.psb_d2d_copy.argtypes = [vp, vp, C.c_size_t, vp]
     L.psb_pack_palette_dense.restype = C.c_longlong
@@ -504,6 +506,11 @@ def evaluate_models(X, labels, n: int, w, w_add, model_stride: int, num_models: 
     """Weighted F1 / accuracy of `num_models` weight sets in one launch (conf int32[M, 64], out float32[M, 2])."""
     check(lib().psb_eval_models(_ptr(X), _ptr(labels), n, _ptr(w), _ptr(w_add), model_stride, num_models, num_features,
                                 num_class_rows, _ptr(conf), _ptr(out), impl, _stream(stream)), "psb_eval_models")
+
+
+def window_stats_update(X, change, num_workers: int, cap: int, num_features: int, sums, inv_std, stream=None) -> None:
+    check(lib().psb_window_stats_update(_ptr(X), _ptr(change), num_workers, cap, num_features, _ptr(sums),
+                                        _ptr(inv_std), _stream(stream)), "psb_window_stats_update")
 
 
 def ring_scatter(stage, n: int, stride_words: int, X, labels, cap: int, num_features: int, stream=None) -> None:

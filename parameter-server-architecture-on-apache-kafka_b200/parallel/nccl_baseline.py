@@ -27,6 +27,7 @@ class NcclBaselineEngine(DeviceEngine):
 
     def step(self, mode=None) -> None:
         comm = native.comm_none()
+        self.solver.inv_std = self._inv[self._win_i].data_ptr() if self.stats_at_ingest else None
         native.worker_step(self.solver, comm, self.W, self.impl, self.X, self.labels, self.win, self.w_dev, self.delta,
                            self.loss, self.info, self.scratch)
         torch.sum(self.delta, dim=0, out=self.sum_delta)

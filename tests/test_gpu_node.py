@@ -164,9 +164,10 @@ def test_checkpoint_restores_rings_buffer_statistics_and_relaxed_shards(tmp_path
         for e in (a, c):
             e.step()
         la, lc = a.read_loss().numpy().copy(), c.read_loss().numpy().copy()
-        tol = 1e-6 if model == 0 else 2e-3            # relaxed: the two workers' REDs land in any order
+        tol = 2e-5 if model == 0 else 2e-3            # the workers' REDs land in any order (float sums)
         assert np.allclose(la, lc, rtol=tol, atol=tol)
-        assert np.abs(a.weights().cpu().numpy() - c.weights().cpu().numpy()).max() < max(tol, 1e-6)
+        wa = a.weights().cpu().numpy()
+        assert np.abs(wa - c.weights().cpu().numpy()).max() < tol * max(1.0, np.abs(wa).max())
         a.close(), c.close()
 
 
@@ -280,3 +281,40 @@ def test_store_into_spare_ring_slots_while_a_step_runs_gives_the_serialized_resu
     assert np.allclose(out[0][0], out[1][0], rtol=3e-4, atol=3e-5)
     assert np.abs(out[0][1] - out[1][1]).max() < 3e-4 * max(1e-2, np.abs(out[0][1]).max())
     assert out[0][2][:, 1].tolist() == [cap] * W               # the windows filled up and wrapped: (steps+1)*r > cap
+
+
+def test_window_statistics_kept_at_ingestion_follow_growing_shrinking_and_wrapping_windows():
+    """psb_window_stats_update: after every batch the 1/std table equals the statistics of the rows currently in
+    each worker's window (unbiased std, 0 for constant columns), also when the dynamic buffer grows, shrinks and wraps."""
+    from psb200.config import PSConfig
+    from psb200.data import random_csr
+    from psb200.engine.device_engine import DeviceEngine
+    F, cap, W = 128, 256, 3
+    cfg = PSConfig(num_workers=W, num_features=F, max_buffer_size=cap, min_buffer_size=32, buffer_size_coefficient=0.3)
+    e = DeviceEngine(cfg, W, impl=0, stage_rows=1024, ring_spare_rows=128)
+    assert e.stats_at_ingest and e.cap == cap + 128
+    rng = np.random.default_rng(0)
+    t = 0.0
+    for step, (n, gap_ms) in enumerate([(90, 10.0), (128, 10.0), (300, 5.0), (60, 400.0), (45, 2000.0), (128, 20.0), (7, 20.0)]):
+        b = random_csr(n * W, F, 20, seed=step)
+        dense = b.to_dense(np.float16)
+        dense[:, 5] = 0.25                                        # a constant non-zero column -> 1/std = 0
+        workers = np.repeat(np.arange(W, dtype=np.int32), n)
+        times = t + np.tile(np.arange(n) * gap_ms, W)
+        t += n * gap_ms
+        e.ingest(torch.from_numpy(dense).pin_memory(), torch.from_numpy(b.labels.astype(np.int32)).pin_memory(),
+                 workers, times)
+        torch.cuda.synchronize()
+        X = e.X.cpu().numpy().astype(np.float64)
+        inv = e._inv[e._win_i].cpu().numpy()
+        for w in range(W):
+            head, count = e.win_host[w].tolist()
+            slots = [(head - count + i) % e.cap for i in range(count)]
+            rows = X[w, slots]
+            var = rows.var(axis=0, ddof=1) if count > 1 else np.zeros(F)
+            ref = np.where(var > 1e-12, 1.0 / np.sqrt(np.maximum(var, 1e-300)), 0.0)
+            assert np.allclose(inv[w], ref, rtol=1e-5, atol=1e-6), (step, w, count)
+            assert inv[w, 5] == 0.0
+    counts = e.win_host[:, 1].tolist()
+    assert all(32 <= c <= cap for c in counts)
+    e.close()

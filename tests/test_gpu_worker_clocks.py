@@ -91,27 +91,24 @@ def test_one_worker_per_worker_mode_equals_the_sequential_engine(impl):
         a.close(), b.close()
 
 
-@pytest.mark.parametrize("model", [2, -1])
-def test_two_virtual_ranks_gate_each_other_through_the_replicated_clock_table(model):
-    """Two ranks' launches on two streams of one GPU: rank 1 holds the straggler, rank 0's workers must stop k ahead."""
+def test_two_virtual_ranks_share_one_replicated_clock_table():
+    """Two ranks' launches on two streams of one GPU, eventual consistency (nobody waits, so the two launches need
+    not overlap; launches that wait on one another must not share a GPU — the bounded-delay gate across ranks is
+    tested on real GPUs, tests/test_gpu_multi.py): every worker publishes its clocks into BOTH blocks."""
     from psb200.engine.device_engine import VirtualCluster
     clocks, wpr = 10, 2
-    cfg = PSConfig(num_workers=2 * wpr, num_features=F, consistency_model=model, max_buffer_size=CAP, min_buffer_size=16)
+    cfg = PSConfig(num_workers=2 * wpr, num_features=F, consistency_model=-1, max_buffer_size=CAP, min_buffer_size=16)
     vc = VirtualCluster(cfg, 2, wpr, 1, async_granularity="worker", spin_limit_cycles=4_000_000_000)
     try:
         _fill(vc.engines)
-        for e in vc.engines:
-            e.inject_delay(wpr, SLOW)                         # global worker id 2 = rank 1's first worker
         vc.step_concurrent(num_clocks=clocks)
         hs = [e.read_hist() for e in vc.engines]
         assert all(e.status() == 0 for e in vc.engines)
         for e in vc.engines:
             assert (e.worker_clocks() == clocks).all()        # both copies of the table are complete
-        lag = np.concatenate([h["lag"] for h in hs], axis=1)
-        if model > 0:
-            assert lag.max() == model and hs[0]["lag"].max() == model
-        else:
-            assert hs[0]["lag"].max() >= clocks - 3
+        assert all(np.isfinite(h["loss"]).all() for h in hs)
+        w = [e.weights().cpu().numpy() for e in vc.engines]   # each rank reads all shards from their owners
+        assert np.abs(w[0] - w[1]).max() < 1e-6 and np.abs(w[0]).max() > 0
     finally:
         vc.close()
 
