@@ -6,7 +6,10 @@ the reference designs for (``KeyRange`` in every message, ``BaseMessage.java:24-
 (``ServerApp.java:38``, ``README.md:115-119``, future work ``README.md:333``).  A worker step is one SGD
 step on a CSR batch (``psb_sparse_step``): the pull is the forward's operand loads from the owning shards,
 the push is a 16-byte RED into them.  Sequential consistency separates readers from writers with a
-device-side phase barrier over peer memory; eventual consistency fuses both into one kernel.
+device-side phase barrier over peer memory; eventual consistency fuses both into one kernel; bounded delay k
+is that one kernel behind the clock gate ``min over ranks of completed steps >= v - k``
+(``MessageTracker.java:69-79``), evaluated in the kernel on the ranks' step counters in peer memory —
+independent of the model size, as in the reference (``ServerProcessor.java:126-131``).
 """
 from __future__ import annotations
 
@@ -40,8 +43,7 @@ class SparseShardedEngine:
         self.rank, self.world = rank, world
         self.num_workers = num_workers_total or world
         self.eta, self.model = eta, consistency_model
-        if consistency_model > 0:
-            raise ValueError("the sharded sparse path implements sequential (0) and eventual (-1) consistency")
+        self.host_delay_s = 0.0                # straggler injection (tests, tools/straggler_sweep.py)
         self.device = device or torch.device("cuda", torch.cuda.current_device())
         self.Fs = (num_features + world - 1) // world
         self.shard_bytes = (self.Fs + 1) * 32
@@ -118,8 +120,20 @@ class SparseShardedEngine:
             self.step_scatter(batch)
         else:
             self.loss.zero_()
-            self._launch(3, 0, 0, batch)
+            if self.host_delay_s:
+                import time
+                time.sleep(self.host_delay_s)
+            v = self.step_index
+            if self.model > 0 and self.world > 1:
+                # bounded delay: start step v only when every rank has completed step v - k; publish v + 1 at the end
+                self._launch(3, max(0, v - self.model), v + 1, batch)
+            else:
+                self._launch(3, 0, 0, batch)
             self.step_index += 1
+
+    def completed_steps(self) -> np.ndarray:
+        """Steps completed by every rank as this rank sees them (the bounded-delay clock words; zeros otherwise)."""
+        return _view(self.ctrl, self.world, self.device, torch.int32).cpu().numpy()
 
     def mean_loss(self, batch: DeviceCSR) -> float:
         return float(self.loss.item()) / batch.n

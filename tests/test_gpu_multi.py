@@ -72,3 +72,17 @@ def test_node_app_on_two_gpus_writes_server_and_worker_rows(tmp_path, model):
     assert len(s) == (6 if model == 0 else 3) and s[-1, 2] == 5 and s[-1, 4] > 0.2 and np.all(np.isfinite(s[:, 4]))
     assert len(w0) == len(w1) == 12 and set(w0[:, 1]) == {0, 1} and set(w1[:, 1]) == {2, 3}
     assert np.all(np.isfinite(w0[:, 3])) and np.all(np.isfinite(w1[:, 3]))
+
+
+@pytest.mark.parametrize("model", [2, -1])
+def test_sharded_sparse_path_bounded_delay_and_eventual_with_a_straggler(model):
+    """Bounded delay on the 2^24-style sharded model (the reference's gate does not depend on the model size,
+    ServerProcessor.java:126-131): fast ranks advance at the straggler's pace after k free steps; eventual ranks do not."""
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    port = 29100 + (os.getpid() + 11 * (model + 2)) % 150
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2",
+                        "--master-addr", "127.0.0.1", "--master-port", str(port),
+                        os.path.join(ROOT, "tools", "mp_sparse_bounded.py"), "--model", str(model)],
+                       capture_output=True, text=True, timeout=600, cwd=ROOT)
+    assert r.returncode == 0 and "-> OK" in r.stdout, r.stdout[-2000:] + r.stderr[-2000:]
