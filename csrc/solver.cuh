@@ -366,10 +366,11 @@ __device__ SolveResult local_solve_cached(Eval& ev, SolveVecs& v, int max_iter, 
     return r;
 }
 
-// On entry v.x holds the start point.  On exit v.x holds the result.
+// On entry v.x holds the start point.  On exit v.x holds the result.  hist_cap: pairs kept (<= PSB_HIST); the pair
+// buffers at index >= hist_cap are never touched (a kernel may park other data there).
 template <class Eval>
 __device__ SolveResult local_solve(Eval& ev, SolveVecs& v, int solver, int max_iter, float sgd_lr, double* red,
-                                   bool have_f0 = false, double f0 = 0.0) {
+                                   bool have_f0 = false, double f0 = 0.0, int hist_cap = PSB_HIST) {
     SolveResult r;
     r.evals = 0, r.iterations = 0, r.status = 0;
     // have_f0: the caller already evaluated loss (f0) and gradient (in v.g) at the start point v.x
@@ -401,13 +402,13 @@ __device__ SolveResult local_solve(Eval& ev, SolveVecs& v, int solver, int max_i
             break;
         }
         // ---- accept: history (rotate, newest first), x <- xt, g <- gt
-        float* s_last = v.s[PSB_HIST - 1];
-        float* y_last = v.y[PSB_HIST - 1];
-        for (int i = PSB_HIST - 1; i > 0; --i) v.s[i] = v.s[i - 1], v.y[i] = v.y[i - 1];
+        float* s_last = v.s[hist_cap - 1];
+        float* y_last = v.y[hist_cap - 1];
+        for (int i = hist_cap - 1; i > 0; --i) v.s[i] = v.s[i - 1], v.y[i] = v.y[i - 1];
         v.s[0] = s_last, v.y[0] = y_last;
         vec_pair_update(v.s[0], v.y[0], v.xt, v.x, v.gt, v.g, v.n4);
         __syncthreads();
-        if (hist < PSB_HIST) ++hist;
+        if (hist < hist_cap) ++hist;
         float* p;
         p = v.x, v.x = v.xt, v.xt = p;
         p = v.g, v.g = v.gt, v.gt = p;

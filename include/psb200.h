@@ -141,6 +141,18 @@ int psb_worker_step(const PsbSolver* s, const PsbComm* comm, int num_workers, in
                     const float* d_w_in, float* d_delta, float* d_loss, int* d_info,
                     float* d_scratch, void* stream);
 
+/* The same step on SPARSE-row buffers (ELL rings: d_idx [num_workers][cap][max_nnz] int32 feature ids, d_val the
+ * fp16 values, d_nnz [num_workers][cap] non-zeros per slot): any num_features, no densification — the reference
+ * fits on sparse vectors of any width (LogisticRegressionTaskSpark.java:146-184).  Same solver, same comm modes
+ * (including PSB_COMM_WORKER and several clocks per launch); the L-BFGS memory is PSB_HIST - 1 pairs here. */
+int psb_worker_step_csr(const PsbSolver* s, const PsbComm* comm, int num_workers, int max_nnz, const int* d_idx,
+                        const void* d_val, const int* d_nnz, const int* d_labels, const int* d_win,
+                        const float* d_w_in, float* d_delta, float* d_loss, int* d_info, float* d_scratch,
+                        void* stream);
+/* staged sparse rows (the record format of psb_ring_scatter) -> ELL ring slots; rows keep their first max_nnz non-zeros */
+int psb_ring_store_ell(const uint32_t* d_stage, int n, int stride_words, int* d_idx, void* d_val, int* d_nnz,
+                       int* d_labels, int cap, int max_nnz, int num_features, void* stream);
+
 /* Worker CTAs of this shape that fit on the current device at the same time when `num_workers` are launched
  * together.  Bounded-delay PSB_COMM_WORKER launches spin on each other's clock words inside the kernel, so all
  * workers that can be in flight on a GPU together (all groups, all streams) must fit; psb_worker_step checks its

@@ -101,6 +101,9 @@ def lib() -> C.CDLL:
     L.psb_worker_step.argtypes = [C.POINTER(PsbSolver), C.POINTER(PsbComm), C.c_int, C.c_int, vp, ip, ip, fp, fp, fp,
                                   ip, fp, vp]
     L.psb_apply_delta.argtypes = [fp, fp, C.c_float, C.c_int, C.c_int, vp]
+    L.psb_worker_step_csr.argtypes = [C.POINTER(PsbSolver), C.POINTER(PsbComm), C.c_int, C.c_int, ip, vp, ip, ip, ip, fp,
+                                      fp, fp, ip, fp, vp]
+    L.psb_ring_store_ell.argtypes = [vp, C.c_int, C.c_int, ip, vp, ip, ip, C.c_int, C.c_int, C.c_int, vp]
     L.psb_eval.argtypes = [vp, ip, C.c_int, fp, C.c_int, C.c_int, ip, fp, C.c_int, vp]
     L.psb_eval_finalize.argtypes = [ip, fp, vp]
     L.psb_sparse_step.argtypes = [C.POINTER(PsbSparseComm), C.c_int, C.c_uint, C.c_uint, vp, vp, vp, vp, C.c_int, C.c_int,
