@@ -1,5 +1,5 @@
 # Build / test / bench shortcuts (the reference builds a fat jar with `gradle build`, build.gradle:19-30).
-.PHONY: build test test-gpu bench clean mock-data
+.PHONY: build test test-gpu bench clean mock-data tsan sass
 build:
 	./build.sh
 test: build
@@ -12,3 +12,12 @@ mock-data:
 	python tools/make_mock_data.py
 clean:
 	rm -rf build parameter-server-architecture-on-apache-kafka_b200/ops/libpsb200.so
+# ThreadSanitizer run of the C++ host runtime (producer thread vs consumer / slot-assignment threads); host only
+tsan:
+	mkdir -p build
+	g++ -std=c++17 -O1 -g -fsanitize=thread -fPIE -pie -x c++ -I/usr/local/cuda/include csrc/host_runtime.cpp \
+	    tools/tsan_host_runtime.cpp tools/tsan_stubs.cpp -o build/tsan_host_runtime -lpthread
+	TSAN_OPTIONS="halt_on_error=1 second_deadlock_stack=1" ./build/tsan_host_runtime
+# full SASS listing of every kernel + mnemonic summary under profiles/sass (no GPU needed)
+sass: build
+	python tools/dump_sass.py
