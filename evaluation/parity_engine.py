@@ -95,6 +95,9 @@ def main():
         tag = {0: "sequential", 10: "bounded10", -1: "eventual"}[model]
         for role in ("server", "worker"):
             shutil.copy(os.path.join(tmp, f"logs-{role}.csv"), os.path.join(HERE, "logs", f"parity_engine_{tag}_{role}.csv"))
+            if os.path.isdir(os.path.join(ROOT, "gpurun_out")):       # on a gpurun box only gpurun_out/ travels back
+                shutil.copy(os.path.join(tmp, f"logs-{role}.csv"),
+                            os.path.join(ROOT, "gpurun_out", f"parity_engine_{tag}_{role}.csv"))
         s = parse_log(os.path.join(tmp, "logs-server.csv"), "server")
         k = min(len(s), len(ref["f1"]))
         d = np.abs(s[:k, 4] - ref["f1"][:k])
