@@ -54,11 +54,45 @@ class CudaBackend:
             self.test_X = None
         self.last_info = None
 
+    STAGE_ROWS = 256
+
     def store_row(self, worker: int, slot: int, idx: np.ndarray, val: np.ndarray, label: int) -> None:
-        dense = np.zeros(self.F, dtype=np.float16)
-        dense[idx] = val
-        self.X[worker, slot].copy_(torch.from_numpy(dense))
-        self.labels[worker, slot] = int(label)
+        """Rows are collected in pinned staging memory and stored into the rings by ONE copy + ONE store kernel
+        (``psb_ring_store_dense``) when a worker step needs them or the staging set is full."""
+        if not hasattr(self, "_stage"):
+            self._stage = torch.zeros((self.STAGE_ROWS, self.F), dtype=torch.float16).pin_memory()
+            self._stage_lab = torch.zeros(self.STAGE_ROWS, dtype=torch.int32).pin_memory()
+            self._stage_ws = torch.zeros((self.STAGE_ROWS, 2), dtype=torch.int32).pin_memory()
+            dev = self.X.device
+            self._stage_dev = torch.zeros((self.STAGE_ROWS, self.F), dtype=torch.float16, device=dev)
+            self._stage_lab_dev = torch.zeros(self.STAGE_ROWS, dtype=torch.int32, device=dev)
+            self._stage_ws_dev = torch.zeros((self.STAGE_ROWS, 2), dtype=torch.int32, device=dev)
+            self._staged = 0
+        k = self._staged
+        row = self._stage[k].numpy()
+        row[:] = 0
+        row[idx] = val
+        self._stage_lab[k] = int(label)
+        self._stage_ws[k, 0], self._stage_ws[k, 1] = int(worker), int(slot)
+        # an earlier staged row of the same slot is superseded (the store kernel writes the rows of a batch in parallel)
+        ws = self._stage_ws[:k].numpy()
+        if k:
+            ws[(ws[:, 0] == worker) & (ws[:, 1] == slot), 1] = -1
+        self._staged = k + 1
+        if self._staged == self.STAGE_ROWS:
+            self.flush_rows()
+
+    def flush_rows(self) -> None:
+        n = getattr(self, "_staged", 0)
+        if not n:
+            return
+        self._stage_dev[:n].copy_(self._stage[:n], non_blocking=True)
+        self._stage_lab_dev[:n].copy_(self._stage_lab[:n], non_blocking=True)
+        self._stage_ws_dev[:n].copy_(self._stage_ws[:n], non_blocking=True)
+        native.ring_store_dense(self._stage_dev, self._stage_lab_dev, self._stage_ws_dev, n, self.X, self.labels,
+                                self.cap, self.F)
+        torch.cuda.current_stream().synchronize()            # the pinned staging set is reused right away
+        self._staged = 0
 
     def snapshot(self) -> np.ndarray:
         return self.w_dev.cpu().numpy().reshape(self.layout.device_rows, 8).copy()
@@ -72,6 +106,7 @@ class CudaBackend:
         return Metrics(f1, acc)
 
     def worker_step(self, worker: int, weights: np.ndarray, slots: List[int], want_metrics: bool):
+        self.flush_rows()
         head = (slots[-1] + 1) % self.cap
         self.win[worker, 0], self.win[worker, 1] = head, len(slots)
         self.w_in.copy_(torch.from_numpy(np.ascontiguousarray(weights, dtype=np.float32).reshape(-1)))

@@ -193,21 +193,24 @@ def test_all_workers_local_models_scored_in_one_launch():
         e.close()
 
 
-@pytest.mark.parametrize("model", [0, -1, 3])
-def test_two_runner_processes_train_through_device_peer_memory(tmp_path, model):
+@pytest.mark.parametrize("model,worker_device,extra", [(0, 0, []), (-1, 0, []), (3, 0, []), (0, 1, []), (-1, 1, []),
+                                                       (0, 0, ["--free_running"])])
+def test_two_runner_processes_train_through_device_peer_memory(tmp_path, model, worker_device, extra):
     """WorkerAppRunner and ServerAppRunner as two processes (run.sh with BACKEND=cuda): the rendezvous hands over two
     CUDA IPC handles, rows travel through the INPUT_DATA topic in device memory, weights and gradients through the
     server's peer-memory block inside the worker kernels; both logs come out in the reference format."""
     import socket
+    if worker_device >= torch.cuda.device_count():
+        pytest.skip("needs a second GPU: the worker app on another device than the server's block")
     with socket.socket() as so:
         so.bind(("127.0.0.1", 0))
         port = so.getsockname()[1]
     addr = f"127.0.0.1:{port}"
     wcmd = [sys.executable, "-m", "psb200.apps.worker_app_runner", "-l", "-test", "synthetic:600", "--backend", "cuda",
-            "-max", "256", "--rendezvous", addr]
+            "-max", "256", "--rendezvous", addr, "--device", str(worker_device)]
     scmd = [sys.executable, "-m", "psb200.apps.server_app_runner", "-l", "-p", "0", "-training", "synthetic:3000", "-test",
             "synthetic:600", "--backend", "cuda", "--num_workers", "3", "-c", str(model), "--max_clock", "5",
-            "--rendezvous", addr, "--clocks_per_launch", "1"]
+            "--rendezvous", addr, "--clocks_per_launch", "1", *extra]
     wdir, sdir = tmp_path / "w", tmp_path / "s"
     wdir.mkdir(), sdir.mkdir()
     wp = subprocess.Popen(wcmd, env=ENV, cwd=wdir, stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True)
@@ -225,7 +228,10 @@ def test_two_runner_processes_train_through_device_peer_memory(tmp_path, model):
     srows, wrows = parse_log(s, "server"), parse_log(w, "worker")
     assert len(wrows) == 15 and sorted(set(wrows[:, 1])) == [0, 1, 2] and sorted(set(wrows[:, 2])) == [0, 1, 2, 3, 4]
     assert np.all(np.isfinite(wrows[:, 3])) and np.all((wrows[:, 4] > 0) & (wrows[:, 4] <= 1))    # local models scored
-    assert list(srows[:, 2]) == [0, 1, 2, 3, 4]            # a server row for every clock of worker 0 (Q6)
+    if extra:                                              # free running: the server logs the clocks it gets to see
+        assert 1 <= len(srows) <= 5 and srows[-1, 2] == 4 and np.all(np.diff(srows[:, 2]) > 0)
+    else:
+        assert list(srows[:, 2]) == [0, 1, 2, 3, 4]        # a server row for every clock of worker 0 (Q6)
     assert srows[-1, 4] > 0.2 and np.all(srows[:, 1] == -1) and np.all(srows[:, 3] == -1)
 
 
