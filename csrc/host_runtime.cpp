@@ -312,26 +312,104 @@ extern "C" int psb_buffer_set_state(void* bp, const double* state, int n) {
 // window of every worker that received a row.  `buffers` is an array of psb_buffer_create handles.
 // (Splitting the workers of a batch over a small thread pool was measured: 0.33 -> 0.8-1.2 ms for 37,888 events —
 //  the wake-ups cost more than the two divisions per event they spread.)
-extern "C" int psb_buffers_on_batch(void** buffers, int num_buffers, const int* workers, const double* now_ms, int n,
-                                    int* worker_slot, int* win) {
-    for (int i = 0; i < n; ++i) {
+// change (optional, [num_buffers][4]): {head before, count before, rows added, count after} per worker — what
+// psb_window_stats_update needs; max_rows_out (optional): the most rows any worker received.
+extern "C" int psb_buffers_on_batch2(void** buffers, int num_buffers, const int* workers, const double* now_ms, int n,
+                                     int* worker_slot, int* win, int* change, int* max_rows_out) {
+    static thread_local std::vector<int> added_tls;
+    added_tls.assign((size_t)num_buffers, 0);
+    int* const added = added_tls.data();                 // (no thread-local lookup inside the loops)
+    if (change)
+        for (int w = 0; w < num_buffers; ++w) {
+            const Buffer* b = (const Buffer*)buffers[w];
+            change[4 * w] = b->head, change[4 * w + 1] = b->count, change[4 * w + 2] = 0, change[4 * w + 3] = b->count;
+        }
+    // The events are grouped by worker first (stable counting sort: a worker's events keep their order, and different
+    // workers' buffers are independent), then every worker's events are processed in one tight loop with the
+    // buffer's state in locals — the same arithmetic as buffer_on_event, ~3x faster than visiting the buffers in
+    // arrival order (whose state the compiler has to reload after every store to the output tables).
+    static thread_local std::vector<int> order_tls, start_tls;
+    order_tls.resize((size_t)n), start_tls.assign((size_t)num_buffers + 1, 0);
+    int* const order = order_tls.data();
+    int* const start = start_tls.data();
+    static thread_local std::vector<int> first_tls;
+    first_tls.assign((size_t)num_buffers, -1);
+    int* const first = first_tls.data();
+    int runs = 0, distinct = 0;
+    for (int i = 0, prev = -1; i < n; ++i) {
         const int w = workers[i];
         if (w < 0 || w >= num_buffers) {
             psb_set_error("psb_buffers_on_batch: worker %d out of range", w);
             return PSB_E_INVALID;
         }
-        int head, count, target;
-        const int slot = buffer_on_event((Buffer*)buffers[w], now_ms[i], &head, &count, &target);
-        worker_slot[2 * i] = w, worker_slot[2 * i + 1] = slot;
+        if (w != prev) {
+            ++runs, prev = w;
+            if (first[w] < 0) first[w] = i, ++distinct;
+        }
+        ++start[w + 1];
+    }
+    const bool grouped = runs == distinct;               // every worker's events are already contiguous: no permutation
+    for (int w = 0; w < num_buffers; ++w) added[w] = start[w + 1], start[w + 1] += start[w];
+    if (!grouped)
+        for (int i = 0; i < n; ++i) order[start[workers[i]]++] = i;      // start[w] now = end of worker w's events
+    else
+        for (int w = 0; w < num_buffers; ++w) start[w] = start[w + 1];
+    for (int w = 0, lo = 0; w < num_buffers; lo = start[w], ++w) {
+        const int hi = start[w];
+        if (hi == lo) continue;
+        const int shift = grouped ? first[w] - lo : 0;   // grouped: event k of the sorted order is event k + shift
+        Buffer* b = (Buffer*)buffers[w];
+        const int min_size = b->min_size, max_size = b->max_size, ring = b->ring, window = b->window;
+        const double bc = (double)b->bc;
+        double* const deltas = b->deltas.data();
+        int n_deltas = b->n_deltas, pos = b->pos, head = b->head, count = b->count;
+        double total = b->total, last = b->last;
+        bool has_last = b->has_last;
+        for (int k = lo; k < hi; ++k) {
+            const int j = grouped ? k + shift : order[k];
+            const double now = now_ms[j];
+            if (!has_last) {
+                has_last = true;
+            } else {
+                const double d = now - last;
+                if (n_deltas == window) total -= deltas[pos];
+                else ++n_deltas;
+                deltas[pos] = d;
+                total += d;
+                if (++pos == window) pos = 0;
+            }
+            last = now;
+            int calc;
+            if (n_deltas == 0) {
+                calc = (int)floor(bc * 60.0 + 0.5);
+            } else if (!(total > 0.0)) {
+                calc = max_size;
+            } else {
+                const double v = bc * (60000.0 / (total / (double)n_deltas));
+                calc = v < 2.0e9 ? (int)(v + 0.5) : max_size;
+            }
+            const int tgt = std::max(min_size, std::min(max_size, calc));
+            worker_slot[2 * j] = w, worker_slot[2 * j + 1] = head;
+            if (++head == ring) head = 0;
+            count = std::min(count + 1, tgt);
+        }
+        b->n_deltas = n_deltas, b->pos = pos, b->head = head, b->count = count, b->total = total, b->last = last;
+        b->has_last = has_last, b->inserted += hi - lo;
         win[2 * w] = head, win[2 * w + 1] = count;
     }
     // A batch that carries more rows for one worker than its ring holds writes some slots twice.  The store
     // kernels handle the rows of a batch in parallel, so only the LAST row of each (worker, slot) may be
     // written: earlier ones get slot -1 and are skipped on the device (the ring then holds the last
-    // max_size rows, as a row-by-row replay would leave it).
-    int min_cap = 1 << 30;
-    for (int w = 0; w < num_buffers; ++w) min_cap = std::min(min_cap, ((Buffer*)buffers[w])->ring);
-    if (n > min_cap) {
+    // ring-size rows, as a row-by-row replay would leave it).
+    int max_rows = 0;
+    bool over = false;
+    for (int w = 0; w < num_buffers; ++w) {
+        const Buffer* b = (const Buffer*)buffers[w];
+        max_rows = std::max(max_rows, added[w]);
+        over = over || added[w] > b->ring;
+        if (change) change[4 * w + 2] = added[w], change[4 * w + 3] = b->count;
+    }
+    if (over) {
         std::vector<int> kept((size_t)num_buffers, 0);
         for (int i = n - 1; i >= 0; --i) {
             const int w = worker_slot[2 * i];
@@ -339,7 +417,12 @@ extern "C" int psb_buffers_on_batch(void** buffers, int num_buffers, const int* 
             else ++kept[w];
         }
     }
+    if (max_rows_out) *max_rows_out = max_rows;
     return 0;
+}
+extern "C" int psb_buffers_on_batch(void** buffers, int num_buffers, const int* workers, const double* now_ms, int n,
+                                    int* worker_slot, int* win) {
+    return psb_buffers_on_batch2(buffers, num_buffers, workers, now_ms, n, worker_slot, win, nullptr, nullptr);
 }
 
 // ------------------------------------------------------------------ streaming producer thread

@@ -320,6 +320,10 @@ int psb_buffer_set_state(void* b, const double* state, int n);
 /* n events at once: fills worker_slot[n][2] and updates win[num_buffers][2] for the touched workers */
 int psb_buffers_on_batch(void** buffers, int num_buffers, const int* workers, const double* now_ms, int n,
                          int* worker_slot, int* win);
+/* the same, and optionally change[num_buffers][4] = {head before, count before, rows added, count after} per worker
+ * (the input of psb_window_stats_update) and *max_rows_out = the most rows any worker received from the batch */
+int psb_buffers_on_batch2(void** buffers, int num_buffers, const int* workers, const double* now_ms, int n,
+                          int* worker_slot, int* win, int* change, int* max_rows_out);
 
 /* Streaming producer thread (CsvProducer.java:36-87 + INPUT_DATA): tokenises the CSV on a host thread,
  * keeps the rows of partitions [worker_begin, worker_begin + worker_count), converts them to dense fp16

@@ -277,16 +277,13 @@ class DeviceEngine:
         workers = np.ascontiguousarray(workers[:n], dtype=np.int32)
         now_ms = np.zeros(n, dtype=np.float64) if now_ms is None else np.ascontiguousarray(now_ms[:n], dtype=np.float64)
         handles, buffers = self._buf_handles, self.buffers
-        # most rows any worker receives from this set: decides whether its store may overlap a running step
-        self.stage_max_rows[j] = int(np.bincount(workers, minlength=1).max()) if n else 0
 
         def assign():
-            ch = self.stage_change_host[j].numpy()
-            ch[:, 0:2] = self.win_host.numpy()                   # windows before the batch
-            ch[:, 2] = np.bincount(workers, minlength=self.W)[: self.W] if n else 0
-            native.buffers_on_batch(buffers, workers, now_ms, self.stage_ws_host[j].numpy(), self.win_host.numpy(),
-                                    handles=handles)
-            ch[:, 3] = self.win_host.numpy()[:, 1]               # ... and the window sizes after it
+            # slot of every row, the windows after the batch, what changed per worker (for the statistics update) and
+            # the most rows any worker receives (decides whether the store may overlap a running step): one native call
+            self.stage_max_rows[j] = native.buffers_on_batch(
+                buffers, workers, now_ms, self.stage_ws_host[j].numpy(), self.win_host.numpy(), handles=handles,
+                change=self.stage_change_host[j].numpy())
             self.stage_win_host[j].copy_(self.win_host)
 
         if self._slot_thread is None:

@@ -142,6 +142,7 @@ def lib() -> C.CDLL:
     L.psb_buffer_inserted.restype = C.c_longlong
     L.psb_buffer_inserted.argtypes = [vp]
     L.psb_buffers_on_batch.argtypes = [vp, C.c_int, vp, vp, C.c_int, vp, vp]
+    L.psb_buffers_on_batch2.argtypes = [vp, C.c_int, vp, vp, C.c_int, vp, vp, vp, C.POINTER(C.c_int)]
     L.psb_buffer_get_state.argtypes = [vp, vp, C.c_int]
     L.psb_buffer_set_ring.argtypes = [vp, C.c_int]
     L.psb_buffer_set_state.argtypes = [vp, vp, C.c_int]
@@ -388,14 +389,19 @@ def buffer_handles(buffers):
 
 
 def buffers_on_batch(buffers, workers: np.ndarray, now_ms: np.ndarray, worker_slot: np.ndarray, win: np.ndarray,
-                     handles=None):
-    """buffers: list of NativeBuffer; fills worker_slot[n,2] / win[W,2] (int32 numpy views, may be pinned)."""
+                     handles=None, change: Optional[np.ndarray] = None) -> int:
+    """buffers: list of NativeBuffer; fills worker_slot[n,2] / win[W,2] (int32 numpy views, may be pinned) and, when
+    given, change[W,4] = (head before, count before, rows added, count after).  Returns the most rows any worker got."""
     n = len(workers)
     arr = handles if handles is not None else buffer_handles(buffers)
     workers = np.ascontiguousarray(workers, dtype=np.int32)
     now_ms = np.ascontiguousarray(now_ms, dtype=np.float64)
-    check(lib().psb_buffers_on_batch(arr, len(buffers), workers.ctypes.data, now_ms.ctypes.data, n,
-                                     worker_slot.ctypes.data, win.ctypes.data), "psb_buffers_on_batch")
+    most = C.c_int(0)
+    check(lib().psb_buffers_on_batch2(arr, len(buffers), workers.ctypes.data, now_ms.ctypes.data, n,
+                                      worker_slot.ctypes.data, win.ctypes.data,
+                                      change.ctypes.data if change is not None else None, C.byref(most)),
+          "psb_buffers_on_batch")
+    return most.value
 
 
 class StreamProducer:
