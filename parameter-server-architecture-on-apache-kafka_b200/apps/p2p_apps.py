@@ -163,6 +163,7 @@ class P2PServer:
             "topic": self.topic_layout.describe(), "topic_bytes": self.topic_layout.bytes,
         }
         self.closing = False
+        self.watchdog_s = 120.0
         torch.cuda.synchronize()
 
     # -- transport set-up
@@ -206,6 +207,7 @@ class P2PServer:
         held = None                                      # a polled batch waiting for a free slot
         in_flight = []                                   # (producer batch, event) copies still reading pinned memory
         eof_sent, logged = False, 0
+        seen_state, seen_at = None, time.time()          # watchdog: what the worker app last reported, and when
         try:
             while True:
                 progressed = False
@@ -238,7 +240,12 @@ class P2PServer:
                 status = int(self._read_words(self.p_status, 1)[0])
                 if status != 0:
                     raise RuntimeError(f"a worker kernel gave up waiting (status word {status})")
-                _, worker_done, _ = w.worker_state()
+                consumed, worker_done, worker_clock = w.worker_state()
+                if (consumed, worker_clock) != seen_state:
+                    seen_state, seen_at = (consumed, worker_clock), time.time()
+                elif self.watchdog_s > 0 and time.time() - seen_at > self.watchdog_s and (w.produced > consumed or logged):
+                    raise RuntimeError(f"the worker app made no progress for {self.watchdog_s:.0f}s "
+                                       f"(batches consumed {consumed} of {w.produced}, clock {worker_clock})")
                 if worker_done:
                     clock_done, consistent = self._snapshot()
                     if consistent and clock_done > logged:
@@ -360,10 +367,13 @@ class P2PWorker:
                 if self.host_delay_s:
                     time.sleep(self.host_delay_s)
                 if self.server_sync:                          # reference: the server scores the weights of clock v
+                    t_wait = time.time()
                     while not self.closing:                   # before it hands them out (ServerProcessor.java:154-182)
                         ctl = self.region.read(0, 16).view(np.int32)
                         if ctl[self.p2p.CTL_SERVER_LOGGED] >= eng.clock or ctl[self.p2p.CTL_STOP]:
                             break
+                        if time.time() - t_wait > 120.0:
+                            raise RuntimeError(f"the server app has not logged clock {eng.clock - 1} for 120 s")
                         time.sleep(0.0002)
                 clock0 = eng.clock
                 eng.step(num_clocks=self.cpl)
