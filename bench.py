@@ -46,7 +46,12 @@ def parse():
     p.add_argument("--features", type=int, default=1024)
     p.add_argument("--density", type=float, default=0.45, help="non-zero fraction of the hashed BoW rows")
     p.add_argument("--solver", default="lbfgs2", choices=["lbfgs2", "sgd"])
-    p.add_argument("--consistency_model", type=int, default=0)
+    p.add_argument("--consistency_model", type=int, default=0,
+                   help="0 sequential (headline), k > 0 bounded delay, -1 eventual; the relaxed models run with per-worker "
+                        "clocks (every worker gated on its own, its delta applied on arrival)")
+    p.add_argument("--clocks_per_launch", type=int, default=1,
+                   help="relaxed models: clocks every worker runs per launch at its own pace (a step is still ONE clock: "
+                        "--steps must be a multiple)")
     p.add_argument("--ingest_rows", type=int, default=128, help="new rows per worker per step in the e2e run")
     p.add_argument("--ingest_format", choices=["palette", "bitmap", "dense"], default="palette",
                    help="e2e wire format of the fresh rows (all lossless w.r.t. the fp16 rings): presence bitmap + per-row "
@@ -174,6 +179,11 @@ def main():
     else:
         Engine = DeviceEngine
     kw = {} if a.no_overlap or a.no_e2e else {"ring_spare_rows": a.ingest_rows, "stats_at_ingest": a.stats == "ingest"}
+    cpl = max(1, a.clocks_per_launch) if a.consistency_model != 0 else 1
+    if a.consistency_model != 0 and a.transport == "p2p":
+        kw.update(async_granularity="worker", max_clocks_per_launch=cpl)
+        if a.steps % cpl or a.warmup % cpl:
+            raise SystemExit("--steps and --warmup must be multiples of --clocks_per_launch")
     eng = Engine(cfg, W, rank, world, impl, dev, w0=w0, stage_rows=W * a.ingest_rows, **kw)
     eng.connect()
     X, y = synth_buffers(torch, W, cap, F, a.density, 1234 + rank, dev)
@@ -193,8 +203,15 @@ def main():
         return float(t.item())
 
     # ---------------------------------------------------------------- device-timed region
-    for _ in range(a.warmup):
-        eng.step()
+    def run_clocks(n):
+        if cpl == 1:
+            for _ in range(n):
+                eng.step()
+        else:
+            for _ in range(n // cpl):
+                eng.step(num_clocks=cpl)
+
+    run_clocks(a.warmup)
     barrier()
     sampler = ClockSampler(local)
     if rank == 0:
@@ -203,8 +220,7 @@ def main():
     barrier()
     launches0 = eng.kernel_launches
     e0.record()
-    for _ in range(a.steps):
-        eng.step()
+    run_clocks(a.steps)
     e1.record()
     barrier()
     ms = max_over_ranks(e0.elapsed_time(e1))
@@ -313,6 +329,7 @@ def main():
                        "parallelism": f"ps-dp{world} ({W} workers/GPU, {world} server shards)",
                        "num_workers": W * world, "buffer_rows": cap, "density": a.density,
                        "local_solver": a.solver, "consistency_model": a.consistency_model, "statistics": a.stats,
+                       "clocks_per_launch": cpl,
                        "l2": f"inputs larger than L2 ({W * cap * F * 2 / 2**20:.0f} MiB of rows per GPU streamed per pass)",
                        "evals_per_step": float(info[:, 0].mean()), "status": status,
                        "cycles64_stats_solve_push_total": [float(info[:, k].mean()) for k in (4, 5, 6, 7)],

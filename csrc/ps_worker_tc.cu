@@ -885,9 +885,20 @@ int psb_worker_tc_resident(const PsbSolver* s, int num_workers) {
     if (cudaGetDevice(&dev) != cudaSuccess) return 0;
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     tc_launch_shape(s->num_features, num_workers, sms, &kNS, &smem);
-    cudaFuncSetAttribute(psb_worker_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, psb_worker_tc_kernel, kThreads, smem);
-    if (per_sm > 512 / kTmemCols) per_sm = 512 / kTmemCols;           // tensor memory: kTmemCols of 512 columns per CTA
+    // CTAs per SM from the resources themselves: registers, shared memory (1 KB reserved per CTA), threads, and
+    // tensor memory (kTmemCols of the SM's 512 columns per CTA — not known to the occupancy calculator, which also
+    // answers 1 for this kernel on the 580 driver although two CTAs per SM do run together)
+    cudaFuncAttributes fa;
+    int regs_sm = 65536, smem_sm = 233472, thr_sm = 2048;
+    if (cudaFuncGetAttributes(&fa, psb_worker_tc_kernel) != cudaSuccess) return 0;
+    cudaDeviceGetAttribute(&regs_sm, cudaDevAttrMaxRegistersPerMultiprocessor, dev);
+    cudaDeviceGetAttribute(&smem_sm, cudaDevAttrMaxSharedMemoryPerMultiprocessor, dev);
+    cudaDeviceGetAttribute(&thr_sm, cudaDevAttrMaxThreadsPerMultiProcessor, dev);
+    const int by_regs = regs_sm / (((fa.numRegs + 7) / 8 * 8) * kThreads);
+    const int by_smem = (int)(smem_sm / (smem + fa.sharedSizeBytes + 1024));
+    per_sm = by_regs < by_smem ? by_regs : by_smem;
+    if (per_sm > thr_sm / kThreads) per_sm = thr_sm / kThreads;
+    if (per_sm > 512 / kTmemCols) per_sm = 512 / kTmemCols;
     return sms * per_sm;
 }
 

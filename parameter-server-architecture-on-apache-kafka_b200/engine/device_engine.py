@@ -516,6 +516,9 @@ class DeviceEngine:
                            self.win[lo:lo + gs], None, None, self.loss[lo:lo + gs], self.info[lo:lo + gs],
                            self.scratch[lo:lo + gs], stream=st)
         self.hist_n[g] = n
+        if self.groups == 1:                                # (overlapped ring stores order themselves on these)
+            self._step_done[self._steps & 1].record(st)
+            self._steps += 1
         self._commits_since_step = 0
         self.kernel_launches += 1
         self.group_clock[g] += n
