@@ -179,11 +179,11 @@ def main():
     else:
         Engine = DeviceEngine
     kw = {} if a.no_overlap or a.no_e2e else {"ring_spare_rows": a.ingest_rows, "stats_at_ingest": a.stats == "ingest"}
-    cpl = max(1, a.clocks_per_launch) if a.consistency_model != 0 else 1
+    cpl = max(1, a.clocks_per_launch) if a.transport == "p2p" else 1
     if a.consistency_model != 0 and a.transport == "p2p":
         kw.update(async_granularity="worker", max_clocks_per_launch=cpl)
-        if a.steps % cpl or a.warmup % cpl:
-            raise SystemExit("--steps and --warmup must be multiples of --clocks_per_launch")
+    if a.steps % cpl or a.warmup % cpl:
+        raise SystemExit("--steps and --warmup must be multiples of --clocks_per_launch")
     eng = Engine(cfg, W, rank, world, impl, dev, w0=w0, stage_rows=W * a.ingest_rows, **kw)
     eng.connect()
     X, y = synth_buffers(torch, W, cap, F, a.density, 1234 + rank, dev)

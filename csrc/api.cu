@@ -169,17 +169,20 @@ int psb_worker_step(const PsbSolver* s, const PsbComm* comm, int num_workers, in
             PSB_REQUIRE(comm->num_clocks >= 0 && comm->num_clocks <= 1 << 20, "num_clocks out of range");
         } else {
             PSB_REQUIRE(comm->workers_per_rank == num_workers, "workers_per_rank must equal num_workers");
-            PSB_REQUIRE(comm->num_clocks <= 1, "several clocks per launch need comm mode PSB_COMM_WORKER");
+            PSB_REQUIRE(comm->num_clocks <= 1 || comm->mode == PSB_COMM_SEQUENTIAL,
+                        "several clocks per launch need comm mode PSB_COMM_WORKER or PSB_COMM_SEQUENTIAL");
             PSB_REQUIRE(!comm->publish || (comm->mode == PSB_COMM_SEQUENTIAL && comm->num_ranks == 1),
                         "the published snapshot is kept in sequential mode on one rank only");
         }
     }
-    if (comm->mode == PSB_COMM_WORKER && comm->max_delay >= 0) {
+    if ((comm->mode == PSB_COMM_WORKER && comm->max_delay >= 0) ||
+        (comm->mode == PSB_COMM_SEQUENTIAL && comm->num_clocks > 1)) {
         // gated workers spin on each other's clock words: every CTA of the launch has to be on the GPU at once
         const int fit = psb_worker_max_resident(s, impl, num_workers);
         if (num_workers > fit) {
-            psb_set_error("bounded-delay launch of %d workers, but only %d worker CTAs of this shape are resident at "
-                          "once on this device: launch fewer workers per GPU", num_workers, fit);
+            psb_set_error("launch of %d workers that wait on each other (bounded delay, or several sequential clocks "
+                          "per launch), but only %d worker CTAs of this shape are resident at once on this device: "
+                          "launch fewer workers per GPU", num_workers, fit);
             return PSB_E_LIMIT;
         }
     }

@@ -195,7 +195,7 @@ psb_worker_simt_kernel(PsbSolver sv, CommCtx cx, const __half* __restrict__ X, c
                        const int* __restrict__ win, const float* __restrict__ w_in, float* __restrict__ delta_out,
                        float* __restrict__ loss_out, int* __restrict__ info_out, float* __restrict__ scratch) {
     extern __shared__ __align__(16) unsigned char smem[];
-    const int nclk = cx.c.mode == PSB_COMM_WORKER && cx.c.num_clocks > 1 ? cx.c.num_clocks : 1;
+    const int nclk = (cx.c.mode == PSB_COMM_WORKER || cx.c.mode == PSB_COMM_SEQUENTIAL) && cx.c.num_clocks > 1 ? cx.c.num_clocks : 1;
     for (int it = 0; it < nclk; ++it) {
         if (!simt_clock(sv, cx, cx.c.clock + it, it, X, labels, win, w_in, delta_out, loss_out, info_out, scratch, smem))
             return;

@@ -729,7 +729,7 @@ psb_worker_tc_kernel(const __grid_constant__ CUtensorMap tmX, PsbSolver sv, Comm
     if (start < 0) start += cap;
     const int* lw = labels + (size_t)w * cap;
     const int gw = cx.c.worker_base + w;
-    const int nclk = cx.c.mode == PSB_COMM_WORKER && cx.c.num_clocks > 1 ? cx.c.num_clocks : 1;
+    const int nclk = (cx.c.mode == PSB_COMM_WORKER || cx.c.mode == PSB_COMM_SEQUENTIAL) && cx.c.num_clocks > 1 ? cx.c.num_clocks : 1;
 
   for (int it = 0; it < nclk; ++it) {
     const int clock = cx.c.clock + it;

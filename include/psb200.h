@@ -79,8 +79,10 @@ typedef struct PsbComm {
     unsigned long long spin_limit; /* clock64 cycles before a wait gives up (watchdog)      */
     void* peers[PSB_MAX_RANKS];
     /* ---- PSB_COMM_WORKER only (leave zero otherwise) */
-    int num_clocks;                /* clocks every worker of this launch runs back to back, each at its own pace
-                                      (0 counts as 1); the window of a worker is read once per launch        */
+    int num_clocks;                /* clocks every worker of this launch runs back to back (0 counts as 1): each at
+                                      its own pace in PSB_COMM_WORKER; in PSB_COMM_SEQUENTIAL the workers meet at
+                                      every clock's version words, without a launch in between (all workers of all
+                                      ranks must be resident).  The window of a worker is read once per launch */
     int worker_base;               /* global id of the launch's worker 0 (clock table index)                 */
     int total_workers;             /* workers of all ranks = live entries of the clock table (<= PSB_MAX_WORKERS) */
     int delay_worker;              /* straggler injection: this global worker id sleeps delay_cycles before   */

@@ -469,9 +469,10 @@ class DeviceEngine:
                 self.step_group(g, num_clocks, stream=False if self.groups == 1 else None)
             self.clock = min(self.group_clock)
             return
-        if num_clocks != 1:
-            raise ValueError("several clocks per launch need async_granularity='worker' and consistency_model != 0")
+        if num_clocks != 1 and mode != native.COMM_SEQUENTIAL:
+            raise ValueError("several clocks per launch need the sequential model or async_granularity='worker'")
         comm = self._comm(mode)
+        comm.num_clocks = int(num_clocks)
         self.solver.inv_std = self._inv[self._win_i].data_ptr() if self.stats_at_ingest else None
         native.worker_step(self.solver, comm, self.W, self.impl, self.X, self.labels, self.win,
                            self.w0 if mode == native.COMM_NONE else None,
@@ -481,7 +482,7 @@ class DeviceEngine:
         self._steps += 1
         self._commits_since_step = 0
         self.kernel_launches += 1
-        self.clock += 1
+        self.clock += int(num_clocks)
 
     def step_group(self, g: int, num_clocks: int = 1, stream=None) -> None:
         """Per-worker mode: enqueue `num_clocks` clocks of the workers of group g — one launch on the group's own

@@ -203,3 +203,26 @@ def test_pipelined_loss_read_returns_the_step_it_was_issued_behind():
     assert torch.equal(eng.read_loss_end(t2), second)
     assert not torch.equal(first, second)         # the two clocks really differ
     eng.close()
+
+
+@pytest.mark.parametrize("impl", [0, 1])
+def test_several_sequential_clocks_in_one_launch_equal_one_launch_per_clock(impl):
+    """PSB_COMM_SEQUENTIAL with num_clocks > 1: the worker CTAs stay on the GPU and meet at every clock's version
+    words instead of at a kernel boundary; same weights and losses as one launch per clock."""
+    from psb200.engine.device_engine import DeviceEngine
+    F, cap, n, W, clocks = 256, 128, 96, 4, 5
+    cfg = PSConfig(num_workers=W, num_features=F, max_buffer_size=cap, min_buffer_size=16)
+    b = _half_batch(ReviewGenerator(F, 5, vocab=3000, mean_len=120.0).train_split(W * n))
+    rows = torch.from_numpy(b.to_dense(np.float16)).view(W, n, F).cuda()
+    labs = torch.from_numpy(b.labels.astype(np.int32)).view(W, n).cuda()
+    out = []
+    for per_launch in (1, clocks):
+        e = DeviceEngine(cfg, W, impl=impl, spin_limit_cycles=4_000_000_000)
+        e.fill(rows, labs)
+        for _ in range(clocks // per_launch):
+            e.step(num_clocks=per_launch)
+        out.append((e.weights().cpu().numpy().copy(), e.read_loss().numpy().copy(), e.clock, e.status()))
+        e.close()
+    assert out[0][2] == out[1][2] == clocks and out[0][3] == out[1][3] == 0
+    assert np.abs(out[0][0] - out[1][0]).max() < 2e-5 * max(1.0, np.abs(out[0][0]).max())
+    assert np.allclose(out[0][1], out[1][1], rtol=2e-5, atol=2e-6)
