@@ -74,13 +74,14 @@ __shared__ int psb_tc_fail;                    // a bounded wait gave up
 __shared__ unsigned int psb_tc_chunk_base;     // ring position (chunks streamed so far)
 __shared__ int psb_tc_need_redo;               // a constant non-zero column was found: redo the first evaluation
 
-__device__ __forceinline__ bool wait_or_fail(uint64_t* bar, uint32_t parity, volatile int* fail) {
+// `site` identifies the wait in the failure report (info[1] = -site when a worker's step gave up)
+__device__ __forceinline__ bool wait_or_fail(uint64_t* bar, uint32_t parity, volatile int* fail, int site = 1) {
     if (tc::mbar_try_wait(bar, parity)) return true;            // common case: no clock read, no fail poll
     const unsigned long long t0 = clock64();
     while (!tc::mbar_try_wait(bar, parity)) {
         if (*fail) return false;
         if ((unsigned long long)(clock64() - t0) > 4000000000ull) {
-            *fail = 1;
+            *fail = site;
             return false;
         }
     }
@@ -166,7 +167,7 @@ struct TcEval {
 #if PSB_TC_PROFILE == 2
             const long long te = clock64();
 #endif
-            if (use > 0 && !wait_or_fail(sh.empty() + slot, (use - 1) & 1, &psb_tc_fail)) return false;
+            if (use > 0 && !wait_or_fail(sh.empty() + slot, (use - 1) & 1, &psb_tc_fail, 2)) return false;
 #if PSB_TC_PROFILE == 2
             const long long ts = clock64();
             prof[0] += ts - te;
@@ -174,7 +175,7 @@ struct TcEval {
             if (fused && idx >= kNS) {        // previous occupant of the slot: chunk idx - kNS of this pass;
                                               // the statistics warps read it on its A use when c % 4 < 2, else on its B use
                 if ((((lag_c >> 1) & 1) == 0) == lag_a) {
-                    if (!wait_or_fail(sh.sdone() + slot, (sd_par >> slot) & 1u, &psb_tc_fail)) return false;
+                    if (!wait_or_fail(sh.sdone() + slot, (sd_par >> slot) & 1u, &psb_tc_fail, 3)) return false;
                     sd_par ^= 1u << slot;
                 }
                 if (++lag_c == nkb) lag_c = 0, lag_a = !lag_a;
@@ -238,7 +239,7 @@ struct TcEval {
 #ifdef PSB_TC_TRACE
                     const long long tw0 = clock64();
 #endif
-                    if (!wait_or_fail(sh.full() + slot, phase, &psb_tc_fail)) return;
+                    if (!wait_or_fail(sh.full() + slot, phase, &psb_tc_fail, 4)) return;
 #ifdef PSB_TC_TRACE
                     const long long tw1 = clock64();
                     st_wait += tw1 - tw0;
@@ -339,7 +340,7 @@ struct TcEval {
 #ifdef PSB_TC_PROFILE
                 const long long tw = clock64();
 #endif
-                if (!wait_or_fail(sh.full() + slot, phase, &psb_tc_fail)) return false;
+                if (!wait_or_fail(sh.full() + slot, phase, &psb_tc_fail, 5)) return false;
 #ifdef PSB_TC_PROFILE
                 prof[0] += clock64() - tw;
 #endif
@@ -364,7 +365,7 @@ struct TcEval {
 #ifdef PSB_TC_PROFILE
             const long long tr = clock64();
 #endif
-            if (!wait_or_fail(sh.r_full(), ruse[0] & 1, &psb_tc_fail)) return false;
+            if (!wait_or_fail(sh.r_full(), ruse[0] & 1, &psb_tc_fail, 6)) return false;
             ++ruse[0];
 #ifdef PSB_TC_PROFILE
             prof[1] += clock64() - tr;
@@ -374,8 +375,8 @@ struct TcEval {
 #ifdef PSB_TC_PROFILE
                 const long long tb = clock64();
 #endif
-                if (!wait_or_fail(sh.full() + slot, phase, &psb_tc_fail)) return false;
-                if (!wait_or_fail(sh.full() + slot + 1, phase, &psb_tc_fail)) return false;
+                if (!wait_or_fail(sh.full() + slot, phase, &psb_tc_fail, 7)) return false;
+                if (!wait_or_fail(sh.full() + slot + 1, phase, &psb_tc_fail, 8)) return false;
 #ifdef PSB_TC_PROFILE
                 prof[2] += clock64() - tb;
 #endif
@@ -437,7 +438,7 @@ struct TcEval {
             }
             float z[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
             if (cfg.a) {
-                if (!wait_or_fail(sh.z_full() + zb, zuse[zb] & 1, &psb_tc_fail)) return;
+                if (!wait_or_fail(sh.z_full() + zb, zuse[zb] & 1, &psb_tc_fail, 9)) return;
                 ++zuse[zb];
                 tc::tc_fence_after();
                 float v[16];
@@ -453,7 +454,7 @@ struct TcEval {
                 // gradient-only pass: nothing paces these warps but the single Rsp buffer — wait until GEMM2(q-1)
                 // has consumed it (the MMA warp commits z_full[(q-1)&1] behind that GEMM)
                 if (q >= 1) {
-                    if (!wait_or_fail(sh.z_full() + ((q - 1) & 1), zuse[(q - 1) & 1] & 1, &psb_tc_fail)) return;
+                    if (!wait_or_fail(sh.z_full() + ((q - 1) & 1), zuse[(q - 1) & 1] & 1, &psb_tc_fail, 10)) return;
                     ++zuse[(q - 1) & 1];
                 }
             }
@@ -482,7 +483,7 @@ struct TcEval {
             if (lane == 0) tc::mbar_arrive(sh.r_full());
         }
         if (!cfg.a && S >= 1) {                  // consume the last "Rsp consumed" commit of a gradient-only pass
-            if (!wait_or_fail(sh.z_full() + ((S - 1) & 1), zuse[(S - 1) & 1] & 1, &psb_tc_fail)) return;
+            if (!wait_or_fail(sh.z_full() + ((S - 1) & 1), zuse[(S - 1) & 1] & 1, &psb_tc_fail, 11)) return;
             ++zuse[(S - 1) & 1];
         }
         for (int o = 16; o; o >>= 1) {
@@ -496,8 +497,8 @@ struct TcEval {
             for (int c = 0; c < 8; ++c) atomicAdd(&sh.sred()[1 + c], rs[c]);
         }
         // drain the gradient accumulators: thread = feature row of each 128-feature tile
-        if (fused && !wait_or_fail(sh.inv_ready(), 0, &psb_tc_fail)) return;
-        if (!wait_or_fail(sh.g_full(), guse & 1, &psb_tc_fail)) return;
+        if (fused && !wait_or_fail(sh.inv_ready(), 0, &psb_tc_fail, 12)) return;
+        if (!wait_or_fail(sh.g_full(), guse & 1, &psb_tc_fail, 13)) return;
         ++guse;
         tc::tc_fence_after();
         for (int j = 0; j < nkb / 2; ++j) {
@@ -824,7 +825,7 @@ psb_worker_tc_kernel(const __grid_constant__ CUtensorMap tmX, PsbSolver sv, Comm
         if (tid == 0) {
             loss_out[w] = psb_tc_fail ? nanf("") : (float)res.loss;
             if (rec) rec->loss = loss_out[w];
-            info_out[8 * w + 0] = res.evals, info_out[8 * w + 1] = res.iterations;
+            info_out[8 * w + 0] = res.evals, info_out[8 * w + 1] = psb_tc_fail ? -psb_tc_fail : res.iterations;
             info_out[8 * w + 2] = psb_tc_fail ? -2 : res.status, info_out[8 * w + 3] = count;
             info_out[8 * w + 4] = (int)((t_stats - t_begin) >> 6), info_out[8 * w + 5] = (int)((t_solve - t_stats) >> 6);
         }
@@ -832,7 +833,8 @@ psb_worker_tc_kernel(const __grid_constant__ CUtensorMap tmX, PsbSolver sv, Comm
             float4* out = (float4*)(delta_out + (size_t)w * nv);
             for (int i = tid; i < n4; i += blockDim.x) out[i] = ((const float4*)delta)[i];
         } else {
-            comm_push(cx, clock, gw, (const float4*)delta);
+            // a step whose barrier wait gave up has no result: it still takes part in the protocol, with no delta
+            comm_push(cx, clock, gw, psb_tc_fail ? nullptr : (const float4*)delta);
         }
         if (tid == 0) info_out[8 * w + 6] = (int)((clock64() - t_solve) >> 6), info_out[8 * w + 7] = (int)((clock64() - t_begin) >> 6);
         PSB_TRACE(7);

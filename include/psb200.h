@@ -135,7 +135,8 @@ size_t psb_worker_scratch_bytes(int num_features);                              
  *   d_w_in  : weights to start from when comm.mode == NONE (else the replica is used)
  *   d_delta : [num_workers][(F+1)*8] out when comm.mode == NONE (may be NULL otherwise)
  *   d_loss  : [num_workers] final train loss of the local solve
- *   d_info  : [num_workers][8] ints: evals, iterations, status, active rows, then SM cycles / 64 spent in
+ *   d_info  : [num_workers][8] ints: evals, iterations (tcgen05 kernel: -site of the barrier wait that gave up when
+ *             status is -2), status, active rows, then SM cycles / 64 spent in
  *             pull+statistics, local solve, delta+push, whole step
  *   impl    : 0 = SIMT fp32 kernel, 1 = tcgen05/TMA kernel                                */
 int psb_worker_step(const PsbSolver* s, const PsbComm* comm, int num_workers, int impl,
