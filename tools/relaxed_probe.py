@@ -19,6 +19,9 @@ p.add_argument("--cpl", type=int, default=8)
 p.add_argument("--workers", type=int, default=296)
 p.add_argument("--launches", type=int, default=6)
 p.add_argument("--model", type=int, default=-1)
+p.add_argument("--delay_worker", type=int, default=-1)
+p.add_argument("--delay_cycles", type=int, default=0)
+p.add_argument("--check", action="store_true", help="synchronise after every launch and report failed barrier waits at once")
 p.add_argument("--spare", type=int, default=0, help="spare ring rows per worker (as bench.py's end-to-end engine)")
 a = p.parse_args()
 rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
@@ -36,10 +39,18 @@ del X, y
 dist.barrier()
 torch.cuda.synchronize()
 ev = [torch.cuda.Event(enable_timing=True) for _ in range(a.launches + 1)]
+if a.delay_worker >= 0:
+    eng.inject_delay(a.delay_worker, a.delay_cycles)
 ev[0].record()
 for i in range(a.launches):
     eng.step(num_clocks=a.cpl)
     ev[i + 1].record()
+    if a.check:
+        torch.cuda.synchronize()
+        inf = eng.info.cpu().numpy()
+        for w in np.nonzero(inf[:, 2] == -2)[0]:
+            print(f"rank {rank}: launch {i} worker {w} FAILED barrier wait site {-inf[w, 1]} evals {inf[w, 0]} "
+                  f"launch ms {ev[i].elapsed_time(ev[i + 1]):.1f}", flush=True)
 torch.cuda.synchronize()
 ms = [round(ev[i].elapsed_time(ev[i + 1]), 2) for i in range(a.launches)]
 info = eng.info.cpu().numpy()
