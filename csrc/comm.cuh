@@ -46,9 +46,13 @@ struct CommCtx {
 __device__ __forceinline__ bool worker_gate(const CommCtx& cx, int clock, int gw, PsbClockRecord* rec) {
     const PsbComm& c = cx.c;
     CommBlock me(c.peers[c.rank], cx.L);
-    if (c.delay_cycles && c.delay_worker == gw) {                 // injected straggler
+    if (c.delay_cycles && (c.delay_worker == gw || c.delay_worker == -2)) {   // injected straggler
+        // -2: every worker sleeps a different pseudo-random fraction of delay_cycles before every clock (jitter tests)
+        const unsigned long long want = c.delay_worker == -2
+            ? c.delay_cycles * (unsigned long long)((((unsigned)gw * 2654435761u) ^ ((unsigned)clock * 40503u)) >> 8 & 63u) / 64ull
+            : c.delay_cycles;
         const unsigned long long t0 = clock64();
-        while ((unsigned long long)(clock64() - t0) < c.delay_cycles) __nanosleep(1000);
+        while ((unsigned long long)(clock64() - t0) < want) __nanosleep(1000);
     }
     const unsigned int* tab = me.wclocks();
     const bool gated = c.max_delay >= 0 && clock > c.max_delay;

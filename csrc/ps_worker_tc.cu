@@ -149,8 +149,8 @@ struct TcEval {
     }
 
     // ---- TMA producer (one thread).  with_b: stream every slab twice, A(s) then B(s).
-    // fused: the statistics warps also read every chunk once (on its A or its B use), so a slot whose previous
-    // occupant was such a use is refilled only after their sdone arrival as well.
+    // fused: the statistics warps also follow every chunk (and read it once, on its A or its B use), so a slot is
+    // refilled only after their sdone arrival for its previous occupant as well.
     __device__ void produce(const PassCfg& cfg) {
         const bool with_a = cfg.a, with_b = cfg.b, fused = cfg.fused;
         const int nkb = F / kBlockK, S = num_active_slabs();
@@ -160,8 +160,6 @@ struct TcEval {
         int slot = (int)(pc0 % (unsigned)kNS);
         unsigned int use = pc0 / (unsigned)kNS;
         int idx = 0;                          // chunks issued in this pass
-        int lag_c = 0;                        // (idx - kNS) % nkb and whether chunk idx - kNS was an A chunk
-        bool lag_a = true;
         unsigned int sd_par = 0u;             // per-slot parity of the statistics warps' sdone barrier
         auto load = [&](int b, int c, uint64_t policy) -> bool {
 #if PSB_TC_PROFILE == 2
@@ -172,13 +170,13 @@ struct TcEval {
             const long long ts = clock64();
             prof[0] += ts - te;
 #endif
-            if (fused && idx >= kNS) {        // previous occupant of the slot: chunk idx - kNS of this pass;
-                                              // the statistics warps read it on its A use when c % 4 < 2, else on its B use
-                if ((((lag_c >> 1) & 1) == 0) == lag_a) {
-                    if (!wait_or_fail(sh.sdone() + slot, (sd_par >> slot) & 1u, &psb_tc_fail, 3)) return false;
-                    sd_par ^= 1u << slot;
-                }
-                if (++lag_c == nkb) lag_c = 0, lag_a = !lag_a;
+            if (fused && idx >= kNS) {
+                // The statistics warp of this slot has SEEN the previous occupant (it arrives on sdone after every use
+                // of its slots, whether it read the chunk or only followed the barrier): a hard handshake.  Waiting
+                // only after the uses it reads left the others to a timing margin — a statistics warp held up for
+                // more than one trip around the ring lost a phase of the slot's `full` barrier for good.
+                if (!wait_or_fail(sh.sdone() + slot, (sd_par >> slot) & 1u, &psb_tc_fail, 3)) return false;
+                sd_par ^= 1u << slot;
             }
 #if PSB_TC_PROFILE == 2
             prof[1] += clock64() - ts;
@@ -285,12 +283,12 @@ struct TcEval {
                             tc::sts_f4(ps, make_float4(u.x + a0, u.y + a1, u.z + a2, u.w + a3));
                             tc::sts_f4(pq, make_float4(v.x + q0, v.y + q1, v.z + q2, v.w + q3));
                         }
-                        __syncwarp();
-                        if (lane == 0) tc::mbar_arrive(sh.sdone() + slot);
 #ifdef PSB_TC_TRACE
                         st_read += clock64() - tw1, ++st_chunks;
 #endif
                     }
+                    __syncwarp();
+                    if (lane == 0) tc::mbar_arrive(sh.sdone() + slot);   // seen (and, on its read use, done with) the slot
                     slot += 2;
                     if (slot >= kNS) slot -= kNS, phase ^= 1u;
                 }

@@ -85,7 +85,8 @@ typedef struct PsbComm {
                                       ranks must be resident).  The window of a worker is read once per launch */
     int worker_base;               /* global id of the launch's worker 0 (clock table index)                 */
     int total_workers;             /* workers of all ranks = live entries of the clock table (<= PSB_MAX_WORKERS) */
-    int delay_worker;              /* straggler injection: this global worker id sleeps delay_cycles before   */
+    int delay_worker;              /* straggler injection: this global worker id (-2: every worker, a different
+                                      pseudo-random fraction each clock) sleeps delay_cycles before            */
     unsigned long long delay_cycles; /* every clock (0: off)                                                  */
     void* hist;                    /* optional PsbClockRecord[num_clocks][num_workers] of this launch (device) */
     int home_remote;               /* peers[rank] lives on another GPU (server process' block): the intra-rank

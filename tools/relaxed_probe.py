@@ -39,7 +39,7 @@ del X, y
 dist.barrier()
 torch.cuda.synchronize()
 ev = [torch.cuda.Event(enable_timing=True) for _ in range(a.launches + 1)]
-if a.delay_worker >= 0:
+if a.delay_cycles:
     eng.inject_delay(a.delay_worker, a.delay_cycles)
 ev[0].record()
 for i in range(a.launches):
