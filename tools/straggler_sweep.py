@@ -35,7 +35,7 @@ eng = DeviceEngine(cfg, W, rank, world, native.IMPL_TC, dev)
 eng.connect()
 X, y = synth_buffers(torch, W, cap, F, 0.45, 5 + rank, dev)
 eng.fill(X, y)
-clocks_view = _view(native.lib().psb_comm_status(eng.block, F, world) + 768 + 128, world, dev, torch.int32)
+clocks_view = _view(native.lib().psb_comm_rank_clocks(eng.block, F, world), world, dev, torch.int32)
 dist.barrier()
 torch.cuda.synchronize()
 t0 = time.time()
