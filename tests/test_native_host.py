@@ -42,6 +42,42 @@ def test_native_buffer_batch_form():
         assert (win[w, 0], win[w, 1]) == (ref[w].ring.head, ref[w].ring.count)
 
 
+@pytest.mark.parametrize("order", ["grouped", "round_robin", "random"])
+def test_batch_slot_assignment_equals_event_by_event_replay_and_reports_what_changed(order):
+    """psb_buffers_on_batch2 groups the events by worker before it runs the policy; slots, windows, the per-worker
+    change table (head / count before, rows added, count after) and the largest per-worker row count must be what an
+    event-by-event replay gives, whatever the arrival order; rings with spare slots wrap at the ring size."""
+    W, n_per = 5, 70
+    rng = np.random.default_rng(3)
+    workers = np.repeat(np.arange(W, dtype=np.int32), n_per)
+    if order == "round_robin":
+        workers = np.tile(np.arange(W, dtype=np.int32), n_per)
+    elif order == "random":
+        workers = rng.permutation(workers).astype(np.int32)
+    now = np.cumsum(rng.choice([5.0, 40.0, 900.0], size=len(workers)))
+    bufs = [native.NativeBuffer(8, 48, 0.3, ring=64) for _ in range(W)]
+    ref = [native.NativeBuffer(8, 48, 0.3, ring=64) for _ in range(W)]
+    for b, r in zip(bufs, ref):                       # some history first, so that "before" is not all zeros
+        for t in (1.0, 2.0, 3.0):
+            b.on_event(t), r.on_event(t)
+    ws = np.zeros((len(workers), 2), dtype=np.int32)
+    win = np.zeros((W, 2), dtype=np.int32)
+    ch = np.zeros((W, 4), dtype=np.int32)
+    most = native.buffers_on_batch(bufs, workers, now, ws, win, change=ch)
+    before = [(r.head, r.count) for r in ref]
+    slots = [ref[w].on_event(t) for w, t in zip(workers, now)]
+    assert most == n_per and ws[:, 0].tolist() == workers.tolist()
+    later = {w: 0 for w in range(W)}
+    for i in range(len(workers) - 1, -1, -1):         # rows beyond the ring size are superseded (slot -1)
+        w = int(workers[i])
+        assert ws[i, 1] == (slots[i] if later[w] < 64 else -1)
+        later[w] += 1
+    for w in range(W):
+        assert (win[w, 0], win[w, 1]) == (ref[w].head, ref[w].count)
+        assert ch[w].tolist() == [before[w][0], before[w][1], n_per, ref[w].count]
+        assert np.array_equal(bufs[w].get_state(), ref[w].get_state())
+
+
 def test_batch_with_more_rows_than_the_ring_keeps_only_the_last_row_of_every_slot():
     """The store kernels write the rows of one batch in parallel, so a (worker, slot) pair may appear once."""
     cap = 8
