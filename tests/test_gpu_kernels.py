@@ -4,7 +4,6 @@ import pytest
 
 torch = pytest.importorskip("torch")
 
-from psb200.config import PSConfig
 from psb200.data import CSRBatch, ReviewGenerator, random_csr
 from psb200.models import LogRegLayout
 from psb200.oracle import LogisticRegressionTask

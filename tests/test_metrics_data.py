@@ -4,7 +4,7 @@ import os
 import numpy as np
 from sklearn.metrics import accuracy_score, f1_score
 
-from psb200.data import (CSRBatch, ReviewGenerator, TEST_SUPPORTS, header, pack_stage_rows, random_csr, read_csv,
+from psb200.data import (ReviewGenerator, TEST_SUPPORTS, header, pack_stage_rows, random_csr, read_csv,
                          stage_stride_words, unpack_stage_rows, write_csv)
 from psb200.utils.metrics import evaluate
 

@@ -7,11 +7,9 @@ import os
 import sys
 
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
-import numpy as np
 import torch
 
 from psb200.config import PSConfig
-from psb200.data import CSRBatch
 from psb200.engine.device_engine import DeviceEngine
 from psb200.engine.sparse_row_engine import SparseRowEngine
 from psb200.ops import native
