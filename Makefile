@@ -1,5 +1,5 @@
 # Build / test / bench shortcuts (the reference builds a fat jar with `gradle build`, build.gradle:19-30).
-.PHONY: build test test-gpu bench clean mock-data tsan sass
+.PHONY: build test test-gpu bench clean mock-data tsan asan sass
 build:
 	./build.sh
 test: build
@@ -18,6 +18,15 @@ tsan:
 	g++ -std=c++17 -O1 -g -fsanitize=thread -fPIE -pie -x c++ -I/usr/local/cuda/include csrc/host_runtime.cpp \
 	    tools/tsan_host_runtime.cpp tools/tsan_stubs.cpp -o build/tsan_host_runtime -lpthread
 	TSAN_OPTIONS="halt_on_error=1 second_deadlock_stack=1" ./build/tsan_host_runtime
+# AddressSanitizer + UBSan run of the host packers and the CSV tokenizer on buffers of exactly the documented size,
+# once with the SSE2 paths and once with the portable ones; host only
+asan:
+	mkdir -p build
+	for defs in "" "-DPSB_NO_SIMD"; do \
+	  g++ -std=c++17 -O1 -g $$defs -fsanitize=address,undefined -fno-sanitize-recover=all -x c++ \
+	      -I/usr/local/cuda/include csrc/host_runtime.cpp tools/asan_packers.cpp tools/tsan_stubs.cpp \
+	      -o build/asan_packers -lpthread && ./build/asan_packers || exit 1; \
+	done
 # full SASS listing of every kernel + mnemonic summary under profiles/sass (no GPU needed)
 sass: build
 	python tools/dump_sass.py

@@ -37,48 +37,71 @@ struct FileBuf {
 };
 
 // Parses one line [p, e): calls emit(col, value) for every non-zero feature, returns the label.
-// Fast path for plain decimals; strtof for anything with an exponent.
+// One pass per field: "0," and "0.0," (nearly every field of a hashed bag-of-words row) are skipped outright,
+// plain decimals accumulate an integer mantissa that is divided by an exact power of ten, anything else
+// (exponents, more than 18 digits, inf / nan) goes through strtof.
 template <class Emit>
 inline int parse_line(const char* p, const char* e, int* ncols, Emit emit) {
+    static const double kPow10[23] = {1e0,  1e1,  1e2,  1e3,  1e4,  1e5,  1e6,  1e7,  1e8,  1e9,  1e10, 1e11,
+                                      1e12, 1e13, 1e14, 1e15, 1e16, 1e17, 1e18, 1e19, 1e20, 1e21, 1e22};
     int col = 0;
     float last = 0.f;
     while (p < e) {
-        const char* q = p;
-        while (q < e && *q != ',') ++q;
-        float v;
-        {
-            const char* s = p;
-            bool neg = false, simple = true;
-            if (s < q && (*s == '-' || *s == '+')) neg = *s == '-', ++s;
-            double acc = 0.0, scale = 1.0;
-            bool frac = false;
-            for (; s < q; ++s) {
-                const char c = *s;
-                if (c >= '0' && c <= '9') {
-                    acc = acc * 10.0 + (c - '0');
-                    if (frac) scale *= 10.0;
-                } else if (c == '.' && !frac) {
-                    frac = true;
-                } else if (c == ' ' || c == '\r') {
-                } else {
-                    simple = false;
-                    break;
-                }
+        if (*p == '0') {
+            while (e - p >= 8) {               // runs of "0,0,0,0,": four absent features per 64-bit compare
+                uint64_t x;
+                memcpy(&x, p, 8);
+                if (x != 0x2c302c302c302c30ULL) break;
+                p += 8, col += 4;
             }
-            if (simple) {
-                v = (float)(acc / scale);
-                if (neg) v = -v;
-            } else {
-                v = strtof(std::string(p, q).c_str(), nullptr);
+            if (p >= e) break;
+            if (*p != '0') continue;
+            if (p + 1 < e && p[1] == ',') {
+                p += 2, ++col;
+                continue;
+            }
+            if (p + 3 < e && p[1] == '.' && p[2] == '0' && p[3] == ',') {
+                p += 4, ++col;
+                continue;
             }
         }
-        if (q < e) {               // a feature column
+        const char* s = p;
+        bool neg = false, simple = true, frac = false;
+        if (*s == '-' || *s == '+') neg = *s == '-', ++s;
+        uint64_t mant = 0;
+        int digits = 0, frac_digits = 0;
+        for (; s < e; ++s) {
+            const unsigned d = (unsigned)(unsigned char)*s - (unsigned)'0';
+            if (d <= 9u) {
+                mant = mant * 10u + d;
+                ++digits, frac_digits += frac;
+            } else if (*s == ',') {
+                break;
+            } else if (*s == '.' && !frac) {
+                frac = true;
+            } else if (*s == ' ' || *s == '\r') {
+            } else {
+                simple = false;
+                break;
+            }
+        }
+        float v;
+        if (simple && digits <= 18 && frac_digits <= 22) {
+            v = (float)((double)mant / kPow10[frac_digits]);
+            if (neg) v = -v;
+        } else {
+            const char* q = (const char*)memchr(p, ',', (size_t)(e - p));
+            if (!q) q = e;
+            v = strtof(std::string(p, q).c_str(), nullptr);
+            s = q;
+        }
+        if (s < e) {               // a feature column
             if (v != 0.f) emit(col, v);
         } else {
             last = v;              // last column: the label
         }
         ++col;
-        p = q + 1;
+        p = s + 1;
     }
     *ncols = col;
     return (int)last;
@@ -436,6 +459,9 @@ extern "C" int psb_buffers_on_batch(void** buffers, int num_buffers, const int* 
 #include <thread>
 
 #include <cuda_fp16.h>
+#if defined(__SSE2__) && !defined(PSB_NO_SIMD)
+#include <emmintrin.h>
+#endif
 
 extern "C" long long psb_pack_palette_dense(const uint16_t* rows, long long n_rows, int F, uint32_t* out_bitmap,
                                             int* out_row_off, uint8_t* out_payload, long long payload_capacity);
@@ -473,8 +499,11 @@ void producer_main(Producer* P) {
     }
     const auto t0 = std::chrono::steady_clock::now();
     auto now_ms = [&] { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count(); };
-    std::vector<char> line(1 << 16);
-    std::string acc;
+    // The file is read in 4 MB blocks and lines are cut with memchr: a row of another rank's partition costs one
+    // scan for its newline, nothing is copied per line.  A line longer than the block grows the block.
+    std::vector<char> buf((size_t)4 << 20);
+    size_t have = 0, pos = 0;                  // buf[pos, have) is unread
+    bool file_done = false;
     long long row_count = 0;
     const long long warm = (long long)P->num_workers * 128;
     int batch = 0, fill = 0;
@@ -501,18 +530,43 @@ void producer_main(Producer* P) {
         }
         return true;
     };
+    // next line without its terminator in [*lp, *le); false at the end of the file
+    auto next_line = [&](const char** lp, const char** le) -> bool {
+        for (;;) {
+            const char* nl = have > pos ? (const char*)memchr(buf.data() + pos, '\n', have - pos) : nullptr;
+            if (nl) {
+                *lp = buf.data() + pos, *le = nl;
+                pos = (size_t)(nl - buf.data()) + 1;
+                return true;
+            }
+            if (file_done) {
+                if (have == pos) return false;
+                *lp = buf.data() + pos, *le = buf.data() + have;      // last line without a newline
+                pos = have;
+                return true;
+            }
+            if (pos) {
+                memmove(buf.data(), buf.data() + pos, have - pos);
+                have -= pos, pos = 0;
+            }
+            if (have == buf.size()) buf.resize(buf.size() * 2);
+            const size_t got = fread(buf.data() + have, 1, buf.size() - have, f);
+            have += got;
+            if (got == 0) file_done = true;
+        }
+    };
     bool first = true;
-    while (!P->stop.load() && fgets(line.data(), (int)line.size(), f)) {
-        acc.assign(line.data());
-        while (!acc.empty() && acc.back() != '\n' && fgets(line.data(), (int)line.size(), f)) acc += line.data();
-        while (!acc.empty() && (acc.back() == '\n' || acc.back() == '\r' || acc.back() == ' ')) acc.pop_back();
+    const char *lp, *le;
+    while (!P->stop.load(std::memory_order_relaxed) && next_line(&lp, &le)) {
+        while (le > lp && (le[-1] == '\r' || le[-1] == ' ')) --le;
         if (first && P->has_header) {
             first = false;
             continue;
         }
         first = false;
-        if (acc.empty()) continue;
+        if (le == lp) continue;
         const int part = (int)(row_count % P->num_workers);
+        double t_row = -1.0;                   // one clock read per kept row; every 64th row of other partitions
         if (part >= P->wbegin && part < P->wbegin + P->wcount) {
             if (fill == 0) {
                 if (!wait_free()) break;
@@ -522,19 +576,22 @@ void producer_main(Producer* P) {
             memset(dst, 0, (size_t)P->F * 2);
             int nc = 0;
             const int F = P->F;
-            const int label = parse_line(acc.data(), acc.data() + acc.size(), &nc, [&](int c, float v) {
+            const int label = parse_line(lp, le, &nc, [&](int c, float v) {
                 if (c < F) {
                     const __half h = __float2half(v);
                     memcpy(dst + c, &h, 2);
                 }
             });
             const size_t o = (size_t)batch * P->batch_rows + fill;
-            P->labels[o] = label, P->workers[o] = part - P->wbegin, P->times[o] = now_ms();
+            t_row = now_ms();
+            P->labels[o] = label, P->workers[o] = part - P->wbegin, P->times[o] = t_row;
             if (++fill == P->batch_rows) publish();
+        } else if ((row_count & 63) == 0) {
+            t_row = now_ms();
         }
         ++row_count;
-        P->rows_sent.store(row_count);
-        if (fill && now_ms() - batch_t0 > P->flush_ms) publish();
+        P->rows_sent.store(row_count, std::memory_order_relaxed);
+        if (fill && t_row >= 0.0 && t_row - batch_t0 > P->flush_ms) publish();
         if (P->p_ms > 0 && row_count >= warm) {
             int sleep_ms = 0;
             if (P->p_ms <= 1000) {
@@ -645,6 +702,54 @@ extern "C" void psb_producer_stop(void* h) {
 }
 
 // ------------------------------------------------------------------ bitmap packing (host side of psb_ring_store_bitmap)
+namespace {
+// Bit b of the result: fp16 value p[b] (b < 32) is non-zero; +0.0 and -0.0 are both "absent".
+#if defined(__SSE2__) && !defined(PSB_NO_SIMD)
+inline uint32_t nonzero_mask32(const uint16_t* p) {
+    const __m128i mag = _mm_set1_epi16(0x7fff), zero = _mm_setzero_si128();
+    const __m128i a = _mm_cmpeq_epi16(_mm_and_si128(_mm_loadu_si128((const __m128i*)(p)), mag), zero);
+    const __m128i b = _mm_cmpeq_epi16(_mm_and_si128(_mm_loadu_si128((const __m128i*)(p + 8)), mag), zero);
+    const __m128i c = _mm_cmpeq_epi16(_mm_and_si128(_mm_loadu_si128((const __m128i*)(p + 16)), mag), zero);
+    const __m128i d = _mm_cmpeq_epi16(_mm_and_si128(_mm_loadu_si128((const __m128i*)(p + 24)), mag), zero);
+    const uint32_t lo = (uint32_t)_mm_movemask_epi8(_mm_packs_epi16(a, b));      // bit set = value is zero
+    const uint32_t hi = (uint32_t)_mm_movemask_epi8(_mm_packs_epi16(c, d));
+    return ~(lo | (hi << 16));
+}
+#else
+// Four values per 64-bit word: rows are ~95 % zeros, so most words cost one load and one test.
+inline uint32_t nonzero_mask32(const uint16_t* p) {
+    uint32_t bits = 0;
+    for (int q = 0; q < 8; ++q) {
+        uint64_t x;
+        memcpy(&x, p + 4 * q, 8);
+        x &= 0x7fff7fff7fff7fffULL;
+        if (x) {
+            // lane <= 0x7fff, so lane + 0x7fff sets bit 15 of the lane iff lane != 0 and never carries over;
+            // the multiply gathers bits 0 / 16 / 32 / 48 into bits 48..51
+            const uint64_t t = ((x + 0x7fff7fff7fff7fffULL) >> 15) & 0x0001000100010001ULL;
+            bits |= (uint32_t)(((t * 0x0001000200040008ULL) >> 48) & 0xFu) << (4 * q);
+        }
+    }
+    return bits;
+}
+#endif
+
+// Appends the values of src[0..32) whose bit is set in `bits` to out[k...] in order and returns the new k.  The first
+// four go without a data-dependent branch (a 32-value group of a ~5 % dense row holds 0-3 non-zeros, so a loop over
+// the set bits mispredicts its exit on nearly every group); a step with no bit left stores a dummy at out[k], which
+// is inside the caller's buffer: such a group has at least 28 absent values, so k <= capacity - 28.
+inline long long gather32(const uint16_t* src, uint32_t bits, uint16_t* out, long long k) {
+    uint32_t m = bits;
+    for (int i = 0; i < 4; ++i) {
+        out[k] = src[__builtin_ctz(m | 0x80000000u)];
+        k += m != 0;
+        m &= m - 1;
+    }
+    for (; m; m &= m - 1) out[k++] = src[__builtin_ctz(m)];
+    return k;
+}
+}  // namespace
+
 extern "C" long long psb_pack_bitmap_dense(const uint16_t* rows, long long n_rows, int F, uint32_t* out_bitmap,
                                            int* out_row_off, uint16_t* out_values) {
     if (!rows || !out_bitmap || !out_row_off || !out_values || F % 32 != 0) {
@@ -657,14 +762,8 @@ extern "C" long long psb_pack_bitmap_dense(const uint16_t* rows, long long n_row
         const uint16_t* row = rows + (size_t)r * F;
         out_row_off[r] = (int)k;
         for (int w = 0; w < words; ++w) {
-            uint32_t bits = 0;
-            for (int b = 0; b < 32; ++b) {
-                const uint16_t h = row[w * 32 + b];
-                if (h & 0x7fffu) {                       // +0.0 and -0.0 are both "absent"
-                    bits |= 1u << b;
-                    out_values[k++] = h;
-                }
-            }
+            const uint32_t bits = nonzero_mask32(row + w * 32);
+            k = gather32(row + w * 32, bits, out_values, k);
             out_bitmap[(size_t)r * words + w] = bits;
         }
     }
@@ -680,26 +779,27 @@ extern "C" long long psb_pack_bitmap_csr(const long long* indptr, const int* ind
         return -1;
     }
     const int words = F / 32;
-    std::vector<uint16_t> dense((size_t)F);
+    std::vector<uint16_t> dense((size_t)F, (uint16_t)0);
+    std::vector<uint32_t> touched((size_t)words, 0u);
     long long k = 0;
     for (long long r = 0; r < n_rows; ++r) {
-        // column order of the source is not trusted: go through a dense scratch row (F is small)
-        std::fill(dense.begin(), dense.end(), (uint16_t)0);
+        // column order of the source is not trusted (and a column may repeat: the last entry wins): go through a
+        // dense scratch row, of which only the 32-value groups this row touched are read and cleared again
         for (long long e = indptr[r]; e < indptr[r + 1]; ++e) {
             const int c = indices[e];
             if (c < 0 || c >= F) continue;
             const __half h = __float2half(values[e]);
             memcpy(&dense[c], &h, 2);
+            touched[c >> 5] = 1u;
         }
         out_row_off[r] = (int)k;
         for (int w = 0; w < words; ++w) {
             uint32_t bits = 0;
-            for (int b = 0; b < 32; ++b) {
-                const uint16_t h = dense[w * 32 + b];
-                if (h & 0x7fffu) {
-                    bits |= 1u << b;
-                    out_values[k++] = h;
-                }
+            if (touched[w]) {
+                bits = nonzero_mask32(dense.data() + w * 32);
+                k = gather32(dense.data() + w * 32, bits, out_values, k);
+                memset(dense.data() + w * 32, 0, 64);
+                touched[w] = 0u;
             }
             out_bitmap[(size_t)r * words + w] = bits;
         }
@@ -722,7 +822,8 @@ extern "C" long long psb_pack_palette_dense(const uint16_t* rows, long long n_ro
     }
     const int words = F / 32;
     long long off = 0;
-    std::vector<uint8_t> codes((size_t)F);
+    std::vector<uint8_t> codes((size_t)F + 1);
+    std::vector<uint16_t> vals((size_t)F);
     for (long long r = 0; r < n_rows; ++r) {
         const uint16_t* row = rows + (size_t)r * F;
         if (off + 2 + 2LL * F > payload_capacity) {
@@ -730,36 +831,53 @@ extern "C" long long psb_pack_palette_dense(const uint16_t* rows, long long n_ro
             return -1;
         }
         out_row_off[r] = (int)off;
-        uint16_t pal[16];
-        int npal = 0, nnz = 0;
-        bool overflow = false;
+        uint32_t* bitmap = out_bitmap + (size_t)r * words;
+        long long nz = 0;                                   // the row's non-zeros, in feature order
         for (int w = 0; w < words; ++w) {
-            uint32_t bits = 0;
-            for (int b = 0; b < 32; ++b) {
-                const uint16_t h = row[w * 32 + b];
-                if (!(h & 0x7fffu)) continue;
-                bits |= 1u << b;
-                if (!overflow) {
-                    int c = 0;
-                    while (c < npal && pal[c] != h) ++c;
-                    if (c == npal) {
-                        if (npal == 16) overflow = true;
-                        else pal[npal++] = h;
-                    }
-                    codes[nnz] = (uint8_t)c;
-                }
-                ++nnz;
-            }
-            out_bitmap[(size_t)r * words + w] = bits;
+            const uint32_t bits = nonzero_mask32(row + w * 32);
+            bitmap[w] = bits;
+            nz = gather32(row + w * 32, bits, vals.data(), nz);
         }
+        const int nnz = (int)nz;
+        alignas(16) uint16_t pal[16] = {0};                 // 0 never equals a non-zero value: free entries do not match
+        int npal = 0;
+        bool overflow = false;
+#if defined(__SSE2__) && !defined(PSB_NO_SIMD)
+        __m128i p0 = _mm_setzero_si128(), p1 = _mm_setzero_si128();
+        for (int i = 0; i < nnz; ++i) {
+            const __m128i h = _mm_set1_epi16((short)vals[i]);
+            const int hit = _mm_movemask_epi8(_mm_packs_epi16(_mm_cmpeq_epi16(p0, h), _mm_cmpeq_epi16(p1, h)));
+            int c;
+            if (hit) {
+                c = __builtin_ctz((unsigned)hit);
+            } else {
+                if (npal == 16) {
+                    overflow = true;
+                    break;
+                }
+                pal[npal] = vals[i];
+                c = npal++;
+                p0 = _mm_load_si128((const __m128i*)pal), p1 = _mm_load_si128((const __m128i*)(pal + 8));
+            }
+            codes[i] = (uint8_t)c;
+        }
+#else
+        for (int i = 0; i < nnz && !overflow; ++i) {
+            const uint16_t h = vals[i];
+            int c = 0;
+            while (c < npal && pal[c] != h) ++c;
+            if (c == npal) {
+                if (npal == 16) overflow = true;
+                else pal[npal++] = h;
+            }
+            codes[i] = (uint8_t)c;
+        }
+#endif
         uint8_t* p = out_payload + off;
         if (overflow || nnz == 0) {
             const uint16_t zero = 0;
             memcpy(p, &zero, 2);
-            uint16_t* v = (uint16_t*)(p + 2);
-            int k = 0;
-            for (int f = 0; f < F && nnz; ++f)
-                if (row[f] & 0x7fffu) v[k++] = row[f];
+            if (nnz) memcpy(p + 2, vals.data(), (size_t)nnz * 2);
             off += 2 + 2LL * nnz;
         } else {
             const uint16_t np = (uint16_t)npal;
@@ -767,10 +885,8 @@ extern "C" long long psb_pack_palette_dense(const uint16_t* rows, long long n_ro
             memcpy(p + 2, pal, (size_t)npal * 2);
             uint8_t* c = p + 2 + 2 * npal;
             const int nb = (nnz + 1) / 2;
-            for (int i = 0; i < nb; ++i) {
-                const uint8_t lo = codes[2 * i], hi = 2 * i + 1 < nnz ? codes[2 * i + 1] : 0;
-                c[i] = (uint8_t)(lo | (hi << 4));
-            }
+            codes[nnz] = 0;                                   // high nibble of the last byte when the count is odd
+            for (int i = 0; i < nb; ++i) c[i] = (uint8_t)(codes[2 * i] | (codes[2 * i + 1] << 4));
             off += 2 + 2LL * npal + ((nb + 1) & ~1);
         }
     }

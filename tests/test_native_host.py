@@ -117,6 +117,35 @@ def test_csv_tokenizer_matches_numpy_reader(tmp_path):
     assert len(a) == 301 and np.allclose(a.row(300)[1], [1e-3, -0.25]) and a.row(300)[2] == 4
 
 
+def test_csv_tokenizer_field_forms(tmp_path):
+    """Every way a field is taken: the 8-byte run skip of "0,0,0,0," at every alignment, "0.0", signs, blanks,
+    leading zeros, long digit strings (strtof beyond 18 digits), exponents, a zero label and a missing final newline
+    (CsvProducer.java:46-58 splits on ',' and parses floats)."""
+    rng = np.random.default_rng(2)
+    forms = ["0", "0.0", "-0", "+0.50", "1", "-1", "007.25", " 3.5", "2.5 ", ".5", "5.", "-.125", "1e-3", "-2.5E+1",
+             "0.000021181", "123456789012345678", "1234567890123456789012", "0.1234567890123456789", "0e5", ""]
+    lines, want = [], []
+    for r in range(60):
+        fields = ["0"] * 40
+        for c in rng.choice(40, size=rng.integers(0, 9), replace=False):
+            fields[c] = forms[rng.integers(0, len(forms))]
+        if r == 7:
+            fields = ["0"] * 40                                   # an all-zero row
+        label = str(int(rng.integers(0, 6)))
+        lines.append(",".join(fields + [label]))
+        want.append(([float(f.strip() or 0) for f in fields], int(label)))
+    path = os.path.join(tmp_path, "forms.csv")
+    with open(path, "w") as f:
+        f.write(",".join(str(i) for i in range(40)) + ",Score\n" + "\n".join(lines))     # no newline at the end
+    a = native.csv_to_csr(path)
+    assert len(a) == 60 and a.num_features == 40
+    for r, (vals, label) in enumerate(want):
+        idx, v, lab = a.row(r)
+        ref = np.asarray(vals, dtype=np.float32)
+        assert lab == label and idx.tolist() == np.nonzero(ref)[0].tolist()
+        assert np.allclose(v, ref[ref != 0], rtol=1e-6, atol=0)
+
+
 def test_bitmap_packers_roundtrip_dense_and_csr():
     """psb_pack_bitmap_dense / _csr: presence bitmap + fp16 values reproduce the fp16 rows bit for bit
     (sparse wire format of ingestion; LabeledData.java:14-28)."""

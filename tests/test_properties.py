@@ -92,10 +92,14 @@ def test_wire_formats_are_lossless(n, F, density, distinct, seed):
     vocab = rng.standard_normal(distinct).astype(np.float16)
     vocab[vocab == 0] = np.float16(0.5)
     rows = (vocab[rng.integers(0, distinct, (n, F))] * (rng.random((n, F)) < density)).astype(np.float16)
+    special = np.array([0x8000, 0x0001, 0x8001, 0x7c00, 0xfc00, 0x7e00, 0xffff], dtype=np.uint16)    # -0, denormals, inf, nan
+    hit = rng.random((n, F)) < 0.02
+    rows.view(np.uint16)[hit] = special[rng.integers(0, len(special), int(hit.sum()))]
     labels = rng.integers(1, 6, n).astype(np.int32)
-    ref = np.where(rows == 0, np.float16(0), rows).view(np.uint16)
+    bits = rows.view(np.uint16)
+    ref = np.where((bits & 0x7fff) == 0, np.uint16(0), bits)                  # +0 / -0 are absent, all else is kept
     for palette in (False, True):
-        pk = native.PackedRows(n + 2, F, pin=False, palette=palette).pack_dense(rows, labels)
+        pk = native.PackedRows(n, F, pin=False, palette=palette).pack_dense(rows, labels)       # buffers of exact size
         assert np.array_equal(pk.to_dense().view(np.uint16), ref)
         assert pk.labels[:n].tolist() == labels.tolist()
     dense_bytes = n * F * 2

@@ -1,0 +1,111 @@
+// AddressSanitizer / UBSan driver for the host packers and the CSV tokenizer: buffers of exactly the documented size,
+// rows from empty to fully dense, so that any store past a buffer's end is caught.  `make asan`.
+#include <cstdint>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <random>
+#include <vector>
+
+#include "../include/psb200.h"
+
+static void expect(bool ok, const char* what) {
+    if (!ok) {
+        fprintf(stderr, "asan driver: %s\n", what);
+        exit(1);
+    }
+}
+
+int main() {
+    std::mt19937 rng(7);
+    const double densities[] = {0.0, 0.02, 0.05, 0.3, 0.9, 1.0};
+    long long checked = 0;
+    for (int F : {32, 96, 1024})
+        for (double dens : densities)
+            for (int distinct : {3, 16, 17, 400}) {
+                const int n = 9;
+                uint16_t* rows = (uint16_t*)malloc((size_t)n * F * 2);
+                for (int i = 0; i < n * F; ++i) {
+                    const bool on = (rng() % 10000) < dens * 10000;
+                    uint16_t v = (uint16_t)(0x3c00 + (rng() % distinct));
+                    if (rng() % 2) v |= 0x8000;
+                    rows[i] = on ? v : (uint16_t)((rng() % 2) ? 0x8000 : 0);      // -0.0 counts as absent
+                }
+                uint32_t* bitmap = (uint32_t*)malloc((size_t)n * (F / 32) * 4);
+                int* row_off = (int*)malloc((size_t)(n + 1) * 4);
+                uint16_t* values = (uint16_t*)malloc((size_t)n * F * 2);
+                const long long cap = (long long)n * (2 * F + 2);
+                uint8_t* payload = (uint8_t*)malloc((size_t)cap);
+                const long long nnz = psb_pack_bitmap_dense(rows, n, F, bitmap, row_off, values);
+                long long want = 0;
+                for (int i = 0; i < n * F; ++i) want += (rows[i] & 0x7fff) != 0;
+                expect(nnz == want && row_off[n] == want, "bitmap packer: wrong number of non-zeros");
+                long long k = 0;
+                for (int i = 0; i < n * F; ++i)
+                    if (rows[i] & 0x7fff) expect(values[k++] == rows[i], "bitmap packer: wrong value order");
+                const long long bytes = psb_pack_palette_dense(rows, n, F, bitmap, row_off, payload, cap);
+                expect(bytes >= 2 * n && bytes <= cap && row_off[n] == bytes, "palette packer: bad payload size");
+                for (int r = 0; r < n; ++r) {                         // decode and compare
+                    const uint8_t* p = payload + row_off[r];
+                    uint16_t npal;
+                    memcpy(&npal, p, 2);
+                    int j = 0;
+                    for (int f = 0; f < F; ++f) {
+                        const uint16_t h = rows[(size_t)r * F + f];
+                        const bool present = (bitmap[(size_t)r * (F / 32) + f / 32] >> (f % 32)) & 1u;
+                        expect(present == ((h & 0x7fff) != 0), "palette packer: bitmap bit");
+                        if (!present) continue;
+                        uint16_t got;
+                        if (npal == 0) {
+                            memcpy(&got, p + 2 + 2 * j, 2);
+                        } else {
+                            const uint8_t c = p[2 + 2 * npal + j / 2];
+                            memcpy(&got, p + 2 + 2 * ((j & 1) ? (c >> 4) : (c & 15)), 2);
+                        }
+                        expect(got == h, "palette packer: value");
+                        ++j;
+                    }
+                }
+                // the CSR packer: same rows as (unsorted) triplets
+                std::vector<long long> indptr(1, 0);
+                std::vector<int> idx;
+                std::vector<float> val;
+                for (int r = 0; r < n; ++r) {
+                    for (int f = F - 1; f >= 0; --f)
+                        if (rows[(size_t)r * F + f] & 0x7fff) idx.push_back(f), val.push_back((float)(1 + f % 7) * 0.25f);
+                    indptr.push_back((long long)idx.size());
+                }
+                idx.push_back(0), val.push_back(0.f);                 // keeps data() non-null for empty inputs
+                const long long nnz2 = psb_pack_bitmap_csr(indptr.data(), idx.data(), val.data(), n, F, bitmap, row_off, values);
+                expect(nnz2 == want, "csr packer: wrong number of non-zeros");
+                checked += n;
+                free(rows), free(bitmap), free(row_off), free(values), free(payload);
+            }
+    // tokenizer: lines that end inside the 8-byte zero-run compare, with and without a final newline
+    for (int cols = 1; cols <= 40; ++cols)
+        for (int tail = 0; tail < 2; ++tail) {
+            char path[] = "/tmp/psb_asan_XXXXXX";
+            const int fd = mkstemp(path);
+            expect(fd >= 0, "mkstemp");
+            FILE* f = fdopen(fd, "w");
+            for (int r = 0; r < 3; ++r) {
+                for (int c = 0; c < cols; ++c) fputs(c == cols / 2 && r == 1 ? "0.5," : "0,", f);
+                fputs(r == 2 && !tail ? "3" : "3\n", f);
+            }
+            fclose(f);
+            long long n_rows = 0, n_nnz = 0;
+            int n_cols = 0;
+            expect(psb_csv_count(path, 0, &n_rows, &n_nnz, &n_cols) == 0, "csv_count");
+            expect(n_rows == 3 && n_nnz == 1 && n_cols == cols, "csv_count: wrong shape");
+            long long* indptr = (long long*)malloc(4 * 8);
+            int* indices = (int*)malloc(4);
+            float* values = (float*)malloc(4);
+            int* labels = (int*)malloc(3 * 4);
+            expect(psb_csv_parse(path, 0, indptr, indices, values, labels, n_rows, n_nnz) == 0, "csv_parse");
+            expect(indices[0] == cols / 2 && values[0] == 0.5f && labels[2] == 3 && indptr[3] == 1, "csv_parse: wrong row");
+            free(indptr), free(indices), free(values), free(labels);
+            remove(path);
+        }
+    printf("asan driver: %lld packed rows and 80 csv files checked\n", checked);
+    return 0;
+}
