@@ -456,6 +456,8 @@ extern "C" int psb_buffers_on_batch(void** buffers, int num_buffers, const int* 
 // sleep every 1000/p rows (:75-82); p > 1000 sleeps p ms per row and p == 0 never sleeps (quirk Q7).
 #include <atomic>
 #include <chrono>
+#include <condition_variable>
+#include <mutex>
 #include <thread>
 
 #include <cuda_fp16.h>
@@ -470,7 +472,7 @@ extern "C" long long psb_pack_bitmap_dense(const uint16_t* rows, long long n_row
 namespace {
 struct Producer {
     std::string path;
-    int has_header, num_workers, wbegin, wcount, F, p_ms, batch_rows, num_batches, flush_ms;
+    int has_header, num_workers, wbegin, wcount, F, p_ms, batch_rows, num_batches, flush_ms, parse_threads = 1;
     uint16_t* rows;
     int* labels;
     int* workers;
@@ -491,6 +493,97 @@ struct Producer {
     }
 };
 
+// A kept line waiting to be tokenised into row `o` of the ring arrays.
+struct ParseJob {
+    const char* lp;
+    const char* le;
+    size_t o;
+};
+
+inline void parse_job(Producer* P, const ParseJob& j) {
+    uint16_t* dst = P->rows + j.o * (size_t)P->F;
+    memset(dst, 0, (size_t)P->F * 2);
+    int nc = 0;
+    const int F = P->F;
+    P->labels[j.o] = parse_line(j.lp, j.le, &nc, [&](int c, float v) {
+        if (c < F) {
+            const __half h = __float2half(v);
+            memcpy(dst + c, &h, 2);
+        }
+    });
+}
+
+// Helper threads of one producer: tokenising text is the cost of a kept row (~3 us), cutting lines is not (~0.6 us),
+// so the reading thread cuts the lines of a batch and the pool tokenises them side by side, each line straight into
+// its row of the batch.  run() returns when every job is done; the reading thread takes part.  A helper polls for
+// the next batch for 3 ms (longer than the reading thread needs to cut a batch or to read the next 4 MB block)
+// before it sleeps on the condition variable, and the reading thread polls for the helpers to finish: a batch is
+// ~1 ms of work, and a thread woken through the kernel starts late and often on the waker's core — sleeping
+// between batches gave 1.4x from four threads where polling gives 3.8x.  Paced streams never reach the pool
+// (fewer than 64 lines at a time are tokenised by the reading thread), so its helpers sleep.
+struct ParsePool {
+    Producer* P;
+    std::vector<std::thread> th;
+    std::mutex m;
+    std::condition_variable cv_start;
+    const ParseJob* jobs = nullptr;
+    size_t n = 0;
+    std::atomic<size_t> next{0}, busy{0};
+    std::atomic<unsigned long long> gen{0};
+    std::atomic<bool> quit{false};
+    ParsePool(Producer* P_, int helpers) : P(P_) {
+        for (int i = 0; i < helpers; ++i) th.emplace_back([this] { worker(); });
+    }
+    ~ParsePool() {
+        {
+            std::lock_guard<std::mutex> l(m);
+            quit.store(true);
+        }
+        cv_start.notify_all();
+        for (auto& t : th) t.join();
+    }
+    void drain() {
+        for (;;) {
+            const size_t i = next.fetch_add(16);
+            if (i >= n) return;
+            for (size_t j = i; j < std::min(i + 16, n); ++j) parse_job(P, jobs[j]);
+        }
+    }
+    void worker() {
+        unsigned long long seen = 0;
+        for (;;) {
+            const auto t0 = std::chrono::steady_clock::now();
+            for (int spins = 0; gen.load(std::memory_order_acquire) == seen && !quit.load(std::memory_order_relaxed); ++spins) {
+                if ((spins & 255) == 255 && std::chrono::steady_clock::now() - t0 > std::chrono::microseconds(3000)) {
+                    std::unique_lock<std::mutex> l(m);
+                    cv_start.wait(l, [&] { return quit.load() || gen.load() != seen; });
+                    break;
+                }
+            }
+            if (quit.load()) return;
+            seen = gen.load(std::memory_order_acquire);      // jobs / n / next were written before gen moved
+            drain();
+            busy.fetch_sub(1, std::memory_order_release);
+        }
+    }
+    void run(const ParseJob* j, size_t count) {
+        if (th.empty() || count < 64) {
+            for (size_t i = 0; i < count; ++i) parse_job(P, j[i]);
+            return;
+        }
+        {
+            std::lock_guard<std::mutex> l(m);                // (the lock orders gen against a helper about to sleep)
+            jobs = j, n = count;
+            next.store(0);
+            busy.store(th.size());
+            gen.fetch_add(1, std::memory_order_release);
+        }
+        cv_start.notify_all();
+        drain();
+        while (busy.load(std::memory_order_acquire) != 0) std::this_thread::yield();
+    }
+};
+
 void producer_main(Producer* P) {
     FILE* f = fopen(P->path.c_str(), "rb");
     if (!f) {
@@ -508,8 +601,21 @@ void producer_main(Producer* P) {
     const long long warm = (long long)P->num_workers * 128;
     int batch = 0, fill = 0;
     double batch_t0 = 0.0;
+    ParsePool pool(P, P->parse_threads - 1);
+    std::vector<ParseJob> jobs;                // lines of the batch being filled, cut and not yet tokenised
+    jobs.reserve((size_t)P->batch_rows);
+    double ms_parse = 0.0, ms_pack = 0.0, ms_wait = 0.0;       // where the thread's time went (PSB_PRODUCER_TRACE)
+    auto flush_jobs = [&] {                    // before the text they point into moves, and before a batch is published
+        if (jobs.empty()) return;
+        const double t = now_ms();
+        pool.run(jobs.data(), jobs.size());
+        jobs.clear();
+        ms_parse += now_ms() - t;
+    };
     auto publish = [&] {
+        flush_jobs();
         if (fill == 0) return;
+        const double t_pack = now_ms();
         if (P->pk_bitmap && P->pk_payload)
             psb_pack_palette_dense(P->rows + (size_t)batch * P->batch_rows * P->F, fill, P->F,
                                    P->pk_bitmap + (size_t)batch * P->batch_rows * (P->F / 32),
@@ -520,14 +626,18 @@ void producer_main(Producer* P) {
                                   P->pk_bitmap + (size_t)batch * P->batch_rows * (P->F / 32),
                                   P->pk_row_off + (size_t)batch * (P->batch_rows + 1),
                                   P->pk_values + (size_t)batch * P->batch_rows * P->F);
+        ms_pack += now_ms() - t_pack;
         P->ready[batch].store(fill, std::memory_order_release);
         batch = (batch + 1) % P->num_batches, fill = 0;
     };
     auto wait_free = [&]() -> bool {
+        if (P->ready[batch].load(std::memory_order_acquire) == -1) return true;
+        const double t = now_ms();
         while (P->ready[batch].load(std::memory_order_acquire) != -1) {
             if (P->stop.load()) return false;
             std::this_thread::sleep_for(std::chrono::microseconds(100));
         }
+        ms_wait += now_ms() - t;
         return true;
     };
     // next line without its terminator in [*lp, *le); false at the end of the file
@@ -545,6 +655,7 @@ void producer_main(Producer* P) {
                 pos = have;
                 return true;
             }
+            flush_jobs();
             if (pos) {
                 memmove(buf.data(), buf.data() + pos, have - pos);
                 have -= pos, pos = 0;
@@ -572,19 +683,11 @@ void producer_main(Producer* P) {
                 if (!wait_free()) break;
                 batch_t0 = now_ms();
             }
-            uint16_t* dst = P->rows + ((size_t)batch * P->batch_rows + fill) * P->F;
-            memset(dst, 0, (size_t)P->F * 2);
-            int nc = 0;
-            const int F = P->F;
-            const int label = parse_line(lp, le, &nc, [&](int c, float v) {
-                if (c < F) {
-                    const __half h = __float2half(v);
-                    memcpy(dst + c, &h, 2);
-                }
-            });
             const size_t o = (size_t)batch * P->batch_rows + fill;
             t_row = now_ms();
-            P->labels[o] = label, P->workers[o] = part - P->wbegin, P->times[o] = t_row;
+            P->workers[o] = part - P->wbegin, P->times[o] = t_row;
+            jobs.push_back(ParseJob{lp, le, o});
+            if (P->parse_threads == 1 || (P->p_ms > 0 && row_count >= warm)) flush_jobs();     // paced rows go out one by one
             if (++fill == P->batch_rows) publish();
         } else if ((row_count & 63) == 0) {
             t_row = now_ms();
@@ -608,6 +711,9 @@ void producer_main(Producer* P) {
     }
     publish();
     fclose(f);
+    if (getenv("PSB_PRODUCER_TRACE"))
+        fprintf(stderr, "psb producer: %lld rows read in %.1f ms with %d tokenising thread(s): tokenise %.1f ms, pack %.1f ms, "
+                        "waiting for a free batch %.1f ms\n", row_count, now_ms(), P->parse_threads, ms_parse, ms_pack, ms_wait);
     P->eof.store(1);
 }
 }  // namespace
@@ -666,6 +772,11 @@ static void* producer_start_impl(const char* path, int has_header, int num_worke
     P->rows = (uint16_t*)h_rows_f16, P->labels = h_labels, P->workers = h_workers, P->times = h_times;
     P->pk_bitmap = h_bitmap, P->pk_row_off = h_row_off, P->pk_values = (uint16_t*)h_values_f16;
     P->pk_payload = h_payload, P->pk_stride = payload_stride;
+    // threads that tokenise (the reading thread included): PSB_PRODUCER_THREADS, else a sixteenth of the cores (one
+    // process per GPU on an 8-GPU node, each with its Python threads beside this one), at most 4
+    int threads = (int)std::min(4u, std::max(1u, std::thread::hardware_concurrency() / 16u));
+    if (const char* e = getenv("PSB_PRODUCER_THREADS")) threads = atoi(e);
+    P->parse_threads = std::max(1, std::min(threads, 16));
     P->th = std::thread(producer_main, P);
     return P;
 }

@@ -4,7 +4,7 @@ import time
 
 import numpy as np
 
-from psb200.data import ReviewGenerator, write_csv
+from psb200.data import ReviewGenerator, read_csv, write_csv
 from psb200.ops import native
 
 
@@ -90,3 +90,29 @@ def test_packed_batches_expand_to_the_dense_rows(tmp_path, mode):
         prod.release(bi)
     prod.stop()
     assert seen == 300
+
+
+@pytest.mark.parametrize("threads", [1, 3])
+def test_tokenising_helper_threads_give_the_rows_of_the_single_thread(tmp_path, monkeypatch, threads):
+    """PSB_PRODUCER_THREADS: the reading thread cuts the lines of a batch, helper threads tokenise them side by
+    side, each line into its own row — rows, labels, partitions and their order must not depend on the thread
+    count (CsvProducer.java:46-61 is one thread; the lines are independent).  The last line has no newline."""
+    F, n = 96, 2500
+    b = ReviewGenerator(num_features=F, vocab=700, mean_len=20).train_split(n)
+    path = os.path.join(tmp_path, "t.csv")
+    write_csv(path, b)
+    with open(path, "rb+") as f:                     # cut the final newline off
+        f.seek(-1, os.SEEK_END)
+        if f.read(1) == b"\n":
+            f.seek(-1, os.SEEK_END)
+            f.truncate()
+    monkeypatch.setenv("PSB_PRODUCER_THREADS", str(threads))
+    prod = native.StreamProducer(path, 3, 0, 2, F, 0, batch_rows=256, num_batches=3, packed="palette")  # partitions 0, 1 of 3
+    rows, labels, workers, times, eof = _drain(prod)
+    prod.stop()
+    idx = np.nonzero(np.arange(n) % 3 < 2)[0]
+    assert eof == 1 and len(rows) == len(idx)
+    assert np.array_equal(labels, b.labels[idx]) and np.array_equal(workers, idx % 3)
+    text = read_csv(path).to_dense(np.float32)        # the values as written (6 decimals), rounded to fp16 once
+    assert np.array_equal(rows.view(np.uint16), text[idx].astype(np.float16).view(np.uint16))
+    assert (np.diff(times) >= 0).all()

@@ -47,26 +47,29 @@ def main():
         t = best(lambda: native.csv_to_csr(path), a.reps)
         out.append({"stage": "csv_count+parse", "rows_per_s": a.rows / t, "MB_per_s": size / t / 1e6,
                     "file_MB": size / 1e6})
-        for packed in (False, "palette"):
-            for parts in (1, 8):                      # this rank keeps every row / one partition in eight
-                def stream():
-                    prod = native.StreamProducer(path, parts, 0, 1, F, 0, batch_rows=512, num_batches=4, packed=packed)
-                    got = 0
-                    while True:
-                        b, n, eof = prod.poll()
-                        if b is None:
-                            if eof:
-                                break
-                            time.sleep(0.0002)
-                            continue
-                        got += n
-                        prod.release(b)
-                    prod.stop()
-                    assert got == (a.rows + parts - 1) // parts, got
-                t = best(stream, max(2, a.reps // 2))
-                out.append({"stage": f"producer thread ({'palette-packed' if packed else 'dense'} batches, "
-                                     f"keeps 1 row in {parts})", "file_rows_per_s": a.rows / t,
-                            "kept_rows_per_s": a.rows / parts / t})
+        for packed, parts, threads in ((False, 1, 1), (False, 8, 1), ("palette", 1, 1), ("palette", 1, 2),
+                                       ("palette", 1, 4)):
+            # parts: this rank keeps every row / one partition in eight; threads: PSB_PRODUCER_THREADS
+            def stream():
+                os.environ["PSB_PRODUCER_THREADS"] = str(threads)
+                prod = native.StreamProducer(path, parts, 0, 1, F, 0, batch_rows=512, num_batches=4, packed=packed)
+                got = 0
+                while True:
+                    b, n, eof = prod.poll()
+                    if b is None:
+                        if eof:
+                            break
+                        time.sleep(0.0002)
+                        continue
+                    got += n
+                    prod.release(b)
+                prod.stop()
+                assert got == (a.rows + parts - 1) // parts, got
+            t = best(stream, max(3, a.reps))
+            out.append({"stage": f"producer ({'palette-packed' if packed else 'dense'} batches, keeps 1 row in "
+                                 f"{parts}, {threads} tokenising thread{'s' if threads > 1 else ''})",
+                        "file_rows_per_s": a.rows / t, "kept_rows_per_s": a.rows / parts / t})
+        os.environ.pop("PSB_PRODUCER_THREADS", None)
 
     for palette in (False, True):
         pk = native.PackedRows(a.rows, F, pin=False, palette=palette)

@@ -1,5 +1,5 @@
 // ThreadSanitizer driver for the C++ host runtime (csrc/host_runtime.cpp): the streaming producer thread filling its
-// ring of batches (tokenise, palette-pack, publish) against a consumer that polls, holds several batches at a
+// ring of batches (cut lines, tokenise them with two helper threads, palette-pack, publish) against a consumer that polls, holds several batches at a
 // time and releases them in order — the access pattern of apps/node.py and apps/p2p_apps.py — plus the buffer
 // policy and tracker used from a second thread the way the engine's slot-assignment helper thread uses them.
 // Build + run: make tsan   (host-only: no GPU, no libcudart calls are made)
@@ -36,6 +36,7 @@ int main() {
     std::vector<uint32_t> h_bitmap((size_t)nb * batch_rows * (F / 32));
     const long long stride = (long long)batch_rows * (2 * F + 2);
     std::vector<uint8_t> h_payload((size_t)nb * stride);
+    setenv("PSB_PRODUCER_THREADS", "3", 1);          // the reading thread + two tokenising helpers
     void* p = psb_producer_start_palette(path.c_str(), 1, W, 0, W, F, 0, batch_rows, nb, h_rows.data(), h_labels.data(),
                                          h_workers.data(), h_times.data(), 5, h_bitmap.data(), h_off.data(),
                                          h_payload.data(), stride);
