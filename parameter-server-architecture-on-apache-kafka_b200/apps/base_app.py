@@ -28,10 +28,10 @@ def load_csv_or_synthetic(path: str, cfg: PSConfig, kind: str) -> CSRBatch:
     try:
         from ..ops import native
         if native.available():
-            return native.csv_to_csr(path, has_header=True)
+            return native.csv_to_csr(path, has_header=cfg.csv_header)
     except Exception:
         pass
-    return read_csv(path, has_header=True)
+    return read_csv(path, has_header=cfg.csv_header)
 
 
 class BaseApp:

@@ -54,6 +54,8 @@ def _common(p: argparse.ArgumentParser) -> None:
     p.add_argument("--rendezvous", default=None, help="override the rendezvous address host:port")
     p.add_argument("--no_standardize", action="store_true")
     p.add_argument("--compat_q1", action="store_true", help="replicate the reference's off-by-one on key 6149")
+    p.add_argument("--no_header", action="store_true",
+                   help="the CSV files have no header line (the reference always skips one, CsvProducer.java:41-43)")
 
 
 def server_parser() -> argparse.ArgumentParser:
@@ -100,7 +102,7 @@ def config_from_args(ns: argparse.Namespace, role: str) -> PSConfig:
     cfg = PSConfig(num_workers=ns.num_workers, num_features=ns.num_features, num_classes=ns.num_classes,
                    test_data_file_path=ns.test_data_file_path, local_solver=ns.local_solver, init=ns.init,
                    seed=ns.seed, transport=ns.transport, remote=ns.remote, verbose=ns.verbose,
-                   logging=ns.logging, standardize=not ns.no_standardize, compat_q1=ns.compat_q1,
+                   logging=ns.logging, standardize=not ns.no_standardize, compat_q1=ns.compat_q1, csv_header=not ns.no_header,
                    min_buffer_size=ns.min_buffer_size, max_buffer_size=ns.max_buffer_size,
                    buffer_size_coefficient=ns.buffer_size_coefficient)
     if role == "server":

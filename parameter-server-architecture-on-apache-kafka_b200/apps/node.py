@@ -126,7 +126,8 @@ def main(argv: Optional[List[str]] = None) -> int:
             raise FileNotFoundError(f"training data file not found: {cfg.training_data_file_path}")
         producer = native.StreamProducer(cfg.training_data_file_path, cfg.num_workers, rank * W, W, cfg.num_features,
                                          cfg.producer_time_per_event, batch_rows=eng.stage_rows, num_batches=4,
-                                         packed="palette")  # bitmap + palette codes over PCIe when F % 32 == 0
+                                         packed="palette",  # bitmap + palette codes over PCIe when F % 32 == 0
+                                         has_header=cfg.csv_header)
         n_total, mine, cursor = 0, np.zeros(0, dtype=np.int64), 0
     else:
         n_total = len(train)

@@ -92,10 +92,11 @@ class MemoryProducer:
 class FileProducer:
     """The C++ producer thread (``psb_producer_start_palette``) behind the same small interface."""
 
-    def __init__(self, path: str, num_workers: int, num_features: int, p_ms: int, batch_rows: int, num_batches: int = 4):
+    def __init__(self, path: str, num_workers: int, num_features: int, p_ms: int, batch_rows: int, num_batches: int = 4,
+                 has_header: bool = True):
         from ..ops import native
         self.p = native.StreamProducer(path, num_workers, 0, num_workers, num_features, p_ms, batch_rows=batch_rows,
-                                       num_batches=num_batches, packed="palette")
+                                       num_batches=num_batches, packed="palette", has_header=has_header)
 
     def poll(self):
         return self.p.poll()
@@ -414,7 +415,8 @@ def make_producer(cfg: PSConfig, batch_rows: int):
                               cfg.producer_time_per_event, batch_rows)
     if not os.path.exists(path):
         raise FileNotFoundError(f"training data file not found: {path}")
-    return FileProducer(path, cfg.num_workers, cfg.num_features, cfg.producer_time_per_event, batch_rows)
+    return FileProducer(path, cfg.num_workers, cfg.num_features, cfg.producer_time_per_event, batch_rows,
+                        has_header=cfg.csv_header)
 
 
 def run_server(app, cfg: PSConfig, ns, server_log: LogSink, worker_log: Optional[LogSink]) -> None:

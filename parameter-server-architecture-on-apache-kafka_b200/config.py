@@ -62,6 +62,7 @@ class PSConfig:
     standardize: bool = True           # Spark default standardization=true
     center: bool = True                # Spark centres multinomial coefs when regParam == 0
     compat_q1: bool = False            # replicate the off-by-one on key 6149
+    csv_header: bool = True            # the reference always skips one line (CsvProducer.java:41-43); --no_header
     init: str = "zero"                 # reference zero-inits despite the method name (Q3)
     seed: int = 0
     transport: str = "loopback"        # loopback (host event loop) | p2p (device peer memory)

@@ -23,3 +23,27 @@ def test_small_sample_sequential_two_workers(tmp_path):
     w = parse_log(str(tmp_path / "logs-worker.csv"), "worker")
     assert len(s) == 4 and len(w) >= 6 and np.all(w[:, 6] == 60)
     assert np.all((s[:, 4] >= 0) & (s[:, 4] <= 1))
+
+
+import pytest
+
+
+@pytest.mark.parametrize("name,features", [("lr_dataset_stripped.csv", 5), ("sample_input_data.csv", 99)])
+def test_headerless_binary_mock_files_train_with_no_header(tmp_path, name, features):
+    """Stand-ins of the reference's two other mock files (mockData/lr_dataset_stripped.csv: 570 rows x 6 columns,
+    mockData/sample_input_data.csv: 49 rows x 100 columns of 0 / 1; no header, binary last column; read by no code
+    of the reference).  Here they stream through the same runner with --no_header, labels 0 / 1 as class rows 0 / 1."""
+    path = os.path.join(ROOT, "mockData", name)
+    rows = np.loadtxt(path, delimiter=",", ndmin=2)
+    assert rows.shape[1] == features + 1 and set(np.unique(rows[:, -1])) == {0.0, 1.0}
+    env = dict(os.environ, PYTHONPATH=ROOT)
+    r = subprocess.run([sys.executable, "-m", "psb200.apps.server_app_runner", "-training", path, "-test", path,
+                        "--no_header", "--num_features", str(features), "--num_classes", "1", "-c", "0", "-p", "0",
+                        "--num_workers", "2", "--in_process", "--max_clock", "4", "-l", "-min", "8", "-max", "64"],
+                       env=env, cwd=tmp_path, capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stderr
+    s = parse_log(str(tmp_path / "logs-server.csv"), "server")
+    w = parse_log(str(tmp_path / "logs-worker.csv"), "worker")
+    assert len(s) == 4 and len(w) >= 6
+    assert w[:, 6].max() == (len(rows) + 1) // 2            # every row of the file reached a worker (no line skipped)
+    assert np.all(np.isfinite(s[:, 4])) and s[-1, 5] >= 0.45
