@@ -54,6 +54,8 @@ def _common(p: argparse.ArgumentParser) -> None:
     p.add_argument("--rendezvous", default=None, help="override the rendezvous address host:port")
     p.add_argument("--no_standardize", action="store_true")
     p.add_argument("--compat_q1", action="store_true", help="replicate the reference's off-by-one on key 6149")
+    p.add_argument("--metrics_port", type=int, default=0,
+                   help="serve Prometheus gauges of the log rows (clocks, loss, F1, accuracy, rows seen) on this port")
     p.add_argument("--no_header", action="store_true",
                    help="the CSV files have no header line (the reference always skips one, CsvProducer.java:41-43)")
 

@@ -116,6 +116,9 @@ def main(argv: Optional[List[str]] = None) -> int:
         server_log = LogSink.to_file("./logs-server.csv", SERVER_LOG_HEADER) if cfg.logging else LogSink()
     wl_name = "./logs-worker.csv" if rank == 0 else f"./logs-worker-{rank}.csv"
     worker_log = LogSink.to_file(wl_name, WORKER_LOG_HEADER) if cfg.logging else (LogSink() if rank == 0 else None)
+    if ns.metrics_port > 0:                         # one endpoint per rank: port + rank
+        from ..utils.monitoring import start_exporter
+        start_exporter(ns.metrics_port + rank, server_log, worker_log)
 
     # this rank's slice of the stream: global row i goes to worker i % numWorkers (CsvProducer.java:61)
     producer = None

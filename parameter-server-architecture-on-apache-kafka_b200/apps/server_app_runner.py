@@ -36,6 +36,8 @@ def main(argv: Optional[List[str]] = None) -> int:
     worker_log = None
     if ns.in_process:
         worker_log = LogSink.to_file("./logs-worker.csv", WORKER_LOG_HEADER) if cfg.logging else LogSink()
+    from ..utils.monitoring import start_exporter
+    exporter = start_exporter(ns.metrics_port, server_log, worker_log)
     if ns.rendezvous:
         import psb200.config as c
         c.RENDEZVOUS_LOCAL = c.RENDEZVOUS_REMOTE = ns.rendezvous
@@ -45,6 +47,8 @@ def main(argv: Optional[List[str]] = None) -> int:
     server_log.close()
     if worker_log is not None:
         worker_log.close()
+    if exporter is not None:
+        exporter.close()
     return 0
 
 

@@ -33,12 +33,16 @@ def main(argv: Optional[List[str]] = None) -> int:
         print(f"    broker address: {broker}")
         print()
     worker_log = LogSink.to_file("./logs-worker.csv", WORKER_LOG_HEADER) if cfg.logging else LogSink()
+    from ..utils.monitoring import start_exporter
+    exporter = start_exporter(ns.metrics_port, worker_log)
     if ns.rendezvous:
         import psb200.config as c
         c.RENDEZVOUS_LOCAL = c.RENDEZVOUS_REMOTE = ns.rendezvous
     app = WorkerApp(cfg, backend=ns.backend, worker_log=worker_log, ns=ns)
     app.call()
     worker_log.close()
+    if exporter is not None:
+        exporter.close()
     return 0
 
 

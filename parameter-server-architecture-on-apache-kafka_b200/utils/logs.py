@@ -28,6 +28,7 @@ class LogSink:
         self.stream = stream if stream is not None else sys.stdout
         self.lock = threading.Lock()
         self.rows: Optional[List[str]] = [] if keep else None
+        self.observers: list = []                 # callables fed every line (utils/monitoring.py: --metrics_port)
         if header is not None:
             self.println(header)
 
@@ -41,6 +42,8 @@ class LogSink:
             self.stream.flush()
             if self.rows is not None:
                 self.rows.append(line)
+        for obs in self.observers:
+            obs(line)
 
     def close(self) -> None:
         if self.stream not in (sys.stdout, sys.stderr):
