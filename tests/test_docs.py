@@ -31,3 +31,34 @@ def test_every_file_and_test_named_in_the_documents_exists():
                 if not os.path.exists(os.path.join(ROOT, "profiles", name)):
                     stale.add((doc, name))
     assert not stale, sorted(stale)
+
+
+def test_header_library_and_integration_table_agree():
+    """Every function include/psb200.h declares is exported by the built library and named in INTEGRATION.md's
+    table; the library exports no undeclared psb_ function (kernels' host stubs aside)."""
+    import subprocess
+
+    import pytest
+
+    from psb200.ops import native
+    if not native.available():
+        pytest.skip("libpsb200.so not built")
+    h = open(os.path.join(ROOT, "include", "psb200.h")).read()
+    h = re.sub(r"//[^\n]*", "", re.sub(r"/\*.*?\*/", "", h, flags=re.S))
+    declared = set(re.findall(r"\b(psb_\w+)\s*\(", h))
+    lib = native.lib()
+    assert not [n for n in declared if not hasattr(lib, n)]
+    out = subprocess.run(["nm", "-D", "--defined-only", lib._name], capture_output=True, text=True).stdout
+    exported = set(re.findall(r" T (psb_\w+)", out))
+    assert not [n for n in exported if n not in declared and not n.endswith("_kernel")]
+    doc = open(os.path.join(ROOT, "INTEGRATION.md")).read()
+    named = set(re.findall(r"psb_\w+", doc))
+    for stem, parts in re.findall(r"(psb_\w+?_)(\w+(?:/\w+)+)", doc):            # psb_producer_start/poll/release/stop
+        named.update(stem + p for p in parts.split("/"))
+    for stem, parts in re.findall(r"(psb_\w+)`((?: / `_\w+`)+)", doc):             # `psb_comm_version_words` / `_rank_clocks`
+        base = stem.rsplit("_", 2)[0] if stem.count("_") > 2 else stem
+        for suffix in re.findall(r"`(_\w+)`", parts):
+            named.update({base + suffix, "_".join(stem.split("_")[:2]) + suffix, "_".join(stem.split("_")[:3]) + suffix})
+    wild = [w[:-1] for w in re.findall(r"psb_\w+_\*", doc)]                        # psb_tracker_*
+    missing = [n for n in declared if n not in named and not any(n.startswith(w) for w in wild)]
+    assert not missing, sorted(missing)
