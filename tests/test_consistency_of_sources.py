@@ -1,4 +1,5 @@
-"""The documents name files and tests; every one of them must exist (COVERAGE.md is read line by line)."""
+"""Documents, header, library and bindings must agree: the files and tests the documents name exist (COVERAGE.md is
+read line by line), the header's functions are exported and listed, the ctypes mirrors match the C structs."""
 import glob
 import os
 import re
@@ -62,3 +63,46 @@ def test_header_library_and_integration_table_agree():
     wild = [w[:-1] for w in re.findall(r"psb_\w+_\*", doc)]                        # psb_tracker_*
     missing = [n for n in declared if n not in named and not any(n.startswith(w) for w in wild)]
     assert not missing, sorted(missing)
+
+
+def test_ctypes_mirrors_match_the_header_field_by_field(tmp_path):
+    """P/ops/native.py restates the structs of include/psb200.h for ctypes; a C program compiled from the header
+    prints the offset and size of every field, which must be what ctypes lays out."""
+    import ctypes
+    import shutil
+    import subprocess
+
+    import pytest
+
+    from psb200.ops import native
+    cc = shutil.which("gcc") or shutil.which("cc")
+    if cc is None:
+        pytest.skip("no C compiler")
+    mirrors = {"PsbSolver": native.PsbSolver, "PsbComm": native.PsbComm, "PsbClockRecord": native.PsbClockRecord,
+               "PsbSparseComm": native.PsbSparseComm, "PsbSlabComm": native.PsbSlabComm}
+    lines = ['#include <stdio.h>', f'#include "{os.path.join(ROOT, "include", "psb200.h")}"', "int main(void) {"]
+    for name, cls in mirrors.items():
+        lines.append(f'  printf("{name} . %zu %zu\\n", (size_t)0, sizeof({name}));')
+        for field, _ in cls._fields_:
+            lines.append(f'  printf("{name} {field} %zu %zu\\n", offsetof({name}, {field}), sizeof((({name}*)0)->{field}));')
+    lines += ["  return 0;", "}"]
+    src = tmp_path / "layout.c"
+    src.write_text("\n".join(lines) + "\n")
+    exe = tmp_path / "layout"
+    r = subprocess.run([cc, "-std=c11", str(src), "-o", str(exe)], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr                        # a field the mirror has and the header lacks fails here
+    out = subprocess.run([str(exe)], capture_output=True, text=True).stdout.split("\n")
+    seen = 0
+    for ln in filter(None, out):
+        name, field, off, size = ln.split()
+        cls = mirrors[name]
+        if field == ".":
+            assert ctypes.sizeof(cls) == int(size), (name, ctypes.sizeof(cls), size)
+        else:
+            f = getattr(cls, field)
+            assert (f.offset, f.size) == (int(off), int(size)), (name, field, f.offset, f.size, off, size)
+        seen += 1
+    assert seen == sum(len(c._fields_) + 1 for c in mirrors.values())
+    # and the header has no field the mirror lacks: the sizes above would differ unless it were padding
+    h = open(os.path.join(ROOT, "include", "psb200.h")).read()
+    assert native.MAX_RANKS == int(re.search(r"#define\s+PSB_MAX_RANKS\s+(\d+)", h).group(1))
