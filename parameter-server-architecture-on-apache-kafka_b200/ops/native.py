@@ -164,6 +164,11 @@ def lib() -> C.CDLL:
     L.psb_ipc_import.argtypes = [vp, C.POINTER(C.c_void_p)]
     L.psb_ipc_close.argtypes = [vp]
     L.psb_enable_peer_access.argtypes = [C.c_int]
+    L.psb_set_l2_fetch_granularity.argtypes = [C.c_int]
+    L.psb_static_scratch_bytes.restype = C.c_size_t
+    L.psb_static_scratch_bytes.argtypes = []
+    L.psb_worker_step_static.argtypes = [C.POINTER(PsbSolver), C.POINTER(PsbComm), C.c_int, C.c_int, vp, ip, ip, fp, fp,
+                                         fp, ip, vp]
     _lib = L
     return L
 

@@ -106,3 +106,49 @@ def test_ctypes_mirrors_match_the_header_field_by_field(tmp_path):
     # and the header has no field the mirror lacks: the sizes above would differ unless it were padding
     h = open(os.path.join(ROOT, "include", "psb200.h")).read()
     assert native.MAX_RANKS == int(re.search(r"#define\s+PSB_MAX_RANKS\s+(\d+)", h).group(1))
+
+
+def test_ctypes_signatures_match_the_header_prototypes():
+    """Every prototype of include/psb200.h against the argtypes / restype P/ops/native.py declares: the same number
+    of parameters, pointers where the header has pointers, 4-byte and 8-byte integers and floats where it has them
+    (an int passed for a size_t leaves the upper half of the register undefined)."""
+    import ctypes as C
+
+    import pytest
+
+    from psb200.ops import native
+    if not native.available():
+        pytest.skip("libpsb200.so not built")
+    lib = native.lib()
+    h = open(os.path.join(ROOT, "include", "psb200.h")).read()
+    h = re.sub(r"//[^\n]*", "", re.sub(r"/\*.*?\*/", "", h, flags=re.S))
+    scalars = {"int": "i4", "unsigned": "i4", "unsigned int": "i4", "uint32_t": "i4", "int32_t": "i4", "size_t": "i8",
+               "long long": "i8", "unsigned long long": "i8", "uint64_t": "i8", "int64_t": "i8", "float": "f4",
+               "double": "f8"}
+
+    def of_c(param):
+        param = param.strip()
+        if param in ("void", ""):
+            return None
+        if "*" in param or "[" in param or "cudaStream_t" in param:
+            return "ptr"
+        return scalars[re.sub(r"\b\w+$", "", param).replace("const", "").strip()]
+
+    def of_py(a):
+        if a in (C.c_void_p, C.c_char_p) or (isinstance(a, type) and issubclass(a, C._Pointer)):
+            return "ptr"
+        return {C.c_int: "i4", C.c_uint: "i4", C.c_size_t: "i8", C.c_longlong: "i8", C.c_ulonglong: "i8",
+                C.c_float: "f4", C.c_double: "f8"}[a]
+
+    protos = re.findall(r"([\w\s\*]+?)\b(psb_\w+)\s*\(([^;{]*?)\)\s*;", h)
+    assert len(protos) >= 69
+    for ret, name, params in protos:
+        want = [k for k in map(of_c, params.split(",")) if k]
+        f = getattr(lib, name)
+        assert f.argtypes is not None or not want, f"{name}: no argtypes declared"
+        assert [of_py(a) for a in (f.argtypes or [])] == want, name
+        ret = ret.replace("const", "").strip()
+        if "*" in ret:
+            assert f.restype in (C.c_void_p, C.c_char_p), name
+        elif ret != "void" and scalars[ret] == "i8":
+            assert f.restype in (C.c_size_t, C.c_longlong, C.c_ulonglong), name     # default restype is a 4-byte int
