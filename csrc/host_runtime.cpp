@@ -162,7 +162,7 @@ inline int parse_line(const char* p, const char* e, int* ncols, Emit emit) {
         p = s + 1;
     }
     *ncols = col;
-    return (int)last;
+    return last >= -2147483648.f && last < 2147483648.f ? (int)last : 0;      // (nan / inf / huge labels: 0, not UB)
 }
 }  // namespace
 

@@ -1,4 +1,4 @@
-// AddressSanitizer / UBSan driver for the host packers and the CSV tokenizer: buffers of exactly the documented size,
+// AddressSanitizer / UBSan driver for the host packers, the CSV tokenizer and the producer thread: buffers of exactly the documented size,
 // rows from empty to fully dense, so that any store past a buffer's end is caught.  `make asan`.
 #include <cstdint>
 #include <cstdio>
@@ -106,6 +106,73 @@ int main() {
             free(indptr), free(indices), free(values), free(labels);
             remove(path);
         }
-    printf("asan driver: %lld packed rows and 80 csv files checked\n", checked);
+    // producer thread on awkward text: an empty line, CRLF, a line longer than the 4 MB read block (the block grows),
+    // more columns than features, junk fields, no newline at the end; with and without tokenising helper threads
+    for (const char* threads : {"1", "3"}) {
+        setenv("PSB_PRODUCER_THREADS", threads, 1);
+        char path[] = "/tmp/psb_asan_prod_XXXXXX";
+        const int fd = mkstemp(path);
+        expect(fd >= 0, "mkstemp");
+        FILE* f = fdopen(fd, "w");
+        const int F = 32, rows_ok = 300;
+        for (int c = 0; c < F; ++c) fprintf(f, "%d,", c);
+        fputs("Score\n", f);
+        for (int r = 0; r < rows_ok; ++r) {
+            for (int c = 0; c < F; ++c) fputs(c == r % F ? "0.25," : "0,", f);
+            fprintf(f, "%d%s", 1 + r % 5, r % 7 == 0 ? "\r\n" : "\n");
+            if (r == 10) fputs("\n", f);                                    // an empty line is not a row
+        }
+        for (int c = 0; c < 2600000; ++c) fputs(c == 5 ? "1.5," : "0,", f);  // 5.2 MB of text in one line
+        fputs("2\n", f);
+        fputs("abc,-,+,.,0x10,1e400,nan,-0.000,", f);                         // junk in the first columns
+        for (int c = 8; c < F; ++c) fputs("0,", f);
+        fputs("4", f);                                                        // last line, no newline
+        fclose(f);
+        const int batch_rows = 128, nb = 3;
+        uint16_t* rows = (uint16_t*)malloc((size_t)nb * batch_rows * F * 2);
+        int* labels = (int*)malloc((size_t)nb * batch_rows * 4);
+        int* workers = (int*)malloc((size_t)nb * batch_rows * 4);
+        double* times = (double*)malloc((size_t)nb * batch_rows * 8);
+        uint32_t* bitmap = (uint32_t*)malloc((size_t)nb * batch_rows * (F / 32) * 4);
+        int* row_off = (int*)malloc((size_t)nb * (batch_rows + 1) * 4);
+        const long long stride = (long long)batch_rows * (2 * F + 2);
+        uint8_t* payload = (uint8_t*)malloc((size_t)nb * stride);
+        void* p = psb_producer_start_palette(path, 1, 2, 0, 2, F, 0, batch_rows, nb, rows, labels, workers, times, 5,
+                                             bitmap, row_off, payload, stride);
+        expect(p != nullptr, "producer_start");
+        long long got = 0, long_line_ok = 0, junk_ok = 0;
+        int eof = 0;
+        for (;;) {
+            int b = 0, n = 0;
+            if (psb_producer_poll(p, &b, &n, &eof)) {
+                for (int i = 0; i < n; ++i) {
+                    const size_t o = (size_t)b * batch_rows + i;
+                    const long long g = got + i;
+                    if (g < rows_ok) {
+                        expect(labels[o] == 1 + g % 5 && workers[o] == g % 2, "producer: label / partition of a plain row");
+                        expect(rows[o * F + g % F] == 0x3400, "producer: 0.25 in its column");       // fp16(0.25)
+                    } else if (g == rows_ok) {
+                        long_line_ok = labels[o] == 2 && rows[o * F + 5] == 0x3e00;                   // fp16(1.5)
+                    } else {
+                        // abc -> 0, "-" "+" "." -> 0, 0x10 -> 16, 1e400 -> inf, nan -> nan, -0.000 -> -0 (absent)
+                        junk_ok = labels[o] == 4 && rows[o * F] == 0 && rows[o * F + 4] == 0x4c00 &&
+                                  rows[o * F + 5] == 0x7c00 && (rows[o * F + 6] & 0x7c00) == 0x7c00 &&
+                                  (rows[o * F + 7] & 0x7fff) == 0;
+                    }
+                }
+                got += n;
+                psb_producer_release(p, b);
+            } else if (eof) {
+                break;
+            }
+        }
+        expect(eof == 1 && got == rows_ok + 2, "producer: wrong number of rows");
+        expect(long_line_ok && junk_ok, "producer: the long line or the junk line came out wrong");
+        expect(psb_producer_rows_sent(p) == rows_ok + 2, "producer: rows_sent");
+        psb_producer_stop(p);
+        free(rows), free(labels), free(workers), free(times), free(bitmap), free(row_off), free(payload);
+        remove(path);
+    }
+    printf("asan driver: %lld packed rows, 80 csv files and 2 awkward producer streams checked\n", checked);
     return 0;
 }
