@@ -23,7 +23,7 @@ tsan:
 asan:
 	mkdir -p build
 	for defs in "" "-DPSB_NO_SIMD"; do \
-	  g++ -std=c++17 -O1 -g $$defs -fsanitize=address,undefined -fno-sanitize-recover=all -x c++ \
+	  g++ -std=c++17 -O1 -g $$defs -fsanitize=address,undefined,float-cast-overflow,float-divide-by-zero -fno-sanitize-recover=all -x c++ \
 	      -I/usr/local/cuda/include csrc/host_runtime.cpp tools/asan_packers.cpp tools/tsan_stubs.cpp \
 	      -o build/asan_packers -lpthread && ./build/asan_packers || exit 1; \
 	done
