@@ -173,6 +173,46 @@ int main() {
         free(rows), free(labels), free(workers), free(times), free(bitmap), free(row_off), free(payload);
         remove(path);
     }
-    printf("asan driver: %lld packed rows, 80 csv files and 2 awkward producer streams checked\n", checked);
+    // buffer policy: tables of exactly n / W entries; a batch with more rows than a ring (the superseded-rows pass),
+    // an out-of-range worker (refused before anything is written), state save / restore with a wrong size
+    {
+        const int W = 3, n = 50;
+        void* bufs[W];
+        for (auto& b : bufs) b = psb_buffer_create(4, 8, 0.3f, 16);
+        expect(psb_buffer_set_ring(bufs[0], 12) == 0 && psb_buffer_set_ring(bufs[1], 4) != 0, "set_ring");
+        int* workers = (int*)malloc(n * 4);
+        double* now = (double*)malloc(n * 8);
+        int* ws = (int*)malloc(2 * n * 4);
+        int* win = (int*)malloc(2 * W * 4);
+        int* change = (int*)malloc(4 * W * 4);
+        for (int i = 0; i < n; ++i) workers[i] = i % 5 == 0 ? 1 : 0, now[i] = 10.0 * i;
+        int most = 0;
+        expect(psb_buffers_on_batch2(bufs, W, workers, now, n, ws, win, change, &most) == 0 && most == 40, "on_batch2");
+        int kept0 = 0, kept1 = 0;
+        for (int i = 0; i < n; ++i) {
+            expect(ws[2 * i] == workers[i] && ws[2 * i + 1] >= -1 && ws[2 * i + 1] < 12, "on_batch2: slot range");
+            if (ws[2 * i + 1] >= 0) (workers[i] ? kept1 : kept0)++;
+        }
+        expect(kept0 == 12 && kept1 == 8 && change[4 * 2 + 2] == 0, "on_batch2: rows kept per ring");
+        workers[7] = W;
+        expect(psb_buffers_on_batch2(bufs, W, workers, now, n, ws, win, change, &most) != 0, "on_batch2: bad worker");
+        double* state = (double*)malloc((9 + 16) * 8);
+        expect(psb_buffer_get_state(bufs[0], state, 9 + 15) < 0 && psb_buffer_get_state(bufs[0], state, 9 + 16) == 25, "get_state");
+        expect(psb_buffer_set_state(bufs[2], state, 24) != 0, "set_state: wrong size");
+        void* twin = psb_buffer_create(4, 8, 0.3f, 16);
+        expect(psb_buffer_set_ring(twin, 12) == 0 && psb_buffer_set_state(twin, state, 25) == 0, "set_state");
+        int h1, c1, t1, h2, c2, t2;
+        expect(psb_buffer_on_event(bufs[0], 1e4, &h1, &c1, &t1) == psb_buffer_on_event(twin, 1e4, &h2, &c2, &t2) &&
+                   h1 == h2 && c1 == c2 && t1 == t2, "restored buffer continues like the original");
+        void* tr = psb_tracker_create(2, 1);
+        int replies[4];
+        expect(psb_tracker_on_gradient(tr, 0, 0, replies, 2) >= 0 && psb_tracker_on_gradient(tr, 0, 5, replies, 2) < 0 &&
+                   psb_tracker_on_gradient(tr, 9, 0, replies, 2) < 0, "tracker: protocol violations are refused");
+        psb_tracker_destroy(tr);
+        for (auto& b : bufs) psb_buffer_destroy(b);
+        psb_buffer_destroy(twin);
+        free(workers), free(now), free(ws), free(win), free(change), free(state);
+    }
+    printf("asan driver: %lld packed rows, 80 csv files, 2 awkward producer streams, buffer policy and tracker checked\n", checked);
     return 0;
 }
