@@ -28,14 +28,13 @@ def test_small_sample_sequential_two_workers(tmp_path):
 import pytest
 
 
-@pytest.mark.parametrize("name,features", [("lr_dataset_stripped.csv", 5), ("sample_input_data.csv", 99)])
-def test_headerless_binary_mock_files_train_with_no_header(tmp_path, name, features):
-    """Stand-ins of the reference's two other mock files (mockData/lr_dataset_stripped.csv: 570 rows x 6 columns,
-    mockData/sample_input_data.csv: 49 rows x 100 columns of 0 / 1; no header, binary last column; read by no code
-    of the reference).  Here they stream through the same runner with --no_header, labels 0 / 1 as class rows 0 / 1."""
+def test_headerless_binary_label_file_trains_with_no_header(tmp_path):
+    """The reference ships two more mock files (headerless, binary last column) that none of its code reads.  A file
+    of that kind streams through the same runner with --no_header, labels 0 / 1 as class rows 0 / 1."""
+    name, features = "headerless_binary_label.csv", 12
     path = os.path.join(ROOT, "mockData", name)
     rows = np.loadtxt(path, delimiter=",", ndmin=2)
-    assert rows.shape[1] == features + 1 and set(np.unique(rows[:, -1])) == {0.0, 1.0}
+    assert rows.shape == (400, features + 1) and set(np.unique(rows[:, -1])) == {0.0, 1.0}
     env = dict(os.environ, PYTHONPATH=ROOT)
     r = subprocess.run([sys.executable, "-m", "psb200.apps.server_app_runner", "-training", path, "-test", path,
                         "--no_header", "--num_features", str(features), "--num_classes", "1", "-c", "0", "-p", "0",
@@ -45,5 +44,5 @@ def test_headerless_binary_mock_files_train_with_no_header(tmp_path, name, featu
     s = parse_log(str(tmp_path / "logs-server.csv"), "server")
     w = parse_log(str(tmp_path / "logs-worker.csv"), "worker")
     assert len(s) == 4 and len(w) >= 6
-    assert w[:, 6].max() == (len(rows) + 1) // 2            # every row of the file reached a worker (no line skipped)
-    assert np.all(np.isfinite(s[:, 4])) and s[-1, 5] >= 0.45
+    assert w[:, 6].max() == len(rows) // 2                  # every row of the file reached a worker (no line skipped)
+    assert np.all(np.isfinite(s[:, 4])) and s[-1, 5] > 0.7  # a linear rule with noise: well above chance

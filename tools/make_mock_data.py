@@ -1,9 +1,8 @@
 """Writes the small sample the reference ships as mockData/small-sample/small_sample_reviews_embedded_{training,test}.csv
 (stripped from its checkout, .MISSING_LARGE_BLOBS:1-2): same format (header 0..1023,Score), synthetic content — and
-synthetic stand-ins of the shape of its two other mock files (no code of the reference reads them; here both train
-with --no_header): mockData/lr_dataset_stripped.csv (570 rows: year, month, day-of-cycle, two small integer
-covariates, binary label; no header) and mockData/sample_input_data.csv (49 rows x 100 columns of 0 / 1, the last
-one the label; no header).
+mockData/headerless_binary_label.csv (400 rows x 12 real-valued features, label 0 / 1, no header line): the kind of
+file the reference's two other mock files are (headerless, binary last column; no code of the reference reads them),
+which trains here with --no_header --num_features 12 --num_classes 1.
 Usage: python tools/make_mock_data.py [train_rows test_rows out_dir]"""
 import os
 import sys
@@ -24,22 +23,13 @@ def main():
     write_csv(os.path.join(out, "small_sample_reviews_embedded_training.csv"), gen.train_split(n_train))
     write_csv(os.path.join(out, "small_sample_reviews_embedded_test.csv"), gen.test_split(n_test))
     root = os.path.dirname(out.rstrip(os.sep))
-    rng = np.random.default_rng(1983)
-    with open(os.path.join(root, "lr_dataset_stripped.csv"), "w") as f:      # 38 (year, month) cycles of 15 samples
-        for i in range(570):
-            cycle, k = divmod(i, 15)
-            year, month = 1983 + (cycle + 2) // 12, (cycle + 2) % 12 + 1
-            day = 0 if k == 0 else 3 * k - 1
-            group = cycle % 4 + 1
-            flag = int(rng.random() < 0.1)
-            p = 1.0 / (1.0 + np.exp(-(0.9 * (group - 2.5) - 0.04 * (day - 20) + 1.5 * flag)))
-            f.write(f"{year},{month},{day},{flag},{group},{int(rng.random() < p)}\n")
-    bits = (rng.random((49, 99)) < 0.5).astype(int)
-    w = rng.standard_normal(99)
-    lab = (bits @ w + 0.5 * rng.standard_normal(49) > np.median(bits @ w)).astype(int)
-    with open(os.path.join(root, "sample_input_data.csv"), "w") as f:
-        for r in range(49):
-            f.write(",".join(map(str, bits[r])) + f",{lab[r]}\n")
+    rng = np.random.default_rng(7)
+    X = np.round(rng.standard_normal((400, 12)) * rng.uniform(0.2, 3.0, 12), 3)
+    w = rng.standard_normal(12)
+    lab = (X @ w + 0.8 * rng.standard_normal(400) > 0).astype(int)
+    with open(os.path.join(root, "headerless_binary_label.csv"), "w") as f:
+        for r in range(400):
+            f.write(",".join(f"{v:g}" for v in X[r]) + f",{lab[r]}\n")
     print("wrote", out, "and", root)
 
 
