@@ -519,6 +519,7 @@ extern "C" int psb_buffers_on_batch(void** buffers, int num_buffers, const int* 
 #include <thread>
 
 #include <cuda_fp16.h>
+#include <sys/mman.h>
 #if defined(__SSE2__) && !defined(PSB_NO_SIMD)
 #include <emmintrin.h>
 #endif
@@ -642,6 +643,76 @@ struct ParsePool {
     }
 };
 
+// A PSBROWS1 file (tools/csv_to_rows.py): the rows of a CSV converted once into the palette wire format, mapped
+// read-only.  64-byte header {magic[8], u32 F, u32 version, u64 rows, u64 payload bytes}, then — each section on a
+// 64-byte boundary — u64 offsets[rows + 1] into the payload, i32 labels[rows], u32 bitmap[rows][F / 32], payload.
+struct RowsFile {
+    const uint8_t* base = nullptr;
+    size_t size = 0;
+    uint32_t F = 0;
+    uint64_t n = 0;
+    const uint64_t* off = nullptr;
+    const int32_t* labels = nullptr;
+    const uint32_t* bitmap = nullptr;
+    const uint8_t* payload = nullptr;
+    static size_t up64(size_t x) { return (x + 63) & ~(size_t)63; }
+    bool open(FILE* f) {
+        fseek(f, 0, SEEK_END);
+        const long sz = ftell(f);
+        if (sz < 64) return false;
+        void* m = mmap(nullptr, (size_t)sz, PROT_READ, MAP_PRIVATE, fileno(f), 0);
+        if (m == MAP_FAILED) return false;
+        base = (const uint8_t*)m, size = (size_t)sz;
+        uint32_t version;
+        uint64_t payload_bytes;
+        memcpy(&F, base + 8, 4), memcpy(&version, base + 12, 4), memcpy(&n, base + 16, 8), memcpy(&payload_bytes, base + 24, 8);
+        if (version != 1 || F == 0 || F % 32 != 0 || n > ((uint64_t)1 << 40)) return false;
+        size_t at = 64;
+        off = (const uint64_t*)(base + at), at = up64(at + (size_t)(n + 1) * 8);
+        labels = (const int32_t*)(base + at), at = up64(at + (size_t)n * 4);
+        bitmap = (const uint32_t*)(base + at), at = up64(at + (size_t)n * (F / 32) * 4);
+        payload = base + at;
+        return at + payload_bytes <= size && (n == 0 || at <= size) && off[n] == payload_bytes;
+    }
+    // the payload of row i is what its bitmap says it must be (a damaged file must not make the store kernel read astray)
+    bool row_ok(uint64_t i) const {
+        if (off[i + 1] < off[i] || off[i + 1] - off[i] < 2 || off[i + 1] > off[n]) return false;
+        const uint64_t len = off[i + 1] - off[i];
+        int nnz = 0;
+        for (uint32_t w = 0; w < F / 32; ++w) nnz += __builtin_popcount(bitmap[i * (F / 32) + w]);
+        uint16_t npal;
+        memcpy(&npal, payload + off[i], 2);
+        if (npal > 16 || (off[i] & 1)) return false;
+        const uint64_t want = npal ? 2 + 2 * (uint64_t)npal + ((((uint64_t)nnz + 1) / 2 + 1) & ~(uint64_t)1) : 2 + 2 * (uint64_t)nnz;
+        return len == want;
+    }
+    void close() {
+        if (base) munmap((void*)base, size);
+        base = nullptr;
+    }
+};
+
+// Expands row i of a rows file into dense fp16 (consumers that did not ask for palette batches).
+inline void rows_file_expand(const RowsFile& R, uint64_t i, uint16_t* dst) {
+    memset(dst, 0, (size_t)R.F * 2);
+    const uint8_t* p = R.payload + R.off[i];
+    uint16_t npal;
+    memcpy(&npal, p, 2);
+    const uint8_t* codes = p + 2 + 2 * npal;
+    int k = 0;
+    for (uint32_t w = 0; w < R.F / 32; ++w)
+        for (uint32_t m = R.bitmap[i * (R.F / 32) + w]; m; m &= m - 1, ++k) {
+            uint16_t v;
+            if (npal) {
+                const int c = (codes[k >> 1] >> ((k & 1) * 4)) & 15;
+                memcpy(&v, p + 2 + 2 * c, 2);
+            } else {
+                memcpy(&v, p + 2 + 2 * k, 2);
+            }
+            dst[w * 32 + __builtin_ctz(m)] = v;
+        }
+}
+
 void producer_main(Producer* P) {
     FILE* f = fopen(P->path.c_str(), "rb");
     if (!f) {
@@ -650,15 +721,12 @@ void producer_main(Producer* P) {
     }
     const auto t0 = std::chrono::steady_clock::now();
     auto now_ms = [&] { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count(); };
-    // The file is read in 4 MB blocks and lines are cut with memchr: a row of another rank's partition costs one
-    // scan for its newline, nothing is copied per line.  A line longer than the block grows the block.
-    std::vector<char> buf((size_t)4 << 20);
-    size_t have = 0, pos = 0;                  // buf[pos, have) is unread
-    bool file_done = false;
     long long row_count = 0;
     const long long warm = (long long)P->num_workers * 128;
     int batch = 0, fill = 0;
     double batch_t0 = 0.0;
+    bool prepacked = false;                    // rows file + palette consumer: the batch's packed form is written directly
+    long long pre_bytes = 0;                   //   payload bytes of the batch so far
     ParsePool pool(P, P->parse_threads - 1);
     std::vector<ParseJob> jobs;                // lines of the batch being filled, cut and not yet tokenised
     jobs.reserve((size_t)P->batch_rows);
@@ -674,7 +742,9 @@ void producer_main(Producer* P) {
         flush_jobs();
         if (fill == 0) return;
         const double t_pack = now_ms();
-        if (P->pk_bitmap && P->pk_payload)
+        if (prepacked)
+            P->pk_row_off[(size_t)batch * (P->batch_rows + 1) + fill] = (int)pre_bytes;
+        else if (P->pk_bitmap && P->pk_payload)
             psb_pack_palette_dense(P->rows + (size_t)batch * P->batch_rows * P->F, fill, P->F,
                                    P->pk_bitmap + (size_t)batch * P->batch_rows * (P->F / 32),
                                    P->pk_row_off + (size_t)batch * (P->batch_rows + 1),
@@ -686,7 +756,7 @@ void producer_main(Producer* P) {
                                   P->pk_values + (size_t)batch * P->batch_rows * P->F);
         ms_pack += now_ms() - t_pack;
         P->ready[batch].store(fill, std::memory_order_release);
-        batch = (batch + 1) % P->num_batches, fill = 0;
+        batch = (batch + 1) % P->num_batches, fill = 0, pre_bytes = 0;
     };
     auto wait_free = [&]() -> bool {
         if (P->ready[batch].load(std::memory_order_acquire) == -1) return true;
@@ -698,6 +768,102 @@ void producer_main(Producer* P) {
         ms_wait += now_ms() - t;
         return true;
     };
+    // Row `row_count` of the stream goes to partition row_count % numWorkers (CsvProducer.java:61).  claim(): the slot
+    // of the ring arrays for it when the partition is this rank's (-1: not ours, -2: stopped while waiting for a free
+    // batch), with worker and arrival time filled in; the caller writes the row, then row_done(), then next_row().
+    double t_row = -1.0;                       // one clock read per kept row; every 64th row of other partitions
+    auto claim = [&]() -> long long {
+        const int part = (int)(row_count % P->num_workers);
+        t_row = -1.0;
+        if (part < P->wbegin || part >= P->wbegin + P->wcount) {
+            if ((row_count & 63) == 0) t_row = now_ms();
+            return -1;
+        }
+        if (fill == 0) {
+            if (!wait_free()) return -2;
+            batch_t0 = now_ms();
+        }
+        const size_t o = (size_t)batch * P->batch_rows + fill;
+        t_row = now_ms();
+        P->workers[o] = part - P->wbegin, P->times[o] = t_row;
+        return (long long)o;
+    };
+    auto row_done = [&] {
+        if (++fill == P->batch_rows) publish();
+    };
+    auto next_row = [&] {                      // flush timer and -p pacing (CsvProducer.java:73-82, quirk Q7)
+        ++row_count;
+        P->rows_sent.store(row_count, std::memory_order_relaxed);
+        if (fill && t_row >= 0.0 && t_row - batch_t0 > P->flush_ms) publish();
+        if (P->p_ms > 0 && row_count >= warm) {
+            int sleep_ms = 0;
+            if (P->p_ms <= 1000) {
+                if (row_count % (1000 / P->p_ms) == 0) sleep_ms = 1000;
+            } else {
+                sleep_ms = P->p_ms;
+            }
+            if (sleep_ms) {
+                publish();
+                for (int s = 0; s < sleep_ms && !P->stop.load(); s += 10)
+                    std::this_thread::sleep_for(std::chrono::milliseconds(std::min(10, sleep_ms - s)));
+            }
+        }
+    };
+    auto finish = [&](int eof_code) {
+        publish();
+        fclose(f);
+        if (getenv("PSB_PRODUCER_TRACE"))
+            fprintf(stderr, "psb producer: %lld rows read in %.1f ms with %d tokenising thread(s): tokenise %.1f ms, pack %.1f ms, "
+                            "waiting for a free batch %.1f ms\n", row_count, now_ms(), P->parse_threads, ms_parse, ms_pack, ms_wait);
+        P->eof.store(eof_code);
+    };
+
+    char magic[8] = {0};
+    const size_t got_magic = fread(magic, 1, 8, f);
+    if (got_magic == 8 && memcmp(magic, "PSBROWS1", 8) == 0) {
+        // ---- converted rows: nothing to tokenise; a kept row is two copies (bitmap, payload) or one expansion
+        RowsFile R;
+        if (!R.open(f) || (int)R.F != P->F) {
+            R.close();
+            finish(3);                         // damaged, or written for another feature count
+            return;
+        }
+        prepacked = P->pk_bitmap && P->pk_payload;
+        const size_t words = R.F / 32;
+        bool bad = false;
+        for (uint64_t i = 0; i < R.n && !P->stop.load(std::memory_order_relaxed); ++i) {
+            const long long o = claim();
+            if (o == -2) break;
+            if (o >= 0) {
+                if (!R.row_ok(i)) {
+                    bad = true;
+                    break;
+                }
+                P->labels[o] = R.labels[i];
+                if (prepacked) {
+                    const size_t len = (size_t)(R.off[i + 1] - R.off[i]);
+                    memcpy(P->pk_bitmap + (size_t)o * words, R.bitmap + i * words, words * 4);
+                    P->pk_row_off[(size_t)batch * (P->batch_rows + 1) + fill] = (int)pre_bytes;
+                    memcpy(P->pk_payload + (size_t)batch * P->pk_stride + pre_bytes, R.payload + R.off[i], len);
+                    pre_bytes += (long long)len;
+                } else {
+                    rows_file_expand(R, i, P->rows + (size_t)o * P->F);
+                }
+                row_done();
+            }
+            next_row();
+        }
+        R.close();
+        finish(bad ? 3 : 1);
+        return;
+    }
+    fseek(f, 0, SEEK_SET);
+
+    // ---- CSV text.  The file is read in 4 MB blocks and lines are cut with memchr: a row of another rank's
+    // partition costs one scan for its newline, nothing is copied per line.  A line longer than the block grows it.
+    std::vector<char> buf((size_t)4 << 20);
+    size_t have = 0, pos = 0;                  // buf[pos, have) is unread
+    bool file_done = false;
     // next line without its terminator in [*lp, *le); false at the end of the file
     auto next_line = [&](const char** lp, const char** le) -> bool {
         for (;;) {
@@ -734,45 +900,16 @@ void producer_main(Producer* P) {
         }
         first = false;
         if (le == lp) continue;
-        const int part = (int)(row_count % P->num_workers);
-        double t_row = -1.0;                   // one clock read per kept row; every 64th row of other partitions
-        if (part >= P->wbegin && part < P->wbegin + P->wcount) {
-            if (fill == 0) {
-                if (!wait_free()) break;
-                batch_t0 = now_ms();
-            }
-            const size_t o = (size_t)batch * P->batch_rows + fill;
-            t_row = now_ms();
-            P->workers[o] = part - P->wbegin, P->times[o] = t_row;
-            jobs.push_back(ParseJob{lp, le, o});
+        const long long o = claim();
+        if (o == -2) break;
+        if (o >= 0) {
+            jobs.push_back(ParseJob{lp, le, (size_t)o});
             if (P->parse_threads == 1 || (P->p_ms > 0 && row_count >= warm)) flush_jobs();     // paced rows go out one by one
-            if (++fill == P->batch_rows) publish();
-        } else if ((row_count & 63) == 0) {
-            t_row = now_ms();
+            row_done();
         }
-        ++row_count;
-        P->rows_sent.store(row_count, std::memory_order_relaxed);
-        if (fill && t_row >= 0.0 && t_row - batch_t0 > P->flush_ms) publish();
-        if (P->p_ms > 0 && row_count >= warm) {
-            int sleep_ms = 0;
-            if (P->p_ms <= 1000) {
-                if (row_count % (1000 / P->p_ms) == 0) sleep_ms = 1000;
-            } else {
-                sleep_ms = P->p_ms;
-            }
-            if (sleep_ms) {
-                publish();
-                for (int s = 0; s < sleep_ms && !P->stop.load(); s += 10)
-                    std::this_thread::sleep_for(std::chrono::milliseconds(std::min(10, sleep_ms - s)));
-            }
-        }
+        next_row();
     }
-    publish();
-    fclose(f);
-    if (getenv("PSB_PRODUCER_TRACE"))
-        fprintf(stderr, "psb producer: %lld rows read in %.1f ms with %d tokenising thread(s): tokenise %.1f ms, pack %.1f ms, "
-                        "waiting for a free batch %.1f ms\n", row_count, now_ms(), P->parse_threads, ms_parse, ms_pack, ms_wait);
-    P->eof.store(1);
+    finish(1);
 }
 }  // namespace
 

@@ -334,7 +334,10 @@ int psb_buffers_on_batch2(void** buffers, int num_buffers, const int* workers, c
  * and fills a ring of `num_batches` caller-provided PINNED batches (h_rows_f16[num_batches][batch_rows][F],
  * h_labels / h_workers / h_times [num_batches][batch_rows]); -p pacing as in the reference.
  * poll: 1 = batch ready (*batch, *n) and handed to the caller until psb_producer_release (several may be held,
- * released in poll order), 0 = nothing; *eof = 1 once the file is exhausted and every batch was polled. */
+ * released in poll order), 0 = nothing; *eof = 1 once the file is exhausted and every batch was polled, 2 when it
+ * could not be opened, 3 when it is a damaged rows file.
+ * `path` may also name a PSBROWS1 rows file (tools/csv_to_rows.py: the same rows converted once into the palette
+ * wire format; `has_header` is ignored): nothing is tokenised, a kept row is two copies into the batch. */
 void* psb_producer_start(const char* path, int has_header, int num_workers_total, int worker_begin,
                          int worker_count, int num_features, int p_ms, int batch_rows, int num_batches,
                          void* h_rows_f16, int* h_labels, int* h_workers, double* h_times, int flush_ms);

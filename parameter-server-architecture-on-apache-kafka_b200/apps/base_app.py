@@ -25,6 +25,9 @@ def load_csv_or_synthetic(path: str, cfg: PSConfig, kind: str) -> CSRBatch:
         return gen.test_split(n, seed=seed + 2) if kind == "test" else gen.train_split(n, seed=seed + 1)
     if not os.path.exists(path):
         raise FileNotFoundError(f"{kind} data file not found: {path}")
+    from ..data import is_rows_file, read_rows_file
+    if is_rows_file(path):                     # a CSV converted once by tools/csv_to_rows.py
+        return read_rows_file(path)
     try:
         from ..ops import native
         if native.available():

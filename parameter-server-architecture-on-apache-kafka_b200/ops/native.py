@@ -453,6 +453,8 @@ class StreamProducer:
         b, n, e = C.c_int(), C.c_int(), C.c_int()
         if lib().psb_producer_poll(self.h, C.byref(b), C.byref(n), C.byref(e)):
             return b.value, n.value, 0
+        if e.value == 3:
+            raise NativeError("the rows file is damaged or was written for another number of features")
         return None, 0, e.value
 
     def packed(self, batch: int, n: int) -> "PackedRows":

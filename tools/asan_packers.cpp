@@ -16,7 +16,51 @@ static void expect(bool ok, const char* what) {
     }
 }
 
-int main() {
+// asan_packers <rows file> <num_features> <rows>: stream a PSBROWS1 file through the producer thread into buffers of
+// exactly the documented size, as palette batches and as dense batches (tests/test_sanitizers.py writes the file).
+static int stream_rows_file(const char* path, int F, long long want_rows) {
+    for (int palette = 0; palette < 2; ++palette) {
+        const int batch_rows = 96, nb = 3;
+        uint16_t* rows = (uint16_t*)malloc((size_t)nb * batch_rows * F * 2);
+        int* labels = (int*)malloc((size_t)nb * batch_rows * 4);
+        int* workers = (int*)malloc((size_t)nb * batch_rows * 4);
+        double* times = (double*)malloc((size_t)nb * batch_rows * 8);
+        uint32_t* bitmap = (uint32_t*)malloc((size_t)nb * batch_rows * (F / 32) * 4);
+        int* row_off = (int*)malloc((size_t)nb * (batch_rows + 1) * 4);
+        const long long stride = (long long)batch_rows * (2 * F + 2);
+        uint8_t* payload = (uint8_t*)malloc((size_t)nb * stride);
+        void* p = palette ? psb_producer_start_palette(path, 1, 3, 0, 3, F, 0, batch_rows, nb, rows, labels, workers, times,
+                                                       5, bitmap, row_off, payload, stride)
+                          : psb_producer_start(path, 1, 3, 0, 3, F, 0, batch_rows, nb, rows, labels, workers, times, 5);
+        expect(p != nullptr, "producer_start on a rows file");
+        long long got = 0, checksum = 0;
+        int eof = 0;
+        for (;;) {
+            int b = 0, n = 0;
+            if (psb_producer_poll(p, &b, &n, &eof)) {
+                if (palette) {
+                    const int* off = row_off + (size_t)b * (batch_rows + 1);
+                    expect(off[0] == 0 && off[n] <= stride, "rows file: payload offsets of a batch");
+                    for (int i = 0; i < off[n]; ++i) checksum += payload[(size_t)b * stride + i];
+                } else {
+                    for (size_t i = 0; i < (size_t)n * F; ++i) checksum += rows[(size_t)b * batch_rows * F + i];
+                }
+                got += n;
+                psb_producer_release(p, b);
+            } else if (eof) {
+                break;
+            }
+        }
+        expect(eof == 1 && got == want_rows, "rows file: wrong number of rows");
+        psb_producer_stop(p);
+        free(rows), free(labels), free(workers), free(times), free(bitmap), free(row_off), free(payload);
+        printf("asan driver: rows file as %s batches: %lld rows, checksum %lld\n", palette ? "palette" : "dense", got, checksum);
+    }
+    return 0;
+}
+
+int main(int argc, char** argv) {
+    if (argc == 4) return stream_rows_file(argv[1], atoi(argv[2]), atoll(argv[3]));
     std::mt19937 rng(7);
     const double densities[] = {0.0, 0.02, 0.05, 0.3, 0.9, 1.0};
     long long checked = 0;

@@ -70,6 +70,29 @@ def main():
                                  f"{parts}, {threads} tokenising thread{'s' if threads > 1 else ''})",
                         "file_rows_per_s": a.rows / t, "kept_rows_per_s": a.rows / parts / t})
         os.environ.pop("PSB_PRODUCER_THREADS", None)
+        # the same rows converted once into a rows file (tools/csv_to_rows.py): nothing to tokenise
+        from psb200.data import write_rows_file
+        rpath = os.path.join(d, "rows.psbrows")
+        rsize = write_rows_file(rpath, batch)
+        for parts in (1, 8):
+            def stream_rows():
+                prod = native.StreamProducer(rpath, parts, 0, 1, F, 0, batch_rows=512, num_batches=4, packed="palette")
+                got = 0
+                while True:
+                    b, n, eof = prod.poll()
+                    if b is None:
+                        if eof:
+                            break
+                        time.sleep(0.0002)
+                        continue
+                    got += n
+                    prod.release(b)
+                prod.stop()
+                assert got == (a.rows + parts - 1) // parts, got
+            t = best(stream_rows, max(3, a.reps))
+            out.append({"stage": f"producer, rows file (palette-packed batches, keeps 1 row in {parts})",
+                        "file_rows_per_s": a.rows / t, "kept_rows_per_s": a.rows / parts / t,
+                        "bytes_per_row": rsize / a.rows})
 
     for palette in (False, True):
         pk = native.PackedRows(a.rows, F, pin=False, palette=palette)
