@@ -81,3 +81,17 @@ def test_plots_are_written_headless(tmp_path):
         w, h = _png_size(os.path.join(tmp_path, n))
         assert w >= 600 and h >= 360
     assert "consistency: sequential, bounded_delay_10, eventual" in open(tmp_path / "LEGEND.txt").read()
+
+
+def test_ground_truth_trainer_reports_like_the_reference_notebook():
+    """python-ground-truth-algorithm.ipynb prints one speed / validation line per epoch and a classification report;
+    the offline trainer on the shipped small sample does the same."""
+    sample = os.path.join(ROOT, "mockData", "small-sample")
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "evaluation", "ground_truth.py"),
+                        os.path.join(sample, "small_sample_reviews_embedded_training.csv"),
+                        os.path.join(sample, "small_sample_reviews_embedded_test.csv")],
+                       capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stderr
+    epochs = [ln for ln in r.stdout.splitlines() if ln.startswith("Epoch[")]
+    assert len(epochs) == 10 and all("samples/sec" in ln and "Validation-Score-accuracy=" in ln for ln in epochs)
+    assert "weighted avg" in r.stdout and "precision" in r.stdout
