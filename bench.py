@@ -161,6 +161,9 @@ def main():
         raise SystemExit(f"--gpus {a.gpus} but WORLD_SIZE={world}")
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
+    from psb200.utils.numa import bind_to_device_node
+    numa = bind_to_device_node(local)      # threads and pinned staging memory next to this rank's GPU (best effort,
+    #                                        never raises; None on a single-node box or with PSB_NUMA_BIND=0)
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         os.environ.setdefault("NCCL_DEBUG", "WARN")          # keep stdout to the one JSON line
@@ -329,7 +332,7 @@ def main():
                        "parallelism": f"ps-dp{world} ({W} workers/GPU, {world} server shards)",
                        "num_workers": W * world, "buffer_rows": cap, "density": a.density,
                        "local_solver": a.solver, "consistency_model": a.consistency_model, "statistics": a.stats,
-                       "clocks_per_launch": cpl,
+                       "clocks_per_launch": cpl, "numa": numa,
                        "l2": f"inputs larger than L2 ({W * cap * F * 2 / 2**20:.0f} MiB of rows per GPU streamed per pass)",
                        "evals_per_step": float(info[:, 0].mean()), "status": status,
                        "cycles64_stats_solve_push_total": [float(info[:, k].mean()) for k in (4, 5, 6, 7)],

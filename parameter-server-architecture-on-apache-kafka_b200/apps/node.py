@@ -68,6 +68,8 @@ def main(argv: Optional[List[str]] = None) -> int:
     local = int(os.environ.get("LOCAL_RANK", "0"))
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
+    from ..utils.numa import bind_to_device_node
+    bind_to_device_node(local)                      # threads and pinned batches next to this rank's GPU (best effort)
     ctl = None                                      # host-side control group (stop agreement, barriers)
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
