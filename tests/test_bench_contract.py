@@ -46,3 +46,21 @@ def test_defaults_and_no_cpu_fallback():
     if not has_gpu:                                   # our arm on a box without a GPU: an error, never a silent CPU run
         r = _run(["--steps", "3", "--warmup", "3"])
         assert r.returncode != 0 and r.stdout.strip() == ""
+
+
+def test_graft_entry_build_compiles_and_imports():
+    """__graft_entry__.build(): every source compiled for sm_100a in-tree (incremental: up-to-date objects are kept),
+    package importable, library loadable — without a GPU."""
+    import shutil
+
+    import pytest
+    if shutil.which("nvcc") is None and not os.path.exists("/usr/local/cuda/bin/nvcc"):
+        pytest.skip("no nvcc")
+    sys.path.insert(0, ROOT)
+    import __graft_entry__ as entry
+    entry.build()
+    from psb200.ops import native
+    assert native.available() and native.lib().psb_version() >= 100
+    assert callable(entry.smoke)
+    flags = open(os.path.join(ROOT, "build.sh")).read()
+    assert "arch=compute_100a,code=sm_100a" in flags and "-lineinfo" in flags
