@@ -18,5 +18,13 @@ for src in csrc/*.cu csrc/*.cpp; do
 done
 wait
 for obj in $OBJS; do [ -f "$obj" ] || { echo "build failed: $obj missing"; exit 1; }; done
-$NVCC -shared -gencode arch=compute_100a,code=sm_100a -o "$OUT" $OBJS -lcudart
-echo "built $OUT"
+stale=0
+[ -f "$OUT" ] || stale=1
+for obj in $OBJS; do [ "$obj" -nt "$OUT" ] && stale=1; done
+if [ "$stale" = 1 ]; then
+  # linked under another name and moved into place: a process that has the old library loaded keeps its own copy
+  $NVCC -shared -gencode arch=compute_100a,code=sm_100a -o "$OUT.new" $OBJS -lcudart && mv -f "$OUT.new" "$OUT"
+  echo "built $OUT"
+else
+  echo "up to date: $OUT"
+fi
