@@ -10,7 +10,7 @@ mkdir -p "$BUILD"
 OBJS=""
 for src in csrc/*.cu csrc/*.cpp; do
   obj="$BUILD/$(basename "${src%.*}").o"
-  if [ ! -f "$obj" ] || [ "$src" -nt "$obj" ] || [ -n "$(find csrc include -newer "$obj" \( -name '*.cuh' -o -name '*.h' \) | head -1)" ]; then
+  if [ ! -f "$obj" ] || [ "$src" -nt "$obj" ] || [ -n "$(find csrc include -newer "$obj" \( -name '*.cuh' -o -name '*.h' -o -name '*.hpp' \) | head -1)" ]; then
     rm -f "$obj"
     $NVCC $FLAGS ${PSB_PTXAS_V:+-Xptxas -v} -x cu -c "$src" -o "$obj" &
   fi

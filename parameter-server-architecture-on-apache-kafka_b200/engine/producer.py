@@ -10,7 +10,7 @@ Quirk Q7: the integer division makes ``p > 1000`` a modulo by zero there; here
 ``p > 1000`` means "sleep p ms per row" and ``p == 0`` means unthrottled.
 
 ``PacedSchedule`` is the pure timing rule on a virtual clock (what the C++
-producer thread in ``csrc/host_runtime.cpp`` executes against the wall clock).
+producer thread in ``csrc/host_producer.cpp`` executes against the wall clock).
 """
 from __future__ import annotations
 

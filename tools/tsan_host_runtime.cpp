@@ -1,4 +1,4 @@
-// ThreadSanitizer driver for the C++ host runtime (csrc/host_runtime.cpp): the streaming producer thread filling its
+// ThreadSanitizer driver for the C++ host runtime (csrc/host_*.cpp): the streaming producer thread filling its
 // ring of batches (cut lines, tokenise them with two helper threads, palette-pack, publish) against a consumer that polls, holds several batches at a
 // time and releases them in order — the access pattern of apps/node.py and apps/p2p_apps.py — plus the buffer
 // policy and tracker used from a second thread the way the engine's slot-assignment helper thread uses them.
