@@ -9,9 +9,11 @@
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
+#include <sys/mman.h>
 
 #include <algorithm>
 #include <string>
+#include <thread>
 #include <vector>
 
 #include "../include/psb200.h"
@@ -109,6 +111,120 @@ extern "C" int psb_csv_parse(const char* path, int has_header, long long* indptr
     }
     return 0;
 }
+
+// One pass, several threads: the file is cut into chunks at line ends, every chunk is tokenised into its own
+// vectors, psb_csv_fill lays them out as one CSR.  (psb_csv_count + psb_csv_parse read and tokenise the file twice.)
+namespace {
+struct CsvChunk {
+    std::vector<long long> row_end;            // non-zeros of the chunk up to and including each row
+    std::vector<int> indices, labels;
+    std::vector<float> values;
+    int cols = 0;
+};
+struct CsvFile {
+    std::vector<CsvChunk> chunks;
+    long long rows = 0, nnz = 0;
+    int cols = 0;
+};
+void csv_parse_chunk(const char* p, const char* end, CsvChunk* out) {
+    out->indices.reserve((size_t)(end - p) / 32), out->values.reserve((size_t)(end - p) / 32);
+    out->labels.reserve((size_t)(end - p) / 1024), out->row_end.reserve((size_t)(end - p) / 1024);
+    while (p < end) {
+        const char* e = (const char*)memchr(p, '\n', (size_t)(end - p));
+        if (!e) e = end;
+        const char* le = e;
+        while (le > p && (le[-1] == '\r' || le[-1] == ' ')) --le;
+        if (le > p) {
+            int nc = 0;
+            out->labels.push_back(parse_line(p, le, &nc, [&](int c, float v) {
+                out->indices.push_back(c), out->values.push_back(v);
+            }));
+            out->row_end.push_back((long long)out->indices.size());
+            if (nc - 1 > out->cols) out->cols = nc - 1;
+        }
+        p = e + 1;
+    }
+}
+}  // namespace
+
+extern "C" void* psb_csv_open(const char* path, int has_header, int threads) {
+    // mapped, not read: the threads fault their own chunks in, nothing is copied or zero-filled first
+    FILE* fp = path ? fopen(path, "rb") : nullptr;
+    if (!fp) {
+        psb_set_error("cannot open %s", path ? path : "(null)");
+        return nullptr;
+    }
+    fseek(fp, 0, SEEK_END);
+    const long size = ftell(fp);
+    if (size <= 0) {
+        fclose(fp);
+        return new CsvFile();
+    }
+    void* map = mmap(nullptr, (size_t)size, PROT_READ, MAP_PRIVATE, fileno(fp), 0);
+    fclose(fp);
+    if (map == MAP_FAILED) {
+        psb_set_error("cannot map %s", path);
+        return nullptr;
+    }
+    struct Unmap {
+        void* m;
+        size_t n;
+        ~Unmap() { munmap(m, n); }
+    } unmap{map, (size_t)size};
+    const char* p = (const char*)map;
+    const char* end = p + size;
+    if (has_header) {
+        const char* e = (const char*)memchr(p, '\n', (size_t)(end - p));
+        p = e ? e + 1 : end;
+    }
+    const size_t bytes = (size_t)(end - p);
+    if (threads <= 0) threads = (int)std::min(8u, std::max(1u, std::thread::hardware_concurrency()));
+    threads = (int)std::max<size_t>(1, std::min<size_t>((size_t)threads, bytes >> 20));      // >= 1 MB of text per thread
+    std::vector<const char*> cut((size_t)threads + 1, end);
+    cut[0] = p;
+    for (int t = 1; t < threads; ++t) {
+        const char* q = p + bytes * (size_t)t / (size_t)threads;
+        if (q < cut[(size_t)t - 1]) q = cut[(size_t)t - 1];
+        const char* e = q < end ? (const char*)memchr(q, '\n', (size_t)(end - q)) : nullptr;
+        cut[(size_t)t] = e ? e + 1 : end;
+    }
+    CsvFile* f = new CsvFile();
+    f->chunks.resize((size_t)threads);
+    std::vector<std::thread> th;
+    for (int t = 1; t < threads; ++t)
+        th.emplace_back(csv_parse_chunk, cut[(size_t)t], cut[(size_t)t + 1], &f->chunks[(size_t)t]);
+    csv_parse_chunk(cut[0], cut[1], &f->chunks[0]);
+    for (auto& t : th) t.join();
+    for (const auto& c : f->chunks) {
+        f->rows += (long long)c.labels.size(), f->nnz += (long long)c.indices.size();
+        f->cols = std::max(f->cols, c.cols);
+    }
+    return f;
+}
+extern "C" int psb_csv_shape(void* h, long long* n_rows, long long* n_nnz, int* n_cols) {
+    const CsvFile* f = (const CsvFile*)h;
+    if (!f) return PSB_E_INVALID;
+    *n_rows = f->rows, *n_nnz = f->nnz, *n_cols = f->cols;
+    return 0;
+}
+// indptr[rows + 1], indices / values [nnz], labels [rows]
+extern "C" int psb_csv_fill(void* h, long long* indptr, int* indices, float* values, int* labels) {
+    const CsvFile* f = (const CsvFile*)h;
+    if (!f || !indptr || !indices || !values || !labels) return PSB_E_INVALID;
+    long long row = 0, k = 0;
+    indptr[0] = 0;
+    for (const auto& c : f->chunks) {
+        for (size_t r = 0; r < c.labels.size(); ++r) indptr[row + 1 + (long long)r] = k + c.row_end[r];
+        if (!c.labels.empty()) memcpy(labels + row, c.labels.data(), c.labels.size() * sizeof(int));
+        if (!c.indices.empty()) {
+            memcpy(indices + k, c.indices.data(), c.indices.size() * sizeof(int));
+            memcpy(values + k, c.values.data(), c.values.size() * sizeof(float));
+        }
+        row += (long long)c.labels.size(), k += (long long)c.indices.size();
+    }
+    return 0;
+}
+extern "C" void psb_csv_close(void* h) { delete (CsvFile*)h; }
 
 // ------------------------------------------------------------------ consistency tracker
 namespace {

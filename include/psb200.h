@@ -304,6 +304,12 @@ long long psb_pack_bitmap_dense(const uint16_t* rows, long long n_rows, int num_
 int psb_csv_count(const char* path, int has_header, long long* n_rows, long long* n_nnz, int* n_cols);
 int psb_csv_parse(const char* path, int has_header, long long* indptr, int* indices, float* values,
                   int* labels, long long n_rows, long long n_nnz);
+/* The same in one pass over the file, tokenised by `threads` threads (<= 0: up to 8): open, ask for the shape, fill
+ * caller arrays indptr[rows + 1] / indices[nnz] / values[nnz] / labels[rows], close.  NULL when the file cannot be read. */
+void* psb_csv_open(const char* path, int has_header, int threads);
+int psb_csv_shape(void* csv, long long* n_rows, long long* n_nnz, int* n_cols);
+int psb_csv_fill(void* csv, long long* indptr, int* indices, float* values, int* labels);
+void psb_csv_close(void* csv);
 
 /* Consistency tracker (MessageTracker.java) — returns replies as (worker, clock) pairs */
 void* psb_tracker_create(int num_workers, int consistency_model);

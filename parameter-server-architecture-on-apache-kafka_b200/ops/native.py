@@ -130,6 +130,12 @@ def lib() -> C.CDLL:
     L.psb_pack_palette_dense.argtypes = [vp, C.c_longlong, C.c_int, vp, vp, vp, C.c_longlong]
     L.psb_ring_store_palette.argtypes = [vp, ip, vp, ip, ip, C.c_int, vp, ip, C.c_int, C.c_int, vp]
     L.psb_csv_parse.argtypes = [C.c_char_p, C.c_int, vp, vp, vp, vp, C.c_longlong, C.c_longlong]
+    L.psb_csv_open.restype = C.c_void_p
+    L.psb_csv_open.argtypes = [C.c_char_p, C.c_int, C.c_int]
+    L.psb_csv_shape.argtypes = [vp, C.POINTER(C.c_longlong), C.POINTER(C.c_longlong), C.POINTER(C.c_int)]
+    L.psb_csv_fill.argtypes = [vp, vp, vp, vp, vp]
+    L.psb_csv_close.argtypes = [vp]
+    L.psb_csv_close.restype = None
     L.psb_tracker_create.restype = C.c_void_p
     L.psb_tracker_create.argtypes = [C.c_int, C.c_int]
     L.psb_tracker_destroy.argtypes = [vp]
@@ -197,7 +203,28 @@ def _stream(stream=None) -> int:
 
 
 # ------------------------------------------------------------------ host runtime wrappers
-def csv_to_csr(path: str, has_header: bool = True):
+def csv_to_csr(path: str, has_header: bool = True, threads: int = 0):
+    """The whole CSV as a CSR batch: one pass over the text, tokenised by `threads` threads (0: up to 8)."""
+    from ..data.csr import CSRBatch
+    L = lib()
+    h = L.psb_csv_open(path.encode(), int(has_header), int(threads))
+    if not h:
+        raise NativeError("csv_open: " + L.psb_last_error().decode())
+    try:
+        n_rows, n_nnz, n_cols = C.c_longlong(), C.c_longlong(), C.c_int()
+        check(L.psb_csv_shape(h, C.byref(n_rows), C.byref(n_nnz), C.byref(n_cols)), "csv_shape")
+        indptr = np.zeros(n_rows.value + 1, dtype=np.int64)
+        indices = np.zeros(max(1, n_nnz.value), dtype=np.int32)
+        values = np.zeros(max(1, n_nnz.value), dtype=np.float32)
+        labels = np.zeros(max(1, n_rows.value), dtype=np.int32)
+        check(L.psb_csv_fill(h, indptr.ctypes.data, indices.ctypes.data, values.ctypes.data, labels.ctypes.data), "csv_fill")
+    finally:
+        L.psb_csv_close(h)
+    return CSRBatch(indptr, indices[: n_nnz.value], values[: n_nnz.value], labels[: n_rows.value], n_cols.value)
+
+
+def csv_to_csr_two_pass(path: str, has_header: bool = True):
+    """The same through psb_csv_count + psb_csv_parse (no allocation inside the library: the caller owns every array)."""
     from ..data.csr import CSRBatch
     L = lib()
     n_rows, n_nnz, n_cols = C.c_longlong(), C.c_longlong(), C.c_int()

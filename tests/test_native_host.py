@@ -117,6 +117,32 @@ def test_csv_tokenizer_matches_numpy_reader(tmp_path):
     assert len(a) == 301 and np.allclose(a.row(300)[1], [1e-3, -0.25]) and a.row(300)[2] == 4
 
 
+def test_one_pass_loader_equals_the_two_pass_loader_for_every_thread_count(tmp_path):
+    """psb_csv_open / shape / fill / close: the file mapped once and tokenised by several threads, each on its own
+    chunk cut at a line end — the same CSR as psb_csv_count + psb_csv_parse, whatever the number of threads; files
+    that are empty, hold only a header, or lack the final newline."""
+    b = ReviewGenerator(num_features=1024, mean_len=60).train_split(2200)          # ~5 MB of text: up to 4 chunks
+    path = os.path.join(tmp_path, "big.csv")
+    write_csv(path, b)
+    with open(path, "rb+") as f:                                                   # no newline at the end
+        f.seek(-1, os.SEEK_END)
+        f.truncate()
+    ref = native.csv_to_csr_two_pass(path)
+    assert len(ref) == 2200 and ref.num_features == 1024
+    for threads in (1, 2, 3, 4, 0):
+        a = native.csv_to_csr(path, threads=threads)
+        assert np.array_equal(a.indptr, ref.indptr) and np.array_equal(a.indices, ref.indices), threads
+        assert np.array_equal(a.values, ref.values) and np.array_equal(a.labels, ref.labels) and a.num_features == 1024
+    empty, head = os.path.join(tmp_path, "empty.csv"), os.path.join(tmp_path, "head.csv")
+    open(empty, "w").close()
+    open(head, "w").write("0,1,2,Score\n")
+    for path2 in (empty, head):
+        a = native.csv_to_csr(path2)
+        assert len(a) == 0 and a.indptr.tolist() == [0]
+    with pytest.raises(native.NativeError):
+        native.csv_to_csr(os.path.join(tmp_path, "nope.csv"))
+
+
 def test_csv_tokenizer_field_forms(tmp_path):
     """Every way a field is taken: the 8-byte run skip of "0,0,0,0," at every alignment, "0.0", signs, blanks,
     leading zeros, long digit strings (strtof beyond 18 digits), exponents, a zero label and a missing final newline

@@ -150,6 +150,39 @@ int main(int argc, char** argv) {
             free(indptr), free(indices), free(values), free(labels);
             remove(path);
         }
+    // the one-pass loader on ~3.3 MB of text: three chunks cut at line ends, tokenised side by side
+    {
+        char path[] = "/tmp/psb_asan_big_XXXXXX";
+        const int fd = mkstemp(path);
+        expect(fd >= 0, "mkstemp");
+        FILE* f = fdopen(fd, "w");
+        const int cols = 500, lines = 3300;
+        for (int r = 0; r < lines; ++r) {
+            for (int c = 0; c < cols; ++c) fputs(c == r % cols ? "-0.125," : "0,", f);
+            fprintf(f, "%d%s", r % 6, r + 1 < lines ? "\n" : "");
+        }
+        fclose(f);
+        for (int threads : {1, 3, 64}) {
+            void* h = psb_csv_open(path, 0, threads);
+            expect(h != nullptr, "csv_open");
+            long long n_rows = 0, n_nnz = 0;
+            int n_cols = 0;
+            expect(psb_csv_shape(h, &n_rows, &n_nnz, &n_cols) == 0 && n_rows == lines && n_nnz == lines && n_cols == cols,
+                   "csv_open: wrong shape");
+            long long* indptr = (long long*)malloc((size_t)(n_rows + 1) * 8);
+            int* indices = (int*)malloc((size_t)n_nnz * 4);
+            float* values = (float*)malloc((size_t)n_nnz * 4);
+            int* labels = (int*)malloc((size_t)n_rows * 4);
+            expect(psb_csv_fill(h, indptr, indices, values, labels) == 0, "csv_fill");
+            for (int r = 0; r < lines; ++r)
+                expect(indptr[r + 1] == r + 1 && indices[r] == r % cols && values[r] == -0.125f && labels[r] == r % 6,
+                       "csv_fill: wrong row");
+            psb_csv_close(h);
+            free(indptr), free(indices), free(values), free(labels);
+        }
+        remove(path);
+        expect(psb_csv_open("/tmp/psb_asan_no_such_file.csv", 1, 0) == nullptr, "csv_open of a missing file");
+    }
     // producer thread on awkward text: an empty line, CRLF, a line longer than the 4 MB read block (the block grows),
     // more columns than features, junk fields, no newline at the end; with and without tokenising helper threads
     for (const char* threads : {"1", "3"}) {

@@ -44,9 +44,13 @@ def main():
         path = os.path.join(d, "rows.csv")
         write_csv(path, batch)
         size = os.path.getsize(path)
-        t = best(lambda: native.csv_to_csr(path), a.reps)
-        out.append({"stage": "csv_count+parse", "rows_per_s": a.rows / t, "MB_per_s": size / t / 1e6,
+        t = best(lambda: native.csv_to_csr_two_pass(path), a.reps)
+        out.append({"stage": "csv_count+parse (two passes)", "rows_per_s": a.rows / t, "MB_per_s": size / t / 1e6,
                     "file_MB": size / 1e6})
+        for threads in (1, 4, 8):
+            t = best(lambda: native.csv_to_csr(path, threads=threads), a.reps)
+            out.append({"stage": f"csv_open/fill (one pass, mapped file, {threads} thread{'s' if threads > 1 else ''})",
+                        "rows_per_s": a.rows / t, "MB_per_s": size / t / 1e6})
         for packed, parts, threads in ((False, 1, 1), (False, 8, 1), ("palette", 1, 1), ("palette", 1, 2),
                                        ("palette", 1, 4)):
             # parts: this rank keeps every row / one partition in eight; threads: PSB_PRODUCER_THREADS
